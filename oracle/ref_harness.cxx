@@ -1,0 +1,384 @@
+// TEST INFRASTRUCTURE ONLY -- never linked or loaded by the product path.
+//
+// A C-ABI over the UNMODIFIED reference (compiled in place from /root/reference by
+// oracle/Makefile into oracle/_ref/libdesref.so).  It lets tests/ and the cpu_baseline
+// leg of bench.py drive the reference's own hot functions one by one and read/write
+// the reference's own `Variables` arrays, so that
+//   * the C restatement in oracle/des_oracle.c is pinned against the real thing, and
+//   * the CUDA path is compared with the real thing on the GPU box's host cores.
+//
+// It re-states nothing: every numeric statement executed here lives in the reference
+// TUs (fields.cxx, rheology.cxx, geometry.cxx, bc.cxx, matprops.cxx, ic.cxx, mesh.cxx,
+// dynearthsol.cxx with `main` renamed on the command line).  Only the call ORDER of one
+// time step is repeated (dynearthsol.cxx:768-894), minus output/remesh/monitor calls.
+#include <cstring>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include <chrono>
+
+#include "constants.hpp"
+#include "parameters.hpp"
+#include "bc.hpp"
+#include "fields.hpp"
+#include "geometry.hpp"
+#include "ic.hpp"
+#include "input.hpp"
+#include "matprops.hpp"
+#include "mesh.hpp"
+#include "output.hpp"
+#include "rheology.hpp"
+#include "phasechanges.hpp"
+#include "utils.hpp"
+
+// defined in dynearthsol.cxx (non-static, no header)
+void init_var(const Param& param, Variables& var);
+void init(const Param& param, Variables& var);
+void update_mesh(const Param& param, Variables& var);
+
+namespace {
+Param *g_param = nullptr;
+Variables *g_var = nullptr;
+
+struct View { void *p; size_t nbytes; };
+
+// Flatten vector<vector<int>> elemmarkers into [nelem*nmat] (row = element).
+std::vector<int> g_flat_markers;
+std::vector<int> g_flat_pairs;
+
+View lookup(const std::string &n)
+{
+    Variables &v = *g_var;
+#define DV(name, ptr) if (n == name) return View{ (ptr)->data(), (ptr)->size() * sizeof((*(ptr))[0]) }
+#define A2(name, ptr) if (n == name) return View{ (ptr)->data(), size_t((ptr)->num_elements()) * sizeof(*(ptr)->data()) }
+    A2("coord", v.coord); A2("coord0", v.coord0); A2("vel", v.vel); A2("force", v.force);
+    A2("force_residual", v.force_residual);
+    A2("connectivity", v.connectivity);
+    A2("stress", v.stress); A2("strain", v.strain); A2("strain_rate", v.strain_rate);
+    A2("tmp_result", v.tmp_result);
+    A2("bnormals", v.bnormals);
+    A2("segment", v.segment); A2("segflag", v.segflag);
+    DV("volume", v.volume); DV("volume_old", v.volume_old); DV("volume_n", v.volume_n);
+    DV("mass", v.mass); DV("tmass", v.tmass); DV("hmass", v.hmass); DV("ymass", v.ymass);
+    DV("edvoldt", v.edvoldt); DV("temperature", v.temperature); DV("plstrain", v.plstrain);
+    DV("delta_plstrain", v.delta_plstrain); DV("dpressure", v.dpressure);
+    DV("viscosity", v.viscosity); DV("ntmp", v.ntmp); DV("etmp", v.etmp);
+    DV("radiogenic_source", v.radiogenic_source);
+    DV("bcflag", v.bcflag);
+    if (n == "support_arr") return View{ v.support.arr_data.data(), v.support.arr_data.size()*sizeof(int) };
+    if (n == "support_idx") return View{ v.support.idx_data.data(), v.support.idx_data.size()*sizeof(int) };
+    if (n == "support_lidx") return View{ v.support.lidx_data.data(), v.support.lidx_data.size()*sizeof(int) };
+    DV("top_elems", v.top_elems);
+    DV("top_nodes", v.surfinfo.top_nodes);
+    DV("dh", v.surfinfo.dh); DV("dhacc", v.surfinfo.dhacc); DV("edvacc_surf", v.surfinfo.edvacc_surf);
+    if (n == "support_surf_arr") return View{ v.surfinfo.support_surf.arr_data.data(), v.surfinfo.support_surf.arr_data.size()*sizeof(int) };
+    if (n == "support_surf_idx") return View{ v.surfinfo.support_surf.idx_data.data(), v.surfinfo.support_surf.idx_data.size()*sizeof(int) };
+    A2("elem_and_nodes", v.surfinfo.elem_and_nodes);
+    A2("connectivity_surface", v.connectivity_surface);
+    if (n == "edge_vec") return View{ v.edge_vec.data(), v.edge_vec.size()*sizeof(double) };
+    if (n == "edge_slot") return View{ v.edge_slot, sizeof(v.edge_slot) };
+    if (n == "vbc_types") return View{ v.vbc_types, sizeof(v.vbc_types) };
+    if (n == "vbc_values") return View{ v.vbc_values, sizeof(v.vbc_values) };
+    if (n == "stress_bc_types") return View{ v.stress_bc_types, sizeof(v.stress_bc_types) };
+    if (n == "stress_bc_values") return View{ v.stress_bc_values, sizeof(v.stress_bc_values) };
+    if (n == "elemmarkers") {
+        const int nmat = g_param->mat.nmat;
+        g_flat_markers.resize(size_t(v.nelem) * nmat);
+        for (int e = 0; e < v.nelem; ++e)
+            for (int m = 0; m < nmat; ++m)
+                g_flat_markers[size_t(e)*nmat + m] = (*v.elemmarkers)[e][m];
+        return View{ g_flat_markers.data(), g_flat_markers.size()*sizeof(int) };
+    }
+    for (int i = 0; i < nbdrytypes; ++i) {
+        char b[32];
+        std::snprintf(b, sizeof b, "bnodes%d", i);
+        if (n == b) return View{ v.bnodes[i]->data(), v.bnodes[i]->size()*sizeof(int) };
+        std::snprintf(b, sizeof b, "bfacets%d", i);
+        if (n == b) {   // (elem, facet) pairs flattened
+            g_flat_pairs.resize(v.bfacets[i]->size()*2);
+            for (size_t k = 0; k < v.bfacets[i]->size(); ++k) {
+                g_flat_pairs[2*k]   = (*v.bfacets[i])[k].first;
+                g_flat_pairs[2*k+1] = (*v.bfacets[i])[k].second;
+            }
+            return View{ g_flat_pairs.data(), g_flat_pairs.size()*sizeof(int) };
+        }
+    }
+#undef DV
+#undef A2
+    return View{ nullptr, 0 };
+}
+
+double *scalar_ptr(const std::string &n)
+{
+    Variables &v = *g_var; Param &p = *g_param;
+    if (n == "dt") return &v.dt;
+    if (n == "time") return &v.time;
+    if (n == "compensation_pressure") return &v.compensation_pressure;
+    if (n == "max_vbc_val") return &v.max_vbc_val;
+    if (n == "max_global_vel_mag") return &v.max_global_vel_mag;
+    if (n == "global_dt_min") return &v.global_dt_min;
+    if (n == "max_surf_vel") return &v.surfinfo.max_surf_vel;
+    if (n == "surf_diff") return &v.surfinfo.surf_diff;
+    if (n == "bottom_temperature") return &v.bottom_temperature;
+    if (n == "gravity") return &p.control.gravity;
+    if (n == "inertial_scaling") return &p.control.inertial_scaling;
+    if (n == "damping_factor") return &p.control.damping_factor;
+    if (n == "dt_fraction") return &p.control.dt_fraction;
+    if (n == "surface_temperature") return &p.bc.surface_temperature;
+    if (n == "winkler_delta_rho") return &p.bc.winkler_delta_rho;
+    if (n == "zlength") return &p.mesh.zlength;
+    if (n == "surf_base_level") return &p.control.surf_base_level;
+    if (n == "sea_water_density") return &p.bc.sea_water_density;
+    if (n == "visc_min") return &p.mat.visc_min;
+    if (n == "visc_max") return &p.mat.visc_max;
+    if (n == "tension_max") return &p.mat.tension_max;
+    if (n == "therm_diff_max") return &p.mat.therm_diff_max;
+    if (n == "elastic_foundation_constant") return &p.bc.elastic_foundation_constant;
+    if (n == "characteristic_speed") return &p.control.characteristic_speed;
+    if (n == "fixed_dt") return &p.control.fixed_dt;
+    return nullptr;
+}
+
+const double_vec *matvec(const std::string &n)
+{
+    const Mat &m = g_param->mat;
+    if (n == "rho0") return &m.rho0;
+    if (n == "alpha") return &m.alpha;
+    if (n == "bulk_modulus") return &m.bulk_modulus;
+    if (n == "shear_modulus") return &m.shear_modulus;
+    if (n == "visc_exponent") return &m.visc_exponent;
+    if (n == "visc_coefficient") return &m.visc_coefficient;
+    if (n == "visc_activation_energy") return &m.visc_activation_energy;
+    if (n == "visc_activation_volume") return &m.visc_activation_volume;
+    if (n == "heat_capacity") return &m.heat_capacity;
+    if (n == "therm_cond") return &m.therm_cond;
+    if (n == "pls0") return &m.pls0;
+    if (n == "pls1") return &m.pls1;
+    if (n == "cohesion0") return &m.cohesion0;
+    if (n == "cohesion1") return &m.cohesion1;
+    if (n == "friction_angle0") return &m.friction_angle0;
+    if (n == "friction_angle1") return &m.friction_angle1;
+    if (n == "dilation_angle0") return &m.dilation_angle0;
+    if (n == "dilation_angle1") return &m.dilation_angle1;
+    if (n == "porosity") return &m.porosity;
+    return nullptr;
+}
+
+int int_param(const std::string &n, bool &ok)
+{
+    const Param &p = *g_param; const Variables &v = *g_var;
+    ok = true;
+    if (n == "nnode") return v.nnode;
+    if (n == "nelem") return v.nelem;
+    if (n == "nseg") return v.nseg;
+    if (n == "steps") return v.steps;
+    if (n == "nmat") return p.mat.nmat;
+    if (n == "rheol_type") return p.mat.rheol_type;
+    if (n == "mattype_ref") return p.mat.mattype_ref;
+    if (n == "damping_option") return p.control.damping_option;
+    if (n == "is_quasi_static") return p.control.is_quasi_static;
+    if (n == "has_thermal_diffusion") return p.control.has_thermal_diffusion;
+    if (n == "has_hydraulic_diffusion") return p.control.has_hydraulic_diffusion;
+    if (n == "is_using_mixed_stress") return p.control.is_using_mixed_stress;
+    if (n == "surface_process_option") return p.control.surface_process_option;
+    if (n == "ref_pressure_option") return p.control.ref_pressure_option;
+    if (n == "use_global_velocity_scaling") return p.control.use_global_velocity_scaling;
+    if (n == "has_moving_mesh") return p.control.has_moving_mesh;
+    if (n == "has_PT") return p.control.has_PT;
+    if (n == "has_winkler_foundation") return p.bc.has_winkler_foundation;
+    if (n == "has_water_loading") return p.bc.has_water_loading;
+    if (n == "has_elastic_foundation") return p.bc.has_elastic_foundation;
+    if (n == "has_body_force_adjustment") return p.ic.has_body_force_adjustment;
+    if (n == "ntop") return v.surfinfo.ntop;
+    if (n == "etop") return v.surfinfo.etop;
+    if (n == "ntop_elems") return v.ntop_elems;
+    if (n == "quality_check_step_interval") return p.mesh.quality_check_step_interval;
+    if (n == "phase_change_option") return p.mat.phase_change_option;
+    if (n == "is_plane_strain") return p.mat.is_plane_strain;
+    ok = false;
+    return 0;
+}
+
+// One pass of the step loop body, dynearthsol.cxx:772-894, without output, monitors,
+// the PT loop, hydraulics, and remeshing.
+void one_step()
+{
+    Param &param = *g_param; Variables &var = *g_var;
+    var.steps++;
+    var.time += var.dt;
+    var.mat->refresh_elem_cache();
+    if (param.control.has_thermal_diffusion)
+        update_temperature(param, var, *var.temperature, *var.tmp_result);
+    update_strain_rate(var, *var.strain_rate);
+    compute_dvoldt(var, *var.ntmp, *var.etmp);
+    compute_edvoldt(var, *var.ntmp, *var.edvoldt);
+    update_stress(param, var, *var.stress, *var.stressyy, *var.dpressure,
+                  *var.viscosity, *var.strain, *var.plstrain, *var.delta_plstrain,
+                  *var.strain_rate, *var.ppressure, *var.dppressure, *var.vel,
+                  *var.dyn_fric_coeff, *var.state_variable);
+    if (param.control.is_using_mixed_stress)
+        NMD_stress(var, *var.stress, *var.ntmp, *var.etmp);
+    update_force(param, var, *var.force, *var.force_residual, *var.tmp_result);
+    update_velocity(var, *var.vel);
+    var.l2_residual = calculate_residual_force(var, *var.force_residual);
+    apply_vbcs(param, var, *var.vel);
+    if (param.control.has_moving_mesh)
+        update_mesh(param, var);
+    if (var.mat->rheol_type & MatProps::rh_elastic)
+        rotate_stress(var, *var.stress, *var.strain);
+    if (var.steps % 10 == 0) {
+        phase_changes(param, var);
+        var.mat->refresh_elem_cache();
+        var.dt = compute_dt(param, var);
+    }
+}
+} // namespace
+
+extern "C" {
+
+// Parse cfg, build mesh and initial state exactly as main() does up to the step loop
+// (dynearthsol.cxx:612-643).  Returns 0 on success.
+int desref_init(const char *cfg_path)
+{
+    if (g_param) return 1;  // one model per process (the reference keeps static state)
+    g_param = new Param;
+    get_input_parameters(cfg_path, *g_param);
+    g_var = new Variables;
+    init_var(*g_param, *g_var);
+    g_var->output = new Output(*g_param, g_var->func_time.start_time, 0);
+    init(*g_param, *g_var);
+    g_var->dt = compute_dt(*g_param, *g_var);
+    return 0;
+}
+
+long desref_nbytes(const char *name) { View w = lookup(name); return w.p ? long(w.nbytes) : -1; }
+
+int desref_get(const char *name, void *out, long nbytes)
+{
+    View w = lookup(name);
+    if (!w.p && w.nbytes == 0 && nbytes == 0) return 0;
+    if (!w.p || long(w.nbytes) != nbytes) return -1;
+    std::memcpy(out, w.p, w.nbytes);
+    return 0;
+}
+
+int desref_set(const char *name, const void *in, long nbytes)
+{
+    if (std::string(name) == "elemmarkers") {
+        const int nmat = g_param->mat.nmat;
+        if (nbytes != long(sizeof(int)) * g_var->nelem * nmat) return -1;
+        const int *src = static_cast<const int*>(in);
+        for (int e = 0; e < g_var->nelem; ++e)
+            for (int m = 0; m < nmat; ++m)
+                (*g_var->elemmarkers)[e][m] = src[size_t(e)*nmat + m];
+        return 0;
+    }
+    View w = lookup(name);
+    if (!w.p || long(w.nbytes) != nbytes) return -1;
+    std::memcpy(w.p, in, w.nbytes);
+    return 0;
+}
+
+int desref_get_scalar(const char *name, double *out)
+{
+    double *p = scalar_ptr(name);
+    if (!p) return -1;
+    *out = *p;
+    return 0;
+}
+
+int desref_set_scalar(const char *name, double v)
+{
+    double *p = scalar_ptr(name);
+    if (!p) return -1;
+    *p = v;
+    return 0;
+}
+
+int desref_get_int(const char *name, int *out)
+{
+    bool ok;
+    int v = int_param(name, ok);
+    if (!ok) return -1;
+    *out = v;
+    return 0;
+}
+
+// Settable switches (so one initialised model can exercise several branches).
+int desref_set_int(const char *name, int val)
+{
+    Param &p = *g_param; std::string n(name);
+    if (n == "rheol_type") {
+        p.mat.rheol_type = val;
+        // MatProps::rheol_type is const and copied at construction (matprops.cxx:176-178):
+        // rebuild it the way reallocate_variables() does (fields.cxx:191-192).
+        delete g_var->mat;
+        g_var->mat = new MatProps(p, *g_var);
+    }
+    else if (n == "damping_option") p.control.damping_option = val;
+    else if (n == "is_using_mixed_stress") p.control.is_using_mixed_stress = val;
+    else if (n == "has_thermal_diffusion") p.control.has_thermal_diffusion = val;
+    else if (n == "surface_process_option") p.control.surface_process_option = val;
+    else if (n == "is_quasi_static") p.control.is_quasi_static = val;
+    else if (n == "steps") g_var->steps = val;
+    else return -1;
+    return 0;
+}
+
+int desref_get_matvec(const char *name, double *out, int n)
+{
+    const double_vec *v = matvec(name);
+    if (!v || int(v->size()) != n) return -1;
+    std::memcpy(out, v->data(), sizeof(double) * n);
+    return 0;
+}
+
+// Call ONE reference hot function on the current state.
+int desref_call(const char *fn)
+{
+    Param &param = *g_param; Variables &var = *g_var; std::string f(fn);
+    if (f == "refresh_elem_cache") var.mat->refresh_elem_cache();
+    else if (f == "update_temperature") update_temperature(param, var, *var.temperature, *var.tmp_result);
+    else if (f == "update_strain_rate") update_strain_rate(var, *var.strain_rate);
+    else if (f == "compute_dvoldt") compute_dvoldt(var, *var.ntmp, *var.etmp);
+    else if (f == "compute_edvoldt") compute_edvoldt(var, *var.ntmp, *var.edvoldt);
+    else if (f == "update_stress")
+        update_stress(param, var, *var.stress, *var.stressyy, *var.dpressure,
+                      *var.viscosity, *var.strain, *var.plstrain, *var.delta_plstrain,
+                      *var.strain_rate, *var.ppressure, *var.dppressure, *var.vel,
+                      *var.dyn_fric_coeff, *var.state_variable);
+    else if (f == "NMD_stress") NMD_stress(var, *var.stress, *var.ntmp, *var.etmp);
+    else if (f == "update_force") update_force(param, var, *var.force, *var.force_residual, *var.tmp_result);
+    else if (f == "update_velocity") update_velocity(var, *var.vel);
+    else if (f == "apply_vbcs") apply_vbcs(param, var, *var.vel);
+    else if (f == "update_coordinate") update_coordinate(var, *var.coord);
+    else if (f == "update_mesh") update_mesh(param, var);
+    else if (f == "compute_volume") compute_volume(var, *var.volume);
+    else if (f == "compute_mass")
+        compute_mass(param, var, var.max_vbc_val, *var.volume_n, *var.mass, *var.tmass,
+                     *var.hmass, *var.ymass, *var.tmp_result);
+    else if (f == "rotate_stress") rotate_stress(var, *var.stress, *var.strain);
+    else if (f == "compute_dt") var.dt = compute_dt(param, var);
+    else if (f == "calculate_residual_force") var.l2_residual = calculate_residual_force(var, *var.force_residual);
+    else if (f == "visc_all") {
+        for (int e = 0; e < var.nelem; ++e) (*var.viscosity)[e] = var.mat->visc(e);
+    }
+    else if (f == "rho_all") {   // into etmp
+        for (int e = 0; e < var.nelem; ++e) (*var.etmp)[e] = var.mat->rho(e);
+    }
+    else return -1;
+    return 0;
+}
+
+double desref_l2_residual() { return g_var->l2_residual; }
+
+// Run n explicit steps; returns wall seconds.
+double desref_step(int n)
+{
+    auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < n; ++i) one_step();
+    auto t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+} // extern "C"
