@@ -1,0 +1,383 @@
+"""ctypes binding of the C-ABI in include/des_gpu.h (libdes_b200.so) plus a thin host-side
+mirror of the reference's step-loop call sites (dynearthsol.cxx:768-894).
+
+There is no CPU fallback: if the CUDA library is missing this module raises on load, and if
+no device is present `DesGpu(...)` raises.  Nothing here imports `oracle/`.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libdes_b200.so")
+
+DES_MAX_MAT = 16
+DES_NBDRY = 10
+DES_NKCLASS = 16
+
+RH_ELASTIC, RH_VISCOUS, RH_MAXWELL, RH_EP, RH_EVP = 1, 2, 3, 5, 7
+
+ERRORS = {0: "OK", 1: "NODEVICE", 2: "CUDA", 3: "ARG", 4: "UNSUPPORTED", 5: "STATE", 11: "NAN"}
+
+
+class DesError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("des_gpu error %d (%s): %s" % (code, ERRORS.get(code, "?"), msg))
+        self.code = code
+
+
+_MATV = C.c_double * DES_MAX_MAT
+
+
+class DesParam(C.Structure):
+    _fields_ = [
+        ("gravity", C.c_double), ("inertial_scaling", C.c_double), ("damping_factor", C.c_double),
+        ("surface_diffusivity", C.c_double), ("surf_base_level", C.c_double),
+        ("dt_fraction", C.c_double), ("fixed_dt", C.c_double), ("characteristic_speed", C.c_double),
+        ("damping_option", C.c_int), ("is_quasi_static", C.c_int), ("has_thermal_diffusion", C.c_int),
+        ("is_using_mixed_stress", C.c_int), ("surface_process_option", C.c_int),
+        ("ref_pressure_option", C.c_int), ("has_moving_mesh", C.c_int),
+        ("has_body_force_adjustment", C.c_int),
+        ("has_winkler_foundation", C.c_int), ("has_water_loading", C.c_int),
+        ("has_elastic_foundation", C.c_int),
+        ("winkler_delta_rho", C.c_double), ("elastic_foundation_constant", C.c_double),
+        ("sea_water_density", C.c_double), ("surface_temperature", C.c_double),
+        ("vbc_types", C.c_int * DES_NBDRY), ("vbc_values", C.c_double * DES_NBDRY),
+        ("vbc_val_lateral", C.c_double * 4), ("vbc_val_z1_loading_period", C.c_double),
+        ("stress_bc_types", C.c_int * 6), ("max_vbc_val", C.c_double),
+        ("zlength", C.c_double),
+        ("rheol_type", C.c_int), ("nmat", C.c_int), ("mattype_ref", C.c_int),
+        ("visc_min", C.c_double), ("visc_max", C.c_double), ("tension_max", C.c_double),
+        ("therm_diff_max", C.c_double),
+        ("rho0", _MATV), ("alpha", _MATV), ("bulk_modulus", _MATV), ("shear_modulus", _MATV),
+        ("visc_exponent", _MATV), ("visc_coefficient", _MATV),
+        ("visc_activation_energy", _MATV), ("visc_activation_volume", _MATV),
+        ("heat_capacity", _MATV), ("therm_cond", _MATV),
+        ("pls0", _MATV), ("pls1", _MATV), ("cohesion0", _MATV), ("cohesion1", _MATV),
+        ("friction_angle0", _MATV), ("friction_angle1", _MATV),
+        ("dilation_angle0", _MATV), ("dilation_angle1", _MATV), ("porosity", _MATV),
+    ]
+
+
+MAT_ARRAYS = ["rho0", "alpha", "bulk_modulus", "shear_modulus", "visc_exponent", "visc_coefficient",
+              "visc_activation_energy", "visc_activation_volume", "heat_capacity", "therm_cond",
+              "pls0", "pls1", "cohesion0", "cohesion1", "friction_angle0", "friction_angle1",
+              "dilation_angle0", "dilation_angle1", "porosity"]
+
+_IP = C.POINTER(C.c_int)
+_DP = C.POINTER(C.c_double)
+
+
+class DesMesh(C.Structure):
+    _fields_ = [
+        ("nnode", C.c_int), ("nelem", C.c_int),
+        ("connectivity", _IP), ("bcflag", C.POINTER(C.c_uint)),
+        ("support_idx", _IP), ("support_arr", _IP), ("support_lidx", _IP),
+        ("nbfacets", C.c_int * DES_NBDRY), ("bfacets", _IP * DES_NBDRY),
+        ("nbnodes", C.c_int * DES_NBDRY), ("bnodes", _IP * DES_NBDRY),
+        ("bnormals", _DP), ("n_edge_vec", C.c_int), ("edge_vec", _DP), ("edge_slot", _IP),
+        ("ntop_elems", C.c_int), ("top_elems", _IP),
+        ("ntop", C.c_int), ("top_nodes", _IP), ("etop", C.c_int),
+        ("support_surf_idx", _IP), ("support_surf_arr", _IP),
+        ("elem_and_nodes", _IP), ("connectivity_surface", _IP),
+    ]
+
+
+STATE_FIELDS = ["coord", "vel", "coord0", "temperature", "stress", "strain", "strain_rate",
+                "plstrain", "delta_plstrain", "volume", "volume_old", "viscosity", "dpressure",
+                "edvoldt", "radiogenic_source", "force", "volume_n", "mass", "tmass", "ntmp",
+                "dhacc", "edvacc_surf"]
+
+
+class DesState(C.Structure):
+    _fields_ = [(f, _DP) for f in STATE_FIELDS]
+
+
+class DesDtReductions(C.Structure):
+    _fields_ = [("minl", C.c_double), ("dt_maxwell", C.c_double), ("dt_diffusion", C.c_double),
+                ("global_dt_min", C.c_double), ("global_max_vem", C.c_double),
+                ("max_surf_vel", C.c_double)]
+
+
+# every symbol include/des_gpu.h declares (tests check the library exports them all)
+ABI_SYMBOLS = [
+    "des_gpu_create", "des_gpu_destroy", "des_gpu_last_error", "des_gpu_upload_mesh",
+    "des_gpu_upload_state", "des_gpu_download_state", "des_gpu_upload_elemmarkers",
+    "des_gpu_set_compensation_pressure", "des_gpu_step", "des_gpu_compute_dt",
+    "des_dt_from_reductions", "des_gpu_sync",
+    "des_gpu_update_temperature", "des_gpu_update_strain_rate", "des_gpu_compute_dvoldt",
+    "des_gpu_compute_edvoldt", "des_gpu_update_stress", "des_gpu_nmd_stress",
+    "des_gpu_update_force", "des_gpu_update_velocity", "des_gpu_apply_vbcs",
+    "des_gpu_update_mesh", "des_gpu_compute_volume", "des_gpu_compute_mass",
+    "des_gpu_rotate_stress", "des_gpu_residual_force",
+    "des_gpu_launch_count", "des_gpu_enable_kernel_timing", "des_gpu_kernel_time",
+    "des_gpu_device_ptr",
+]
+
+_lib = None
+
+
+def load_library():
+    """Load libdes_b200.so (built in-tree by __graft_entry__.build()).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(no CPU fallback exists)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    H = C.c_void_p
+    L.des_gpu_create.argtypes = [C.POINTER(DesParam), C.c_int, C.POINTER(H)]
+    L.des_gpu_destroy.argtypes = [H]
+    L.des_gpu_last_error.argtypes = [H]
+    L.des_gpu_last_error.restype = C.c_char_p
+    L.des_gpu_upload_mesh.argtypes = [H, C.POINTER(DesMesh)]
+    L.des_gpu_upload_state.argtypes = [H, C.POINTER(DesState)]
+    L.des_gpu_download_state.argtypes = [H, C.POINTER(DesState)]
+    L.des_gpu_upload_elemmarkers.argtypes = [H, _IP]
+    L.des_gpu_set_compensation_pressure.argtypes = [H, C.c_double]
+    L.des_gpu_step.argtypes = [H, C.c_double, C.c_double, C.c_int]
+    L.des_gpu_compute_dt.argtypes = [H, C.POINTER(DesDtReductions)]
+    L.des_dt_from_reductions.argtypes = [C.POINTER(DesParam), C.POINTER(DesDtReductions), _DP]
+    L.des_dt_from_reductions.restype = C.c_double
+    L.des_gpu_sync.argtypes = [H]
+    for f in ["update_temperature", "update_stress", "update_velocity", "apply_vbcs", "update_mesh",
+              "rotate_stress"]:
+        getattr(L, "des_gpu_" + f).argtypes = [H, C.c_double]
+    for f in ["update_strain_rate", "compute_dvoldt", "compute_edvoldt", "nmd_stress", "update_force",
+              "compute_volume", "compute_mass"]:
+        getattr(L, "des_gpu_" + f).argtypes = [H]
+    L.des_gpu_residual_force.argtypes = [H, _DP]
+    L.des_gpu_launch_count.argtypes = [H]
+    L.des_gpu_launch_count.restype = C.c_longlong
+    L.des_gpu_enable_kernel_timing.argtypes = [H, C.c_int]
+    L.des_gpu_kernel_time.argtypes = [H, C.c_int, _DP, C.POINTER(C.c_longlong), C.POINTER(C.c_char_p)]
+    L.des_gpu_device_ptr.argtypes = [H, C.c_char_p]
+    L.des_gpu_device_ptr.restype = C.c_void_p
+    _lib = L
+    return L
+
+
+def make_param(**kw):
+    """DesParam from keyword scalars / per-material sequences, with input.cxx's defaults."""
+    d = dict(gravity=10.0, inertial_scaling=1e5, damping_factor=0.8, surface_diffusivity=1e-6,
+             surf_base_level=0.0, dt_fraction=1.0, fixed_dt=0.0, characteristic_speed=0.0,
+             damping_option=1, is_quasi_static=1, has_thermal_diffusion=1, is_using_mixed_stress=1,
+             surface_process_option=0, ref_pressure_option=0, has_moving_mesh=1,
+             has_body_force_adjustment=0, has_winkler_foundation=1, has_water_loading=1,
+             has_elastic_foundation=0, winkler_delta_rho=0.0, elastic_foundation_constant=0.0,
+             sea_water_density=1030.0, surface_temperature=273.0,
+             vbc_val_z1_loading_period=1e300, max_vbc_val=1e-12, zlength=0.0,
+             rheol_type=RH_EP, nmat=1, mattype_ref=0, visc_min=1e19, visc_max=1e24,
+             tension_max=1e9, therm_diff_max=5e-6)
+    p = DesParam()
+    d.update({k: v for k, v in kw.items() if k in d})
+    for k, v in d.items():
+        setattr(p, k, v)
+    nmat = d["nmat"]
+    for name in MAT_ARRAYS:
+        if name in kw:
+            a = np.broadcast_to(np.asarray(kw[name], dtype=np.float64), (nmat,))
+            arr = getattr(p, name)
+            for m in range(nmat):
+                arr[m] = float(a[m])
+    for name, n in (("vbc_types", DES_NBDRY), ("vbc_values", DES_NBDRY), ("vbc_val_lateral", 4),
+                    ("stress_bc_types", 6)):
+        if name in kw:
+            arr = getattr(p, name)
+            for i in range(n):
+                arr[i] = kw[name][i]
+    unknown = set(kw) - set(d) - set(MAT_ARRAYS) - {"vbc_types", "vbc_values", "vbc_val_lateral",
+                                                    "stress_bc_types"}
+    if unknown:
+        raise TypeError("unknown DesParam fields: %s" % sorted(unknown))
+    return p
+
+
+def _ptr(a, ct):
+    return a.ctypes.data_as(C.POINTER(ct)) if a is not None and a.size else C.POINTER(ct)()
+
+
+class DesGpu:
+    """One device-resident model.  Host arrays use the reference's SoA layout
+    (Array2D a[d*n + i], array2d.hpp:410-425)."""
+
+    def __init__(self, param, device=0):
+        self.lib = load_library()
+        self.param = param
+        self.h = C.c_void_p()
+        rc = self.lib.des_gpu_create(C.byref(param), device, C.byref(self.h))
+        if rc:
+            msg = self.lib.des_gpu_last_error(self.h).decode() if self.h else "no handle"
+            if self.h:
+                self.lib.des_gpu_destroy(self.h)
+                self.h = C.c_void_p()
+            raise DesError(rc, msg)
+        self.nnode = self.nelem = self.etop = 0
+        self._keep = []
+
+    def _ck(self, rc):
+        if rc:
+            raise DesError(rc, self.lib.des_gpu_last_error(self.h).decode())
+
+    def close(self):
+        if self.h:
+            self.lib.des_gpu_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- data movement ----------------------------------------------------------------
+    def upload_mesh(self, m):
+        """`m`: dict with the reference's topology arrays (see DesMesh in des_gpu.h)."""
+        keep = {}
+
+        def arr(name, dt):
+            a = m.get(name)
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dtype=dt)
+            keep[name] = a
+            return a
+
+        dm = DesMesh()
+        dm.nnode, dm.nelem = int(m["nnode"]), int(m["nelem"])
+        dm.connectivity = _ptr(arr("connectivity", np.int32), C.c_int)
+        dm.bcflag = _ptr(arr("bcflag", np.uint32), C.c_uint)
+        dm.support_idx = _ptr(arr("support_idx", np.int32), C.c_int)
+        dm.support_arr = _ptr(arr("support_arr", np.int32), C.c_int)
+        dm.support_lidx = _ptr(arr("support_lidx", np.int32), C.c_int)
+        for i in range(DES_NBDRY):
+            bf = arr("bfacets%d" % i, np.int32)
+            bn = arr("bnodes%d" % i, np.int32)
+            dm.nbfacets[i] = 0 if bf is None else bf.size // 2
+            dm.bfacets[i] = _ptr(bf, C.c_int)
+            dm.nbnodes[i] = 0 if bn is None else bn.size
+            dm.bnodes[i] = _ptr(bn, C.c_int)
+        dm.bnormals = _ptr(arr("bnormals", np.float64), C.c_double)
+        ev = arr("edge_vec", np.float64)
+        dm.n_edge_vec = 0 if ev is None else ev.size
+        dm.edge_vec = _ptr(ev, C.c_double)
+        dm.edge_slot = _ptr(arr("edge_slot", np.int32), C.c_int)
+        te = arr("top_elems", np.int32)
+        dm.ntop_elems = 0 if te is None else te.size
+        dm.top_elems = _ptr(te, C.c_int)
+        tn = arr("top_nodes", np.int32)
+        dm.ntop = 0 if tn is None else tn.size
+        dm.top_nodes = _ptr(tn, C.c_int)
+        dm.etop = dm.nbfacets[5]
+        dm.support_surf_idx = _ptr(arr("support_surf_idx", np.int32), C.c_int)
+        dm.support_surf_arr = _ptr(arr("support_surf_arr", np.int32), C.c_int)
+        dm.elem_and_nodes = _ptr(arr("elem_and_nodes", np.int32), C.c_int)
+        dm.connectivity_surface = _ptr(arr("connectivity_surface", np.int32), C.c_int)
+        self._ck(self.lib.des_gpu_upload_mesh(self.h, C.byref(dm)))
+        self.nnode, self.nelem, self.etop = dm.nnode, dm.nelem, dm.etop
+
+    def _sizes(self):
+        N, E = self.nnode, self.nelem
+        s = {f: E for f in STATE_FIELDS}
+        for f in ("coord", "vel", "coord0", "force"):
+            s[f] = 3 * N
+        for f in ("temperature", "volume_n", "mass", "tmass", "ntmp", "dhacc"):
+            s[f] = N
+        for f in ("stress", "strain", "strain_rate"):
+            s[f] = 6 * E
+        s["edvacc_surf"] = self.etop
+        return s
+
+    def upload_state(self, **fields):
+        st = DesState()
+        sizes = self._sizes()
+        keep = []
+        for k, v in fields.items():
+            a = np.ascontiguousarray(v, dtype=np.float64).reshape(-1)
+            if a.size != sizes[k]:
+                raise ValueError("%s: expected %d doubles, got %d" % (k, sizes[k], a.size))
+            keep.append(a)
+            setattr(st, k, _ptr(a, C.c_double))
+        self._ck(self.lib.des_gpu_upload_state(self.h, C.byref(st)))
+
+    def download_state(self, *names):
+        st = DesState()
+        sizes = self._sizes()
+        out = {}
+        for k in names:
+            out[k] = np.empty(sizes[k], dtype=np.float64)
+            setattr(st, k, _ptr(out[k], C.c_double) if out[k].size else _DP())
+        self._ck(self.lib.des_gpu_download_state(self.h, C.byref(st)))
+        return out
+
+    def upload_elemmarkers(self, em):
+        a = np.ascontiguousarray(em, dtype=np.int32).reshape(-1)
+        if a.size != self.nelem * self.param.nmat:
+            raise ValueError("elemmarkers: expected nelem*nmat ints")
+        self._ck(self.lib.des_gpu_upload_elemmarkers(self.h, _ptr(a, C.c_int)))
+
+    def set_compensation_pressure(self, p):
+        self._ck(self.lib.des_gpu_set_compensation_pressure(self.h, float(p)))
+
+    # ---- stepping -----------------------------------------------------------------------
+    def step(self, dt, time=0.0, steps=0):
+        self._ck(self.lib.des_gpu_step(self.h, float(dt), float(time), int(steps)))
+
+    def compute_dt_reductions(self):
+        r = DesDtReductions()
+        self._ck(self.lib.des_gpu_compute_dt(self.h, C.byref(r)))
+        return r
+
+    def compute_dt(self):
+        """compute_dt (geometry.cxx:1480-1647): device reductions + host scalar algebra.
+        Returns (dt, max_global_vel_mag, reductions)."""
+        r = self.compute_dt_reductions()
+        vmag = C.c_double()
+        dt = self.lib.des_dt_from_reductions(C.byref(self.param), C.byref(r), C.byref(vmag))
+        if not dt > 0:
+            raise DesError(11, "dt <= 0")
+        return dt, vmag.value, r
+
+    def sync(self):
+        self._ck(self.lib.des_gpu_sync(self.h))
+
+    def run(self, nsteps, dt, time=0.0, steps=0, dt_interval=10):
+        """The reference's step loop (dynearthsol.cxx:768-894) for `nsteps` steps:
+        step, and compute_dt every `dt_interval` steps.  Returns (dt, time, steps)."""
+        for _ in range(nsteps):
+            steps += 1
+            time += dt
+            self.step(dt, time, steps)
+            if steps % dt_interval == 0:
+                dt = self.compute_dt()[0]
+        return dt, time, steps
+
+    # ---- twins ----------------------------------------------------------------------------
+    def call(self, fn, *args):
+        f = getattr(self.lib, "des_gpu_" + fn)
+        self._ck(f(self.h, *[float(a) for a in args]))
+
+    def residual_force(self):
+        v = C.c_double()
+        self._ck(self.lib.des_gpu_residual_force(self.h, C.byref(v)))
+        return v.value
+
+    # ---- instrumentation --------------------------------------------------------------
+    def launch_count(self):
+        return int(self.lib.des_gpu_launch_count(self.h))
+
+    def enable_kernel_timing(self, on=True):
+        self._ck(self.lib.des_gpu_enable_kernel_timing(self.h, int(on)))
+
+    def kernel_times(self):
+        out = []
+        for i in range(DES_NKCLASS):
+            ms, n, nm = C.c_double(), C.c_longlong(), C.c_char_p()
+            self._ck(self.lib.des_gpu_kernel_time(self.h, i, C.byref(ms), C.byref(n), C.byref(nm)))
+            if n.value:
+                out.append((nm.value.decode(), ms.value, n.value))
+        return out
+
+    def device_ptr(self, name):
+        return self.lib.des_gpu_device_ptr(self.h, name.encode())

@@ -1,0 +1,747 @@
+// Host side of the C-ABI in include/des_gpu.h: device state, data movement, the step
+// schedule.  No torch, no CPU fallback: every numeric path below launches a kernel from
+// des_kernels.cuh on the handle's stream.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <cfloat>
+#include <map>
+#include <string>
+#include <unordered_map>
+#include <vector>
+#include <algorithm>
+#include <limits>
+
+#include "des_kernels.cuh"
+
+namespace {
+
+enum KClass { KC_ELEM_A = 0, KC_NODE_A, KC_ELEM_B, KC_NODE_B, KC_ELEM_C, KC_NODE_C,
+              KC_SBC, KC_SURFACE, KC_DT, KC_PACK, KC_TWIN, KC_COUNT };
+const char *kclass_name[DES_NKCLASS] = {
+    "elem_a(volume,mass,rotate|Tdiff,strain_rate,dvol)", "node_a(mass,T,dvoldt gather)",
+    "elem_b(edvoldt,rheology)", "node_b(dp gather)", "elem_c(NMD,force)",
+    "node_c(force gather,bc,damping,v,vbc,x)", "sbc_facets", "surface", "compute_dt",
+    "pack/unpack", "twin", "", "", "", "", "" };
+
+struct EvPair { cudaEvent_t a, b; int cls; };
+
+} // namespace
+
+struct DesGpu {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    DesParam hp;
+    DevParams P;
+    Dev D;
+    std::vector<void *> mesh_allocs;    // freed at upload_mesh / destroy
+    std::string err;
+    bool have_mesh = false, have_state = false;
+    bool tail_pending = false;          // end-of-step element work deferred into next E-A
+    double dt_prev = 0;                 // dt of the step whose tail is pending
+    double compensation_pressure = 0;
+    double last_dt = 0;                 // dt of the last step (for max_surf_vel)
+    bool surf_ran = false;
+    long long launches = 0;
+    // staging
+    void *stage = nullptr; size_t stage_bytes = 0;
+    DtPartial *dt_partials = nullptr; int dt_blocks = 0;
+    // timing
+    bool timing = false;
+    std::vector<EvPair> ev_pool; size_t ev_used = 0;
+    double kc_ms[DES_NKCLASS]; long long kc_n[DES_NKCLASS];
+    std::unordered_map<std::string, void *> named;
+};
+
+namespace {
+
+int fail(DesGpu *h, int code, const std::string &msg)
+{
+    if (h) h->err = msg;
+    return code;
+}
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return fail(h, DES_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+void drain_events(DesGpu *h)
+{
+    if (h->ev_used == 0) return;
+    cudaStreamSynchronize(h->stream);
+    for (size_t i = 0; i < h->ev_used; ++i) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, h->ev_pool[i].a, h->ev_pool[i].b);
+        h->kc_ms[h->ev_pool[i].cls] += ms;
+        h->kc_n[h->ev_pool[i].cls] += 1;
+    }
+    h->ev_used = 0;
+}
+
+struct LaunchScope {
+    DesGpu *h; int idx;
+    LaunchScope(DesGpu *h_, int cls) : h(h_), idx(-1) {
+        h->launches++;
+        if (!h->timing) return;
+        if (h->ev_used == h->ev_pool.size()) {
+            if (h->ev_pool.size() < 4096) {
+                EvPair p; cudaEventCreate(&p.a); cudaEventCreate(&p.b); p.cls = 0;
+                h->ev_pool.push_back(p);
+            } else drain_events(h);
+        }
+        idx = int(h->ev_used++);
+        h->ev_pool[idx].cls = cls;
+        cudaEventRecord(h->ev_pool[idx].a, h->stream);
+    }
+    ~LaunchScope() { if (idx >= 0) cudaEventRecord(h->ev_pool[idx].b, h->stream); }
+};
+
+#define LAUNCH(cls, kern, n, bs, ...) do { if ((n) > 0) { LaunchScope ls_(h, cls); auto kfn_ = kern; \
+    kfn_<<<DES_GRID((n), (bs)), (bs), 0, h->stream>>>(__VA_ARGS__); } } while (0)
+
+template <class T>
+int dalloc(DesGpu *h, T **p, size_t n, const char *name = nullptr)
+{
+    *p = nullptr;
+    if (n == 0) n = 1;
+    void *q = nullptr;
+    CK(cudaMalloc(&q, n * sizeof(T)));
+    h->mesh_allocs.push_back(q);
+    *p = static_cast<T *>(q);
+    if (name) h->named[name] = q;
+    return DES_OK;
+}
+
+int ensure_stage(DesGpu *h, size_t bytes)
+{
+    if (bytes <= h->stage_bytes) return DES_OK;
+    if (h->stage) cudaFree(h->stage);
+    h->stage = nullptr; h->stage_bytes = 0;
+    CK(cudaMalloc(&h->stage, bytes));
+    h->stage_bytes = bytes;
+    return DES_OK;
+}
+
+template <class T>
+int h2d(DesGpu *h, T *dst, const T *src, size_t n)
+{
+    if (n == 0) return DES_OK;
+    CK(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    return DES_OK;
+}
+
+template <class T>
+int upload_new(DesGpu *h, const T **devp, const T *src, size_t n, const char *name = nullptr)
+{
+    T *p;
+    int rc = dalloc(h, &p, n, name);
+    if (rc) return rc;
+    if (n && !src) return fail(h, DES_E_ARG, std::string("null host array: ") + (name ? name : "?"));
+    rc = h2d(h, p, src, n);
+    *devp = p;
+    return rc;
+}
+
+void free_mesh(DesGpu *h)
+{
+    for (void *p : h->mesh_allocs) cudaFree(p);
+    h->mesh_allocs.clear();
+    h->named.clear();
+    memset(&h->D, 0, sizeof(h->D));
+    h->have_mesh = h->have_state = false;
+    h->tail_pending = false;
+    h->surf_ran = false;
+}
+
+int fill_dev_params(DesGpu *h)
+{
+    const DesParam &p = h->hp;
+    DevParams &P = h->P;
+    memset(&P, 0, sizeof(P));
+    if (p.nmat < 1 || p.nmat > DES_MAX_MAT) return fail(h, DES_E_ARG, "nmat out of range");
+    switch (p.rheol_type) {
+    case DES_RH_ELASTIC: case DES_RH_MAXWELL: case DES_RH_EP: case DES_RH_EVP: break;
+    default: return fail(h, DES_E_UNSUPPORTED, "rheology type outside the hot-path scope "
+                         "(viscous / rate-and-state / plane strain)");
+    }
+    if (p.damping_option < 0 || p.damping_option > 3)
+        return fail(h, DES_E_UNSUPPORTED, "damping_option must be 0..3 (4 = Rayleigh is not built)");
+    if (p.surface_process_option != 0 && p.surface_process_option != 1)
+        return fail(h, DES_E_UNSUPPORTED, "surface_process_option must be 0 or 1 in 3D");
+    if (p.ref_pressure_option < 0 || p.ref_pressure_option > 2)
+        return fail(h, DES_E_UNSUPPORTED, "ref_pressure_option must be 0..2");
+    for (int i = 0; i < 6; ++i)
+        if (p.stress_bc_types[i] != 0 && !p.has_body_force_adjustment)
+            return fail(h, DES_E_UNSUPPORTED, "apply_stress_bcs_neumann (stress_bc_*) is not built");
+
+    P.gravity = p.gravity; P.damping_factor = p.damping_factor;
+    P.surf_diff = p.surface_diffusivity; P.surf_base_level = p.surf_base_level;
+    P.winkler_delta_rho = p.winkler_delta_rho;
+    P.elastic_foundation_constant = p.elastic_foundation_constant;
+    P.sea_water_density = p.sea_water_density;
+    P.surface_temperature = p.surface_temperature; P.zlength = p.zlength;
+    P.pseudo_speed = p.max_vbc_val * p.inertial_scaling;
+    P.visc_min = p.visc_min; P.visc_max = p.visc_max; P.tension_max = p.tension_max;
+    P.therm_diff_max = p.therm_diff_max;
+    for (int i = 0; i < DES_NBDRY; ++i) { P.vbc_values[i] = p.vbc_values[i]; P.vbc_types[i] = p.vbc_types[i]; }
+    for (int i = 0; i < 4; ++i) P.vbc_val_lateral[i] = p.vbc_val_lateral[i];
+    P.vbc_val_z1_loading_period = p.vbc_val_z1_loading_period;
+    P.damping_option = p.damping_option; P.is_quasi_static = p.is_quasi_static;
+    P.has_thermal_diffusion = p.has_thermal_diffusion;
+    P.is_using_mixed_stress = p.is_using_mixed_stress;
+    P.surface_process_option = p.surface_process_option;
+    P.ref_pressure_option = p.ref_pressure_option;
+    P.has_winkler_foundation = p.has_winkler_foundation;
+    P.has_water_loading = p.has_water_loading;
+    P.has_elastic_foundation = p.has_elastic_foundation;
+    P.rheol_type = p.rheol_type; P.nmat = p.nmat; P.mattype_ref = p.mattype_ref;
+    int nmemo = 0;
+    for (int m = 0; m < p.nmat; ++m) {
+        P.rho0[m] = p.rho0[m]; P.alpha[m] = p.alpha[m];
+        P.bulk_modulus[m] = p.bulk_modulus[m]; P.shear_modulus[m] = p.shear_modulus[m];
+        // matprops.cxx:236-252, evaluated with the HOST libm like the reference does
+        const double gas_constant = 8.3144;
+        P.visc_pow_edot[m] = 1 / p.visc_exponent[m] - 1;
+        const double pow1 = -1 / p.visc_exponent[m];
+        P.visc_coef_term[m] = std::pow(0.75 * p.visc_coefficient[m], pow1);
+        P.visc_nR[m] = p.visc_exponent[m] * gas_constant;
+        P.visc_activation_energy[m] = p.visc_activation_energy[m];
+        P.visc_activation_volume[m] = p.visc_activation_volume[m];
+        P.heat_capacity[m] = p.heat_capacity[m]; P.therm_cond[m] = p.therm_cond[m];
+        P.pls0[m] = p.pls0[m]; P.pls1[m] = p.pls1[m];
+        P.cohesion0[m] = p.cohesion0[m]; P.cohesion1[m] = p.cohesion1[m];
+        P.friction_angle0[m] = p.friction_angle0[m]; P.friction_angle1[m] = p.friction_angle1[m];
+        P.dilation_angle0[m] = p.dilation_angle0[m]; P.dilation_angle1[m] = p.dilation_angle1[m];
+        P.porosity[m] = p.porosity[m];
+        const double ang[4] = { p.friction_angle0[m], p.friction_angle1[m],
+                                p.dilation_angle0[m], p.dilation_angle1[m] };
+        for (int a = 0; a < 4; ++a) {
+            bool dup = false;
+            for (int i = 0; i < nmemo; ++i) if (P.memo_angle[i] == ang[a]) dup = true;
+            if (dup) continue;
+            P.memo_angle[nmemo] = ang[a];
+            P.memo_sin[nmemo] = std::sin(ang[a] * (M_PI / 180));
+            P.memo_tan[nmemo] = std::tan(ang[a] * (M_PI / 180));
+            nmemo++;
+        }
+    }
+    P.nmemo = nmemo;
+    return DES_OK;
+}
+
+// Builds the per-boundary-node lists apply_stress_bcs walks (bc.cxx:681-812): for each
+// live boundary, each boundary node, each support element (ascending) that owns a facet
+// on that boundary, the (facet, local facet node) whose traction the node receives.
+int build_stress_bcs(DesGpu *h, const DesMesh *m)
+{
+    const DesParam &p = h->hp;
+    Dev &D = h->D;
+    std::vector<int> felem, ffacet, fbdry;
+    std::map<int, std::vector<int> > rows;
+    unsigned mask = 0;
+    const int E = m->nelem;
+    if (p.gravity != 0) {
+        for (int i = 0; i < DES_NBDRY; ++i) {
+            if (p.vbc_types[i] != 0 && p.vbc_types[i] != 2 && p.vbc_types[i] != 4) continue;
+            if (i == 4 && !p.has_winkler_foundation) continue;
+            if (i == 5 && !p.has_water_loading) continue;
+            const int nf = m->nbfacets[i];
+            if (nf == 0) continue;
+            mask |= 1u << i;
+            const int base = int(felem.size());
+            std::unordered_map<int, int> emap;
+            emap.reserve(size_t(nf) * 2);
+            for (int n = 0; n < nf; ++n) {
+                const int e = m->bfacets[i][2*n], f = m->bfacets[i][2*n + 1];
+                felem.push_back(e); ffacet.push_back(f); fbdry.push_back(i);
+                emap[e] = n;    // sequential order: the last facet of an element wins (bc.cxx:769)
+            }
+            static const int nof[4][3] = {{1,2,3},{0,3,2},{0,1,3},{0,2,1}};
+            for (int j = 0; j < m->nbnodes[i]; ++j) {
+                const int n = m->bnodes[i][j];
+                for (int k = m->support_idx[n]; k < m->support_idx[n + 1]; ++k) {
+                    const int e = m->support_arr[k];
+                    auto it = emap.find(e);
+                    if (it == emap.end()) continue;
+                    const int ib = it->second;
+                    const int f = m->bfacets[i][2*ib + 1];
+                    for (int l = 0; l < 3; ++l) {
+                        if (n == m->connectivity[size_t(nof[f][l]) * E + e]) {
+                            rows[n].push_back((base + ib) * 3 + l);
+                            break;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    h->P.sbc_mask = mask;
+    D.nsbc_facets = int(felem.size());
+    int rc;
+    if ((rc = upload_new(h, &D.sbc_felem, felem.data(), felem.size()))) return rc;
+    if ((rc = upload_new(h, &D.sbc_ffacet, ffacet.data(), ffacet.size()))) return rc;
+    if ((rc = upload_new(h, &D.sbc_fbdry, fbdry.data(), fbdry.size()))) return rc;
+    if ((rc = dalloc(h, &D.sbc_ftr, felem.size() * 9))) return rc;
+    std::vector<int> idx(1, 0), ent, row;
+    if (!rows.empty()) {
+        row.assign(m->nnode, -1);
+        int r = 0;
+        for (auto &kv : rows) {
+            row[kv.first] = r++;
+            ent.insert(ent.end(), kv.second.begin(), kv.second.end());
+            idx.push_back(int(ent.size()));
+        }
+    }
+    if ((rc = upload_new(h, &D.sbc_row, row.data(), row.size()))) return rc;
+    if ((rc = upload_new(h, &D.sbc_idx, idx.data(), idx.size()))) return rc;
+    if ((rc = upload_new(h, &D.sbc_ent, ent.data(), ent.size()))) return rc;
+    CK(cudaStreamSynchronize(h->stream));   // the std::vectors above die here
+    return DES_OK;
+}
+
+// ---- schedule pieces -----------------------------------------------------------------
+
+// tail_flags of k_elem_a for the fused step: volume+mass when the mesh moves
+// (dynearthsol.cxx:871-872), rotation when the rheology has the elastic bit (:875-876)
+int tail_flags(const DesGpu *h)
+{
+    return (h->hp.has_moving_mesh ? 3 : 0) | ((h->hp.rheol_type & DES_RH_ELASTIC) ? 4 : 0);
+}
+int head_flags(const DesGpu *h) { return (h->hp.has_thermal_diffusion ? 1 : 0) | 2 | 4; }
+
+// Completes the deferred end-of-step element work (volume, mass, rotation) on its own.
+int flush_tail(DesGpu *h)
+{
+    if (!h->tail_pending) return DES_OK;
+    const int mm = h->hp.has_moving_mesh;
+    LAUNCH(KC_ELEM_A, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, h->dt_prev, tail_flags(h), 0);
+    if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, false>), h->D.nnode, 256, h->P, h->D, 0.0, 0);
+    h->tail_pending = false;
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
+int run_surface(DesGpu *h, double dt, bool with_volume_n)
+{
+    Dev &D = h->D;
+    if (h->hp.surface_process_option == 1 && D.ntop > 0) {
+        CK(cudaMemsetAsync(D.maxdh_bits, 0, sizeof(unsigned long long), h->stream));
+        LAUNCH(KC_SURFACE, k_surf_facets, D.etop, 128, D);
+        LAUNCH(KC_SURFACE, k_surf_nodes, D.ntop, 128, h->P, D, dt);
+        LAUNCH(KC_SURFACE, k_surf_edvacc, D.etop, 128, D);
+        h->surf_ran = true;
+    }
+    LAUNCH(KC_SURFACE, k_surf_correct_elems, D.ntop_elems, 128, D);
+    if (with_volume_n) LAUNCH(KC_SURFACE, k_surf_correct_nodes, D.ntop, 128, D);
+    return DES_OK;
+}
+
+} // namespace
+
+// =========================================================================================
+extern "C" {
+
+int des_gpu_create(const DesParam *param, int device, DesGpu **out)
+{
+    if (!param || !out) return DES_E_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || device < 0 || device >= ndev)
+        return DES_E_NODEVICE;
+    if (cudaSetDevice(device) != cudaSuccess) return DES_E_NODEVICE;
+    DesGpu *h = new DesGpu;
+    h->device = device;
+    h->hp = *param;
+    memset(&h->D, 0, sizeof(h->D));
+    memset(h->kc_ms, 0, sizeof(h->kc_ms));
+    memset(h->kc_n, 0, sizeof(h->kc_n));
+    int rc = fill_dev_params(h);
+    if (rc == DES_OK && cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
+        rc = fail(h, DES_E_CUDA, "cudaStreamCreate failed");
+    *out = h;   // returned even on failure so the caller can read last_error, then destroy
+    return rc;
+}
+
+int des_gpu_destroy(DesGpu *h)
+{
+    if (!h) return DES_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    free_mesh(h);
+    if (h->stage) cudaFree(h->stage);
+    if (h->dt_partials) cudaFree(h->dt_partials);
+    for (auto &p : h->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return DES_OK;
+}
+
+const char *des_gpu_last_error(const DesGpu *h) { return h ? h->err.c_str() : "null handle"; }
+
+int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
+{
+    if (!h || !m) return DES_E_ARG;
+    if (m->nnode <= 0 || m->nelem <= 0) return fail(h, DES_E_ARG, "empty mesh");
+    if (size_t(m->nelem) * 4 >= (size_t(1) << 31)) return fail(h, DES_E_ARG, "nelem*4 overflows int32");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    free_mesh(h);
+    Dev &D = h->D;
+    const int N = m->nnode, E = m->nelem;
+    D.nnode = N; D.nelem = E;
+    int rc;
+    // connectivity -> int4, support -> packed entries
+    {
+        if ((rc = ensure_stage(h, size_t(E) * 8 * sizeof(int)))) return rc;
+        int *st = static_cast<int *>(h->stage);
+        int4 *conn; if ((rc = dalloc(h, &conn, E, "conn"))) return rc;
+        if ((rc = h2d(h, st, m->connectivity, size_t(E) * 4))) return rc;
+        LAUNCH(KC_PACK, k_pack_conn, E, 256, E, st, conn);
+        D.conn = conn;
+        CK(cudaStreamSynchronize(h->stream));
+        int *ent; if ((rc = dalloc(h, &ent, size_t(E) * 4, "sup_ent"))) return rc;
+        if ((rc = h2d(h, st, m->support_arr, size_t(E) * 4))) return rc;
+        if ((rc = h2d(h, st + size_t(E) * 4, m->support_lidx, size_t(E) * 4))) return rc;
+        LAUNCH(KC_PACK, k_pack_support, E * 4, 256, E * 4, st, st + size_t(E) * 4, ent);
+        D.sup_ent = ent;
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if (m->support_idx[N] != 4 * E) return fail(h, DES_E_ARG, "support_idx[nnode] != 4*nelem");
+    if ((rc = upload_new(h, &D.sup_idx, m->support_idx, size_t(N) + 1, "sup_idx"))) return rc;
+    if ((rc = upload_new(h, &D.bcflag, m->bcflag, size_t(N), "bcflag"))) return rc;
+    {
+        int *mk; if ((rc = dalloc(h, &mk, size_t(E) * h->hp.nmat, "elemmarkers"))) return rc;
+        D.elemmarkers = mk;
+    }
+    // node fields
+    if ((rc = dalloc(h, &D.xT, N, "xT"))) return rc;
+    if ((rc = dalloc(h, &D.vv, N, "vv"))) return rc;
+    if ((rc = dalloc(h, &D.coord0, h->hp.has_elastic_foundation ? N : 1))) return rc;
+    if ((rc = dalloc(h, &D.force, size_t(N) * 3, "force"))) return rc;
+    if ((rc = dalloc(h, &D.mass, N, "mass"))) return rc;
+    if ((rc = dalloc(h, &D.tmass, N, "tmass"))) return rc;
+    if ((rc = dalloc(h, &D.volume_n, N, "volume_n"))) return rc;
+    if ((rc = dalloc(h, &D.ntmp, N, "ntmp"))) return rc;
+    if ((rc = dalloc(h, &D.dhacc, N, "dhacc"))) return rc;
+    CK(cudaMemsetAsync(D.xT, 0, sizeof(double4) * N, h->stream));
+    CK(cudaMemsetAsync(D.vv, 0, sizeof(double4) * N, h->stream));
+    CK(cudaMemsetAsync(D.force, 0, sizeof(double) * 3 * N, h->stream));
+    CK(cudaMemsetAsync(D.tmass, 0, sizeof(double) * N, h->stream));
+    CK(cudaMemsetAsync(D.dhacc, 0, sizeof(double) * N, h->stream));
+    // element fields
+    if ((rc = dalloc(h, &D.stress, size_t(E) * 6, "stress"))) return rc;
+    if ((rc = dalloc(h, &D.strain, size_t(E) * 6, "strain"))) return rc;
+    if ((rc = dalloc(h, &D.strain_rate, size_t(E) * 6, "strain_rate"))) return rc;
+    if ((rc = dalloc(h, &D.plstrain, E, "plstrain"))) return rc;
+    if ((rc = dalloc(h, &D.delta_plstrain, E, "delta_plstrain"))) return rc;
+    if ((rc = dalloc(h, &D.volume, E, "volume"))) return rc;
+    if ((rc = dalloc(h, &D.volume_old, E, "volume_old"))) return rc;
+    if ((rc = dalloc(h, &D.dpressure, E, "dpressure"))) return rc;
+    if ((rc = dalloc(h, &D.edvoldt, E, "edvoldt"))) return rc;
+    if ((rc = dalloc(h, &D.viscosity, E, "viscosity"))) return rc;
+    { double *r; if ((rc = dalloc(h, &r, E, "radiogenic"))) return rc; D.radiogenic = r;
+      CK(cudaMemsetAsync(r, 0, sizeof(double) * E, h->stream)); }
+    if ((rc = dalloc(h, &D.ca, size_t(E) * 8, "ca"))) return rc;
+    if ((rc = dalloc(h, &D.etmp, E, "etmp"))) return rc;
+    if ((rc = dalloc(h, &D.fc, size_t(E) * 12, "fc"))) return rc;
+    CK(cudaMemsetAsync(D.strain_rate, 0, sizeof(double) * 6 * E, h->stream));
+    CK(cudaMemsetAsync(D.strain, 0, sizeof(double) * 6 * E, h->stream));
+    CK(cudaMemsetAsync(D.stress, 0, sizeof(double) * 6 * E, h->stream));
+    CK(cudaMemsetAsync(D.dpressure, 0, sizeof(double) * E, h->stream));
+    CK(cudaMemsetAsync(D.delta_plstrain, 0, sizeof(double) * E, h->stream));
+    CK(cudaMemsetAsync(D.ca, 0, sizeof(double) * 8 * E, h->stream));
+    // slant-boundary tables
+    for (int i = 0; i < DES_NBDRY; ++i)
+        for (int d = 0; d < 3; ++d)
+            h->P.bnormals[i][d] = m->bnormals ? m->bnormals[d * DES_NBDRY + i] : 0.0;
+    {
+        std::vector<int> slot(100, -1);
+        if (m->edge_slot) slot.assign(m->edge_slot, m->edge_slot + 100);
+        if ((rc = upload_new(h, &D.edge_slot, slot.data(), 100))) return rc;
+        if ((rc = upload_new(h, &D.edge_vec, m->edge_vec, size_t(m->n_edge_vec)))) return rc;
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    // surface
+    D.ntop = m->ntop; D.etop = m->etop; D.ntop_elems = m->ntop_elems;
+    if ((rc = upload_new(h, &D.top_nodes, m->top_nodes, size_t(m->ntop)))) return rc;
+    if ((rc = upload_new(h, &D.top_elems, m->top_elems, size_t(m->ntop_elems)))) return rc;
+    if (m->etop != m->nbfacets[5]) return fail(h, DES_E_ARG, "etop != nbfacets[z1]");
+    {
+        std::vector<int> fe(m->etop), ff(m->etop);
+        for (int i = 0; i < m->etop; ++i) { fe[i] = m->bfacets[5][2*i]; ff[i] = m->bfacets[5][2*i + 1]; }
+        if ((rc = upload_new(h, &D.top_felem, fe.data(), fe.size()))) return rc;
+        if ((rc = upload_new(h, &D.top_ffacet, ff.data(), ff.size()))) return rc;
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if (m->ntop > 0) {
+        if ((rc = upload_new(h, &D.ssup_idx, m->support_surf_idx, size_t(m->ntop) + 1))) return rc;
+        if ((rc = upload_new(h, &D.ssup_arr, m->support_surf_arr, size_t(m->support_surf_idx[m->ntop])))) return rc;
+    }
+    if ((rc = upload_new(h, &D.elem_and_nodes, m->elem_and_nodes, size_t(m->etop) * 3))) return rc;
+    if ((rc = upload_new(h, &D.conn_surf, m->connectivity_surface, size_t(m->etop) * 4))) return rc;
+    if ((rc = dalloc(h, &D.dh, m->ntop))) return rc;
+    if ((rc = dalloc(h, &D.edvacc_surf, m->etop, "edvacc_surf"))) return rc;
+    if ((rc = dalloc(h, &D.s_area, m->etop))) return rc;
+    if ((rc = dalloc(h, &D.s_slope, size_t(m->etop) * 3))) return rc;
+    if ((rc = dalloc(h, &D.maxdh_bits, 1))) return rc;
+    CK(cudaMemsetAsync(D.edvacc_surf, 0, sizeof(double) * std::max(1, m->etop), h->stream));
+    CK(cudaMemsetAsync(D.dh, 0, sizeof(double) * std::max(1, m->ntop), h->stream));
+    CK(cudaMemsetAsync(D.maxdh_bits, 0, sizeof(unsigned long long), h->stream));
+
+    if ((rc = build_stress_bcs(h, m))) return rc;
+
+    h->dt_blocks = 148 * 4;
+    if (!h->dt_partials) CK(cudaMalloc(&h->dt_partials, sizeof(DtPartial) * h->dt_blocks));
+    CK(cudaStreamSynchronize(h->stream));
+    h->have_mesh = true;
+    return DES_OK;
+}
+
+int des_gpu_upload_elemmarkers(DesGpu *h, const int *elemmarkers)
+{
+    if (!h || !elemmarkers) return DES_E_ARG;
+    if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    CK(cudaSetDevice(h->device));
+    int rc = flush_tail(h);     // the pending mass computation must see the OLD markers
+    if (rc) return rc;
+    rc = h2d(h, const_cast<int *>(h->D.elemmarkers), elemmarkers, size_t(h->D.nelem) * h->hp.nmat);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(h->stream));
+    return DES_OK;
+}
+
+int des_gpu_set_compensation_pressure(DesGpu *h, double p)
+{
+    if (!h) return DES_E_ARG;
+    h->compensation_pressure = p;
+    return DES_OK;
+}
+
+int des_gpu_upload_state(DesGpu *h, const DesState *s)
+{
+    if (!h || !s) return DES_E_ARG;
+    if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    CK(cudaSetDevice(h->device));
+    int rc = flush_tail(h);
+    if (rc) return rc;
+    Dev &D = h->D;
+    const size_t N = D.nnode, E = D.nelem;
+    if ((rc = ensure_stage(h, std::max(N * 3, size_t(1)) * sizeof(double)))) return rc;
+    double *st = static_cast<double *>(h->stage);
+    if (s->coord) {
+        if ((rc = h2d(h, st, s->coord, N * 3))) return rc;
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), st, D.xT);
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if (s->vel) {
+        if ((rc = h2d(h, st, s->vel, N * 3))) return rc;
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), st, D.vv);
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if (s->coord0 && h->hp.has_elastic_foundation) {
+        if ((rc = h2d(h, st, s->coord0, N * 3))) return rc;
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), st, D.coord0);
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if (s->temperature) {
+        if ((rc = h2d(h, st, s->temperature, N))) return rc;
+        LAUNCH(KC_PACK, k_pack_w, int(N), 256, int(N), st, D.xT);
+        CK(cudaStreamSynchronize(h->stream));
+    }
+#define UP(field, dev, n) if (s->field) { if ((rc = h2d(h, dev, (const double *)s->field, n))) return rc; }
+    UP(stress, D.stress, E * 6) UP(strain, D.strain, E * 6) UP(strain_rate, D.strain_rate, E * 6)
+    UP(plstrain, D.plstrain, E) UP(delta_plstrain, D.delta_plstrain, E)
+    UP(volume, D.volume, E) UP(volume_old, D.volume_old, E)
+    UP(viscosity, D.viscosity, E) UP(dpressure, D.dpressure, E) UP(edvoldt, D.edvoldt, E)
+    UP(radiogenic_source, const_cast<double *>(D.radiogenic), E)
+    UP(force, D.force, N * 3) UP(volume_n, D.volume_n, N) UP(mass, D.mass, N) UP(tmass, D.tmass, N)
+    UP(ntmp, D.ntmp, N) UP(dhacc, D.dhacc, N) UP(edvacc_surf, D.edvacc_surf, size_t(D.etop))
+#undef UP
+    CK(cudaStreamSynchronize(h->stream));
+    h->have_state = true;
+    return DES_OK;
+}
+
+int des_gpu_download_state(DesGpu *h, const DesState *s)
+{
+    if (!h || !s) return DES_E_ARG;
+    if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    CK(cudaSetDevice(h->device));
+    int rc = flush_tail(h);
+    if (rc) return rc;
+    Dev &D = h->D;
+    const size_t N = D.nnode, E = D.nelem;
+    if ((rc = ensure_stage(h, std::max(N * 3, size_t(1)) * sizeof(double)))) return rc;
+    double *st = static_cast<double *>(h->stage);
+#define DN(dst, src, n) CK(cudaMemcpyAsync(dst, src, (n) * sizeof(double), cudaMemcpyDeviceToHost, h->stream))
+    if (s->coord) {
+        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, st);
+        DN(s->coord, st, N * 3); CK(cudaStreamSynchronize(h->stream));
+    }
+    if (s->vel) {
+        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.vv, st);
+        DN(s->vel, st, N * 3); CK(cudaStreamSynchronize(h->stream));
+    }
+    if (s->temperature) {
+        LAUNCH(KC_PACK, k_unpack_w, int(N), 256, int(N), D.xT, st);
+        DN(s->temperature, st, N); CK(cudaStreamSynchronize(h->stream));
+    }
+#define DOWN(field, dev, n) if (s->field) { DN(s->field, dev, n); }
+    DOWN(stress, D.stress, E * 6) DOWN(strain, D.strain, E * 6) DOWN(strain_rate, D.strain_rate, E * 6)
+    DOWN(plstrain, D.plstrain, E) DOWN(delta_plstrain, D.delta_plstrain, E)
+    DOWN(volume, D.volume, E) DOWN(volume_old, D.volume_old, E)
+    DOWN(viscosity, D.viscosity, E) DOWN(dpressure, D.dpressure, E) DOWN(edvoldt, D.edvoldt, E)
+    DOWN(radiogenic_source, D.radiogenic, E)
+    DOWN(force, D.force, N * 3) DOWN(volume_n, D.volume_n, N) DOWN(mass, D.mass, N) DOWN(tmass, D.tmass, N)
+    DOWN(ntmp, D.ntmp, N) DOWN(dhacc, D.dhacc, N) DOWN(edvacc_surf, D.edvacc_surf, size_t(D.etop))
+#undef DOWN
+#undef DN
+    CK(cudaStreamSynchronize(h->stream));
+    return DES_OK;
+}
+
+int des_gpu_sync(DesGpu *h)
+{
+    if (!h) return DES_E_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
+// -----------------------------------------------------------------------------------------
+int des_gpu_step(DesGpu *h, double dt, double time, int steps)
+{
+    (void)steps;
+    if (!h) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
+    Dev &D = h->D;
+    const int N = D.nnode, E = D.nelem;
+    const int mm = h->hp.has_moving_mesh;
+
+    // E-A / N-A
+    if (h->tail_pending) {
+        LAUNCH(KC_ELEM_A, (k_elem_a<true, true>), E, 256, h->P, D, h->dt_prev, tail_flags(h), head_flags(h));
+        if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, true>), N, 256, h->P, D, dt, head_flags(h));
+        else    LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, head_flags(h));
+        h->tail_pending = false;
+    }
+    else {
+        LAUNCH(KC_ELEM_A, (k_elem_a<false, true>), E, 256, h->P, D, 0.0, 0, head_flags(h));
+        LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, head_flags(h));
+    }
+    // E-B / N-B
+    LAUNCH(KC_ELEM_B, k_elem_b, E, 128, h->P, D, dt, 0);
+    if (h->hp.is_using_mixed_stress) LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
+    // E-C / N-C
+    LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
+    if (h->hp.is_using_mixed_stress) LAUNCH(KC_ELEM_C, (k_elem_c<true>), E, 256, h->P, D);
+    else                             LAUNCH(KC_ELEM_C, (k_elem_c<false>), E, 256, h->P, D);
+    int bc_z1 = h->hp.vbc_types[5];
+    if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
+    LAUNCH(KC_NODE_C, k_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
+    // update_mesh remainder
+    if (mm) {
+        int rc = run_surface(h, dt, false);
+        if (rc) return rc;
+        std::swap(D.volume, D.volume_old);      // dynearthsol.cxx:466-470
+    }
+    h->tail_pending = true;
+    h->dt_prev = dt;
+    h->last_dt = dt;
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
+int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out)
+{
+    if (!h || !out) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    int rc = flush_tail(h);
+    if (rc) return rc;
+    {
+        LaunchScope ls(h, KC_DT);
+        k_dt<<<h->dt_blocks, 256, 0, h->stream>>>(h->P, h->D, h->dt_partials);
+    }
+    std::vector<DtPartial> part(h->dt_blocks);
+    unsigned long long bits = 0;
+    CK(cudaMemcpyAsync(part.data(), h->dt_partials, sizeof(DtPartial) * h->dt_blocks,
+                       cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&bits, h->D.maxdh_bits, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    DtPartial r = part[0];
+    for (int i = 1; i < h->dt_blocks; ++i) {
+        r.minl = std::min(r.minl, part[i].minl);
+        r.dt_maxwell = std::min(r.dt_maxwell, part[i].dt_maxwell);
+        r.dt_diffusion = std::min(r.dt_diffusion, part[i].dt_diffusion);
+        r.global_dt_min = std::min(r.global_dt_min, part[i].global_dt_min);
+        r.max_vem = std::max(r.max_vem, part[i].max_vem);
+    }
+    out->minl = r.minl; out->dt_maxwell = r.dt_maxwell; out->dt_diffusion = r.dt_diffusion;
+    out->global_dt_min = r.global_dt_min; out->global_max_vem = r.max_vem;
+    double maxdh; memcpy(&maxdh, &bits, sizeof(double));
+    out->max_surf_vel = (h->surf_ran && h->last_dt > 0) ? maxdh / h->last_dt : 0.0;   // bc.cxx:1825
+    return DES_OK;
+}
+
+// geometry.cxx:1597-1630 (use_global_velocity_scaling == false)
+double des_dt_from_reductions(const DesParam *p, const DesDtReductions *r, double *max_global_vel_mag)
+{
+    if (p->fixed_dt != 0) return p->fixed_dt;
+    double max_vbc_val;
+    if (p->characteristic_speed == 0) {
+        max_vbc_val = p->max_vbc_val;
+        if (p->surface_process_option > 0)
+            max_vbc_val = std::max(max_vbc_val, r->max_surf_vel * 5e-1);
+    }
+    else
+        max_vbc_val = p->characteristic_speed;
+    double gmv = std::max(r->global_max_vem, p->max_vbc_val);
+    if (max_global_vel_mag) *max_global_vel_mag = gmv;
+    double dt_advection = 0.5 * r->minl / max_vbc_val;
+    double dt_elastic = (p->is_quasi_static) ?
+        0.5 * r->minl / (max_vbc_val * p->inertial_scaling) :
+        0.5 * r->minl / std::sqrt(p->bulk_modulus[p->mattype_ref] / p->rho0[p->mattype_ref]);
+    double dt_hydro = std::numeric_limits<double>::max();
+    double dt = std::min({dt_elastic, r->dt_maxwell, dt_advection, r->dt_diffusion, dt_hydro}) * p->dt_fraction;
+    return dt;
+}
+
+// ---- instrumentation --------------------------------------------------------------------
+long long des_gpu_launch_count(const DesGpu *h) { return h ? h->launches : 0; }
+
+int des_gpu_enable_kernel_timing(DesGpu *h, int on)
+{
+    if (!h) return DES_E_ARG;
+    drain_events(h);
+    h->timing = on != 0;
+    memset(h->kc_ms, 0, sizeof(h->kc_ms));
+    memset(h->kc_n, 0, sizeof(h->kc_n));
+    return DES_OK;
+}
+
+int des_gpu_kernel_time(DesGpu *h, int which, double *ms, long long *launches, const char **name)
+{
+    if (!h || which < 0 || which >= DES_NKCLASS) return DES_E_ARG;
+    drain_events(h);
+    if (ms) *ms = h->kc_ms[which];
+    if (launches) *launches = h->kc_n[which];
+    if (name) *name = kclass_name[which];
+    return DES_OK;
+}
+
+void *des_gpu_device_ptr(DesGpu *h, const char *name)
+{
+    if (!h || !name) return nullptr;
+    std::string n(name);
+    // arrays whose pointer changes (volume swap) are resolved live
+    if (n == "volume") return h->D.volume;
+    if (n == "volume_old") return h->D.volume_old;
+    auto it = h->named.find(n);
+    return it == h->named.end() ? nullptr : it->second;
+}
+
+} // extern "C"
+
+#include "des_twins.cuh"

@@ -1,0 +1,220 @@
+/* des_gpu.h -- C-ABI of the B200-native explicit time-step core for DynEarthSol (3D).
+ *
+ * This is the drop-in boundary for the reference's step loop (dynearthsol.cxx:768-894):
+ * plain pointers and sizes, no C++/torch types.  The reference has no plugin ABI of its
+ * own (its boundary is free C++ functions taking `const Param&` / `Variables&`,
+ * fields.hpp / rheology.hpp / geometry.hpp / bc.hpp), so each entry point below names the
+ * reference call it replaces.  All host arrays use the reference's in-memory layout:
+ * Array2D<T,N> is SoA, element [i][d] at a[d*n + i] (array2d.hpp:410-425, built -DSOA);
+ * double_vec / int_vec are plain contiguous arrays.  Indices are int32, fields are FP64.
+ *
+ * Ownership: host pointers are BORROWED for the duration of one call and never cached
+ * (remesh() re-news nearly every array, fields.cxx:125-194).  The handle owns all device
+ * memory.  Errors: every call returns 0 or a DES_E_* code; the library never exit()s.
+ * Threading: call from one host thread (the driver is single-threaded at call level).
+ *
+ * There is NO CPU fallback: without a CUDA device des_gpu_create() fails with DES_E_NODEVICE.
+ */
+#ifndef DES_GPU_H
+#define DES_GPU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DES_MAX_MAT 16      /* materials per model (reference: mat.num_materials) */
+#define DES_NBDRY 10        /* constants.hpp:27-37: x0 x1 y0 y1 z0 z1 n0 n1 n2 n3 */
+
+/* status codes; the numeric values of the runtime ones follow utils.hpp:20-44 in spirit */
+enum {
+    DES_OK = 0,
+    DES_E_NODEVICE = 1,     /* no CUDA device / CUDA runtime failure at create */
+    DES_E_CUDA = 2,         /* a CUDA call failed; see des_gpu_last_error() */
+    DES_E_ARG = 3,          /* bad argument (null pointer, size mismatch) */
+    DES_E_UNSUPPORTED = 4,  /* option outside the hot-path scope */
+    DES_E_STATE = 5,        /* call out of order (e.g. step before upload) */
+    DES_E_NAN = 11          /* runtime NaN / non-positive dt (EXIT_RUNTIME_NAN analogue) */
+};
+
+/* rheology bit flags, matprops.hpp:86-95 */
+enum {
+    DES_RH_ELASTIC = 1, DES_RH_VISCOUS = 2, DES_RH_MAXWELL = 3,
+    DES_RH_EP = 5, DES_RH_EVP = 7
+};
+
+typedef struct DesGpu DesGpu;   /* opaque */
+
+/* The scalars of Param.{control,bc,mat,mesh} and Variables the kernels read
+ * (parameters.hpp:160-560; input.cxx defaults).  Filled by the bridge from `Param`. */
+typedef struct DesParam {
+    /* control */
+    double gravity;                 /* control.gravity */
+    double inertial_scaling;        /* control.inertial_scaling */
+    double damping_factor;          /* control.damping_factor */
+    double surface_diffusivity;     /* var.surfinfo.surf_diff (= control.surface_diffusivity) */
+    double surf_base_level;         /* control.surf_base_level */
+    double dt_fraction;             /* control.dt_fraction */
+    double fixed_dt;                /* control.fixed_dt (0 = dynamic) */
+    double characteristic_speed;    /* control.characteristic_speed (0 = use max_vbc_val) */
+    int damping_option;             /* control.damping_option 0..4, fields.cxx:490-575 */
+    int is_quasi_static;            /* control.is_quasi_static */
+    int has_thermal_diffusion;      /* control.has_thermal_diffusion */
+    int is_using_mixed_stress;      /* control.is_using_mixed_stress -> NMD_stress */
+    int surface_process_option;     /* 0 or 1 (simple_diffusion) */
+    int ref_pressure_option;        /* 0, 1 (PREM), 2 (modified PREM); matprops.cxx:153-174 */
+    int has_moving_mesh;            /* control.has_moving_mesh */
+    int has_body_force_adjustment;  /* ic.has_body_force_adjustment (gates neumann bcs) */
+    /* bc */
+    int has_winkler_foundation, has_water_loading, has_elastic_foundation;
+    double winkler_delta_rho, elastic_foundation_constant, sea_water_density;
+    double surface_temperature;
+    int vbc_types[DES_NBDRY];       /* var.vbc_types, dynearthsol.cxx:62-71 */
+    double vbc_values[DES_NBDRY];   /* var.vbc_values */
+    double vbc_val_lateral[4];      /* bc.vbc_val_{x0,x1,y0,y1}_l (type 6) */
+    double vbc_val_z1_loading_period;
+    int stress_bc_types[6];         /* must be all 0 (neumann path: DES_E_UNSUPPORTED) */
+    double max_vbc_val;             /* var.max_vbc_val (find_max_vbc, bc.cxx:66-91) */
+    /* mesh */
+    double zlength;                 /* mesh.zlength (Winkler datum) */
+    /* mat */
+    int rheol_type;                 /* DES_RH_* */
+    int nmat;
+    int mattype_ref;
+    double visc_min, visc_max, tension_max, therm_diff_max;
+    double rho0[DES_MAX_MAT], alpha[DES_MAX_MAT];
+    double bulk_modulus[DES_MAX_MAT], shear_modulus[DES_MAX_MAT];
+    double visc_exponent[DES_MAX_MAT], visc_coefficient[DES_MAX_MAT];
+    double visc_activation_energy[DES_MAX_MAT], visc_activation_volume[DES_MAX_MAT];
+    double heat_capacity[DES_MAX_MAT], therm_cond[DES_MAX_MAT];
+    double pls0[DES_MAX_MAT], pls1[DES_MAX_MAT];
+    double cohesion0[DES_MAX_MAT], cohesion1[DES_MAX_MAT];
+    double friction_angle0[DES_MAX_MAT], friction_angle1[DES_MAX_MAT];
+    double dilation_angle0[DES_MAX_MAT], dilation_angle1[DES_MAX_MAT];
+    double porosity[DES_MAX_MAT];
+} DesParam;
+
+/* Topology produced by the reference's host mesh code (mesh.cxx), immutable between
+ * remeshes.  Replaces nothing: it is what the kernels gather through. */
+typedef struct DesMesh {
+    int nnode, nelem;
+    const int *connectivity;        /* conn_t, [4*nelem] SoA */
+    const unsigned *bcflag;         /* [nnode] */
+    const int *support_idx;         /* Support.idx_data [nnode+1]  (mesh.cxx:3287-3329) */
+    const int *support_arr;         /* Support.arr_data [4*nelem], ascending element ids */
+    const int *support_lidx;        /* Support.lidx_data [4*nelem] */
+    int nbfacets[DES_NBDRY];
+    const int *bfacets[DES_NBDRY];  /* (elem, facet) pairs, [2*nbfacets[i]] */
+    int nbnodes[DES_NBDRY];
+    const int *bnodes[DES_NBDRY];
+    const double *bnormals;         /* array_t(10): [3*10] SoA stride 10 (bc.cxx:94-224) */
+    int n_edge_vec;                 /* number of doubles in edge_vec */
+    const double *edge_vec;
+    const int *edge_slot;           /* [100], -1 = no shared edge */
+    int ntop_elems;
+    const int *top_elems;           /* var.top_elems */
+    int ntop;                       /* surfinfo.ntop */
+    const int *top_nodes;           /* surfinfo.top_nodes [ntop] */
+    int etop;                       /* surfinfo.etop == nbfacets[z1] */
+    const int *support_surf_idx;    /* surfinfo.support_surf.idx_data [ntop+1] */
+    const int *support_surf_arr;    /* surfinfo.support_surf.arr_data */
+    const int *elem_and_nodes;      /* segment_t [3*etop] SoA: top-node LOCAL index per facet node */
+    const int *connectivity_surface;/* conn_t(etop): [4*etop] SoA, first 3 columns used */
+} DesMesh;
+
+/* Field arrays.  NULL members are skipped, so the same struct serves as an upload list,
+ * a download list and a download mask.  Classification: SURVEY.md section 8b. */
+typedef struct DesState {
+    double *coord, *vel, *coord0;                   /* [3*nnode] SoA */
+    double *temperature;                            /* [nnode] */
+    double *stress, *strain, *strain_rate;          /* [6*nelem] SoA {XX,YY,ZZ,XY,XZ,YZ} */
+    double *plstrain, *delta_plstrain;              /* [nelem] */
+    double *volume, *volume_old;                    /* [nelem] */
+    double *viscosity, *dpressure, *edvoldt;        /* [nelem] */
+    double *radiogenic_source;                      /* [nelem] */
+    double *force;                                  /* [3*nnode] (derived) */
+    double *volume_n, *mass, *tmass;                /* [nnode] (derived) */
+    double *ntmp;                                   /* [nnode] scratch (debug/parity) */
+    double *dhacc;                                  /* surfinfo.dhacc [nnode] */
+    double *edvacc_surf;                            /* surfinfo.edvacc_surf [etop] */
+} DesState;
+
+/* What compute_dt()'s element loop reduces (geometry.cxx:1506-1593) plus the surface
+ * velocity it reads; the scalar algebra after the loop stays on the host
+ * (des_dt_from_reductions). */
+typedef struct DesDtReductions {
+    double minl, dt_maxwell, dt_diffusion, global_dt_min, global_max_vem, max_surf_vel;
+} DesDtReductions;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+/* after init()/restart() (dynearthsol.cxx:634-650); replaces init_offload_device() */
+int des_gpu_create(const DesParam *param, int device, DesGpu **out);
+/* end() (dynearthsol.cxx:440-445) */
+int des_gpu_destroy(DesGpu *h);
+const char *des_gpu_last_error(const DesGpu *h);
+
+/* ---- data movement ------------------------------------------------------------------- */
+/* after init, restart and every remesh() (dynearthsol.cxx:950): new topology; drops all
+ * device fields, so an upload_state must follow. */
+int des_gpu_upload_mesh(DesGpu *h, const DesMesh *mesh);
+/* H->D of the members that are non-NULL */
+int des_gpu_upload_state(DesGpu *h, const DesState *s);
+/* D->H into the reference's own Variables storage, before output (dynearthsol.cxx:926),
+ * phase_changes (:885), bad_mesh_quality (:942), remesh (:950), average_fields (:903).
+ * Completes any deferred end-of-step work first. */
+int des_gpu_download_state(DesGpu *h, const DesState *s);
+/* the four refresh_elem_cache() sites (dynearthsol.cxx:206,479,776,887): flat
+ * [nelem*nmat] copy of elemmarkers; replaces MatProps::refresh_elem_cache (matprops.cxx:259) */
+int des_gpu_upload_elemmarkers(DesGpu *h, const int *elemmarkers);
+/* scalars of Variables that change while running */
+int des_gpu_set_compensation_pressure(DesGpu *h, double p);
+
+/* ---- the step ------------------------------------------------------------------------ */
+/* One explicit step == dynearthsol.cxx:778-876 for a run without PT loop / hydraulics:
+ * update_temperature, update_strain_rate, compute_dvoldt, compute_edvoldt, update_stress,
+ * NMD_stress, update_force (+apply_stress_bcs, apply_damping), update_velocity, apply_vbcs,
+ * update_mesh (update_coordinate, surface_processes, volume swap, compute_volume,
+ * compute_mass), rotate_stress.  `time` and `steps` are var.time / var.steps AFTER the
+ * increment at dynearthsol.cxx:773-774.  Asynchronous; the end-of-step element work
+ * (volume, mass, rotation) may be deferred and fused with the next step's first kernel. */
+int des_gpu_step(DesGpu *h, double dt, double time, int steps);
+/* compute_dt (dynearthsol.cxx:643,893; geometry.cxx:1480): device reductions only */
+int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out);
+/* host scalar algebra of geometry.cxx:1597-1630 (no GPU work); returns dt, <=0 on error */
+double des_dt_from_reductions(const DesParam *param, const DesDtReductions *r,
+                              double *max_global_vel_mag);
+int des_gpu_sync(DesGpu *h);
+
+/* ---- fine-grained twins of the reference calls (PT loop dynearthsol.cxx:803-864,
+ * isostasy_adjustment :506-539, remeshing.cxx:3133-3168; also the per-function parity
+ * tests).  Same device state; each is the un-fused reference loop nest. --------------- */
+int des_gpu_update_temperature(DesGpu *h, double dt);               /* fields.cxx:197 */
+int des_gpu_update_strain_rate(DesGpu *h);                          /* fields.cxx:405 */
+int des_gpu_compute_dvoldt(DesGpu *h);                              /* geometry.cxx:203 */
+int des_gpu_compute_edvoldt(DesGpu *h);                             /* geometry.cxx:249 */
+int des_gpu_update_stress(DesGpu *h, double dt);                    /* rheology.cxx:703 */
+int des_gpu_nmd_stress(DesGpu *h);                                  /* geometry.cxx:282 */
+int des_gpu_update_force(DesGpu *h);                                /* fields.cxx:609 */
+int des_gpu_update_velocity(DesGpu *h, double dt);                  /* fields.cxx:725 */
+int des_gpu_apply_vbcs(DesGpu *h, double time);                     /* bc.cxx:227 */
+int des_gpu_update_mesh(DesGpu *h, double dt);                      /* dynearthsol.cxx:448 */
+int des_gpu_compute_volume(DesGpu *h);                              /* geometry.cxx:170 */
+int des_gpu_compute_mass(DesGpu *h);                                /* geometry.cxx:1743 */
+int des_gpu_rotate_stress(DesGpu *h, double dt);                    /* fields.cxx:827 */
+int des_gpu_residual_force(DesGpu *h, double *l2);                  /* fields.cxx:700 */
+
+/* ---- instrumentation ----------------------------------------------------------------- */
+/* kernels launched by this handle since create (bench.py's gpu_launches) */
+long long des_gpu_launch_count(const DesGpu *h);
+/* cumulative device time (ms, CUDA events on the launching stream) of the kernel class
+ * `which` (0..DES_NKCLASS-1) and its launch count, when timing is enabled */
+#define DES_NKCLASS 16
+int des_gpu_enable_kernel_timing(DesGpu *h, int on);
+int des_gpu_kernel_time(DesGpu *h, int which, double *ms, long long *launches, const char **name);
+/* raw device pointer of a named internal array (for zero-copy harnesses that keep
+ * inputs resident in HBM); NULL if unknown */
+void *des_gpu_device_ptr(DesGpu *h, const char *name);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DES_GPU_H */

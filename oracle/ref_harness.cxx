@@ -12,6 +12,8 @@
 // dynearthsol.cxx with `main` renamed on the command line).  Only the call ORDER of one
 // time step is repeated (dynearthsol.cxx:768-894), minus output/remesh/monitor calls.
 #include <cstring>
+#include <cstdlib>
+#include <new>
 #include <cstdio>
 #include <string>
 #include <vector>
@@ -40,7 +42,7 @@ namespace {
 Param *g_param = nullptr;
 Variables *g_var = nullptr;
 
-struct View { void *p; size_t nbytes; };
+struct View { bool found; void *p; size_t nbytes; };
 
 // Flatten vector<vector<int>> elemmarkers into [nelem*nmat] (row = element).
 std::vector<int> g_flat_markers;
@@ -49,8 +51,8 @@ std::vector<int> g_flat_pairs;
 View lookup(const std::string &n)
 {
     Variables &v = *g_var;
-#define DV(name, ptr) if (n == name) return View{ (ptr)->data(), (ptr)->size() * sizeof((*(ptr))[0]) }
-#define A2(name, ptr) if (n == name) return View{ (ptr)->data(), size_t((ptr)->num_elements()) * sizeof(*(ptr)->data()) }
+#define DV(name, ptr) if (n == name) return View{ true, (ptr)->data(), (ptr)->size() * sizeof((*(ptr))[0]) }
+#define A2(name, ptr) if (n == name) return View{ true, (ptr)->data(), size_t((ptr)->num_elements()) * sizeof(*(ptr)->data()) }
     A2("coord", v.coord); A2("coord0", v.coord0); A2("vel", v.vel); A2("force", v.force);
     A2("force_residual", v.force_residual);
     A2("connectivity", v.connectivity);
@@ -65,34 +67,34 @@ View lookup(const std::string &n)
     DV("viscosity", v.viscosity); DV("ntmp", v.ntmp); DV("etmp", v.etmp);
     DV("radiogenic_source", v.radiogenic_source);
     DV("bcflag", v.bcflag);
-    if (n == "support_arr") return View{ v.support.arr_data.data(), v.support.arr_data.size()*sizeof(int) };
-    if (n == "support_idx") return View{ v.support.idx_data.data(), v.support.idx_data.size()*sizeof(int) };
-    if (n == "support_lidx") return View{ v.support.lidx_data.data(), v.support.lidx_data.size()*sizeof(int) };
+    if (n == "support_arr") return View{ true, v.support.arr_data.data(), v.support.arr_data.size()*sizeof(int) };
+    if (n == "support_idx") return View{ true, v.support.idx_data.data(), v.support.idx_data.size()*sizeof(int) };
+    if (n == "support_lidx") return View{ true, v.support.lidx_data.data(), v.support.lidx_data.size()*sizeof(int) };
     DV("top_elems", v.top_elems);
     DV("top_nodes", v.surfinfo.top_nodes);
     DV("dh", v.surfinfo.dh); DV("dhacc", v.surfinfo.dhacc); DV("edvacc_surf", v.surfinfo.edvacc_surf);
-    if (n == "support_surf_arr") return View{ v.surfinfo.support_surf.arr_data.data(), v.surfinfo.support_surf.arr_data.size()*sizeof(int) };
-    if (n == "support_surf_idx") return View{ v.surfinfo.support_surf.idx_data.data(), v.surfinfo.support_surf.idx_data.size()*sizeof(int) };
+    if (n == "support_surf_arr") return View{ true, v.surfinfo.support_surf.arr_data.data(), v.surfinfo.support_surf.arr_data.size()*sizeof(int) };
+    if (n == "support_surf_idx") return View{ true, v.surfinfo.support_surf.idx_data.data(), v.surfinfo.support_surf.idx_data.size()*sizeof(int) };
     A2("elem_and_nodes", v.surfinfo.elem_and_nodes);
     A2("connectivity_surface", v.connectivity_surface);
-    if (n == "edge_vec") return View{ v.edge_vec.data(), v.edge_vec.size()*sizeof(double) };
-    if (n == "edge_slot") return View{ v.edge_slot, sizeof(v.edge_slot) };
-    if (n == "vbc_types") return View{ v.vbc_types, sizeof(v.vbc_types) };
-    if (n == "vbc_values") return View{ v.vbc_values, sizeof(v.vbc_values) };
-    if (n == "stress_bc_types") return View{ v.stress_bc_types, sizeof(v.stress_bc_types) };
-    if (n == "stress_bc_values") return View{ v.stress_bc_values, sizeof(v.stress_bc_values) };
+    if (n == "edge_vec") return View{ true, v.edge_vec.data(), v.edge_vec.size()*sizeof(double) };
+    if (n == "edge_slot") return View{ true, v.edge_slot, sizeof(v.edge_slot) };
+    if (n == "vbc_types") return View{ true, v.vbc_types, sizeof(v.vbc_types) };
+    if (n == "vbc_values") return View{ true, v.vbc_values, sizeof(v.vbc_values) };
+    if (n == "stress_bc_types") return View{ true, v.stress_bc_types, sizeof(v.stress_bc_types) };
+    if (n == "stress_bc_values") return View{ true, v.stress_bc_values, sizeof(v.stress_bc_values) };
     if (n == "elemmarkers") {
         const int nmat = g_param->mat.nmat;
         g_flat_markers.resize(size_t(v.nelem) * nmat);
         for (int e = 0; e < v.nelem; ++e)
             for (int m = 0; m < nmat; ++m)
                 g_flat_markers[size_t(e)*nmat + m] = (*v.elemmarkers)[e][m];
-        return View{ g_flat_markers.data(), g_flat_markers.size()*sizeof(int) };
+        return View{ true, g_flat_markers.data(), g_flat_markers.size()*sizeof(int) };
     }
     for (int i = 0; i < nbdrytypes; ++i) {
         char b[32];
         std::snprintf(b, sizeof b, "bnodes%d", i);
-        if (n == b) return View{ v.bnodes[i]->data(), v.bnodes[i]->size()*sizeof(int) };
+        if (n == b) return View{ true, v.bnodes[i]->data(), v.bnodes[i]->size()*sizeof(int) };
         std::snprintf(b, sizeof b, "bfacets%d", i);
         if (n == b) {   // (elem, facet) pairs flattened
             g_flat_pairs.resize(v.bfacets[i]->size()*2);
@@ -100,12 +102,12 @@ View lookup(const std::string &n)
                 g_flat_pairs[2*k]   = (*v.bfacets[i])[k].first;
                 g_flat_pairs[2*k+1] = (*v.bfacets[i])[k].second;
             }
-            return View{ g_flat_pairs.data(), g_flat_pairs.size()*sizeof(int) };
+            return View{ true, g_flat_pairs.data(), g_flat_pairs.size()*sizeof(int) };
         }
     }
 #undef DV
 #undef A2
-    return View{ nullptr, 0 };
+    return View{ false, nullptr, 0 };
 }
 
 double *scalar_ptr(const std::string &n)
@@ -136,6 +138,11 @@ double *scalar_ptr(const std::string &n)
     if (n == "elastic_foundation_constant") return &p.bc.elastic_foundation_constant;
     if (n == "characteristic_speed") return &p.control.characteristic_speed;
     if (n == "fixed_dt") return &p.control.fixed_dt;
+    if (n == "vbc_val_x0_l") return &p.bc.vbc_val_x0_l;
+    if (n == "vbc_val_x1_l") return &p.bc.vbc_val_x1_l;
+    if (n == "vbc_val_y0_l") return &p.bc.vbc_val_y0_l;
+    if (n == "vbc_val_y1_l") return &p.bc.vbc_val_y1_l;
+    if (n == "vbc_val_z1_loading_period") return &v.vbc_val_z1_loading_period;
     return nullptr;
 }
 
@@ -241,9 +248,11 @@ extern "C" {
 int desref_init(const char *cfg_path)
 {
     if (g_param) return 1;  // one model per process (the reference keeps static state)
-    g_param = new Param;
+    // main() keeps `Param` on a fresh stack and `static Variables var` in zero-initialised
+    // storage (dynearthsol.cxx:616,627); give both the same all-zero start here.
+    g_param = new (std::calloc(1, sizeof(Param))) Param();
     get_input_parameters(cfg_path, *g_param);
-    g_var = new Variables;
+    g_var = new (std::calloc(1, sizeof(Variables))) Variables;
     init_var(*g_param, *g_var);
     g_var->output = new Output(*g_param, g_var->func_time.start_time, 0);
     init(*g_param, *g_var);
@@ -251,14 +260,13 @@ int desref_init(const char *cfg_path)
     return 0;
 }
 
-long desref_nbytes(const char *name) { View w = lookup(name); return w.p ? long(w.nbytes) : -1; }
+long desref_nbytes(const char *name) { View w = lookup(name); return w.found ? long(w.nbytes) : -1; }
 
 int desref_get(const char *name, void *out, long nbytes)
 {
     View w = lookup(name);
-    if (!w.p && w.nbytes == 0 && nbytes == 0) return 0;
-    if (!w.p || long(w.nbytes) != nbytes) return -1;
-    std::memcpy(out, w.p, w.nbytes);
+    if (!w.found || long(w.nbytes) != nbytes) return -1;
+    if (w.nbytes) std::memcpy(out, w.p, w.nbytes);
     return 0;
 }
 

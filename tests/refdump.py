@@ -1,0 +1,120 @@
+"""Run the UNMODIFIED reference (oracle/_ref/libdesref.so) on a cfg and dump inputs, per-function
+outputs of the first step and whole-step states to an .npz.  This is the script that generated
+tests/golden/*.npz; on a box where libdesref.so is present the GPU parity tests call it live.
+
+usage: python tests/refdump.py CFG OUT.npz [--steps 1,20] [--set name=int ...]
+"""
+import argparse
+import os
+import sys
+import tempfile
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from refharness import Ref  # noqa: E402
+
+MESH_ARRAYS = ["connectivity", "bcflag", "support_idx", "support_arr", "support_lidx", "bnormals",
+               "edge_vec", "edge_slot", "top_elems", "top_nodes", "support_surf_idx",
+               "support_surf_arr", "elem_and_nodes", "connectivity_surface", "vbc_types",
+               "vbc_values", "stress_bc_types"] + \
+              ["bfacets%d" % i for i in range(10)] + ["bnodes%d" % i for i in range(10)]
+STATE_ARRAYS = ["coord", "vel", "coord0", "temperature", "stress", "strain", "strain_rate",
+                "plstrain", "delta_plstrain", "volume", "volume_old", "viscosity", "dpressure",
+                "edvoldt", "radiogenic_source", "force", "volume_n", "mass", "tmass", "ntmp",
+                "dhacc", "edvacc_surf"]
+SCALARS = ["dt", "time", "compensation_pressure", "max_vbc_val", "gravity", "inertial_scaling",
+           "damping_factor", "dt_fraction", "surface_temperature", "winkler_delta_rho", "zlength",
+           "surf_base_level", "sea_water_density", "visc_min", "visc_max", "tension_max",
+           "therm_diff_max", "elastic_foundation_constant", "characteristic_speed", "fixed_dt",
+           "surf_diff", "vbc_val_x0_l", "vbc_val_x1_l", "vbc_val_y0_l", "vbc_val_y1_l",
+           "vbc_val_z1_loading_period", "max_surf_vel"]
+INTS = ["nnode", "nelem", "nmat", "rheol_type", "mattype_ref", "damping_option", "is_quasi_static",
+        "has_thermal_diffusion", "is_using_mixed_stress", "surface_process_option",
+        "ref_pressure_option", "has_moving_mesh", "has_winkler_foundation", "has_water_loading",
+        "has_elastic_foundation", "has_body_force_adjustment", "ntop", "etop", "ntop_elems"]
+MATV = ["rho0", "alpha", "bulk_modulus", "shear_modulus", "visc_exponent", "visc_coefficient",
+        "visc_activation_energy", "visc_activation_volume", "heat_capacity", "therm_cond", "pls0",
+        "pls1", "cohesion0", "cohesion1", "friction_angle0", "friction_angle1", "dilation_angle0",
+        "dilation_angle1", "porosity"]
+
+# the reference's step, one call at a time (dynearthsol.cxx:776-876), and what each call writes
+STEP_CALLS = [
+    ("update_temperature", ["temperature"]),
+    ("update_strain_rate", ["strain_rate"]),
+    ("compute_dvoldt", ["ntmp"]),
+    ("compute_edvoldt", ["edvoldt"]),
+    ("update_stress", ["stress", "strain", "strain_rate", "plstrain", "delta_plstrain",
+                       "dpressure", "viscosity"]),
+    ("NMD_stress", ["stress", "ntmp"]),
+    ("update_force", ["force"]),
+    ("update_velocity", ["vel"]),
+    ("apply_vbcs", ["vel"]),
+    ("update_mesh", ["coord", "volume", "volume_old", "volume_n", "mass", "tmass", "stress",
+                     "strain", "strain_rate", "plstrain", "dhacc", "edvacc_surf"]),
+    ("rotate_stress", ["stress", "strain"]),
+]
+
+
+def snapshot(r, out, prefix):
+    for a in STATE_ARRAYS:
+        out[prefix + a] = r.get(a)
+    out[prefix + "dt"] = np.float64(r.scalar("dt"))
+    out[prefix + "time"] = np.float64(r.scalar("time"))
+    out[prefix + "max_surf_vel"] = np.float64(r.scalar("max_surf_vel"))
+
+
+def dump(cfg, out_path, steps=(1,), sets=(), by_function=True):
+    with tempfile.TemporaryDirectory() as wd:
+        r = Ref(cfg, workdir=wd)
+        for name, val in sets:
+            r.set_int(name, val)
+        out = {}
+        for a in MESH_ARRAYS:
+            out["mesh_" + a] = r.get(a)
+        out["elemmarkers"] = r.get("elemmarkers")
+        for s in SCALARS:
+            out["p_" + s] = np.float64(r.scalar(s))
+        for s in INTS:
+            out["p_" + s] = np.int32(r.int(s))
+        for s in MATV:
+            out["p_" + s] = r.matvec(s)
+        snapshot(r, out, "s0_")
+        done = 0
+        if by_function:
+            # step 1, call by call (same order as desref_step / the driver)
+            r.set_int("steps", 1)
+            r.set_scalar("time", r.scalar("time") + r.scalar("dt"))
+            thermal = r.int("has_thermal_diffusion")
+            mixed = r.int("is_using_mixed_stress")
+            for fn, writes in STEP_CALLS:
+                if fn == "update_temperature" and not thermal:
+                    continue
+                if fn == "NMD_stress" and not mixed:
+                    continue
+                if fn == "rotate_stress" and not (r.int("rheol_type") & 1):
+                    continue
+                r.call(fn)
+                for a in writes:
+                    out["f_%s_%s" % (fn, a)] = r.get(a)
+            done = 1
+            if 1 in steps:
+                snapshot(r, out, "s1_")
+        for k in sorted(steps):
+            if k <= done:
+                continue
+            r.step(k - done)
+            done = k
+            snapshot(r, out, "s%d_" % k)
+        out["steps"] = np.asarray(sorted(steps), dtype=np.int32)
+        np.savez_compressed(out_path, **out)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("cfg")
+    ap.add_argument("out")
+    ap.add_argument("--steps", default="1")
+    ap.add_argument("--set", action="append", default=[])
+    a = ap.parse_args()
+    dump(a.cfg, a.out, steps=[int(s) for s in a.steps.split(",")],
+         sets=[(s.split("=")[0], int(s.split("=")[1])) for s in a.set])

@@ -1,0 +1,132 @@
+"""GPU parity: the CUDA path, called through the C-ABI, against the UNMODIFIED reference on
+the same inputs.  FP64 tolerance from BASELINE.json's north_star: 1e-10 relative after one
+step (measured as max|a-b| / max|b| per field, the compare.py measure)."""
+import numpy as np
+import pytest
+
+import refmodel
+from conftest import ref_dump
+from refdump import STEP_CALLS
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-10
+FIELDS = ["coord", "vel", "temperature", "stress", "strain", "strain_rate", "plstrain",
+          "delta_plstrain", "volume", "volume_old", "force", "volume_n", "mass", "tmass",
+          "dhacc", "edvacc_surf"]
+
+CASES = ["box-ep-tiny", "box-ep", "box-evp", "box-maxwell", "box-elastic-nomix"]
+
+
+def compare(got, d, prefix, fields, tol=TOL):
+    bad = []
+    report = []
+    for k in fields:
+        if prefix + k not in d:
+            continue
+        err = refmodel.rel_err(got[k], d[prefix + k])
+        exact = np.array_equal(got[k], d[prefix + k])
+        report.append("%s:%s" % (k, "bit-exact" if exact else "%.2e" % err))
+        if not err < tol:
+            bad.append((k, err))
+    assert not bad, "fields beyond %g: %s   [all: %s]" % (tol, bad, " ".join(report))
+    return report
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_one_step(case):
+    d = ref_dump(case, [1, 20])
+    g = refmodel.model_from_dump(d)
+    dt = float(d["s0_dt"])
+    g.step(dt, dt, 1)
+    got = g.download_state(*FIELDS)
+    compare(got, d, "s1_", FIELDS)
+    g.close()
+
+
+TWIN = {"update_temperature": ("update_temperature", "dt"), "update_strain_rate": ("update_strain_rate",),
+        "compute_dvoldt": ("compute_dvoldt",), "compute_edvoldt": ("compute_edvoldt",),
+        "update_stress": ("update_stress", "dt"), "NMD_stress": ("nmd_stress",),
+        "update_force": ("update_force",), "update_velocity": ("update_velocity", "dt"),
+        "apply_vbcs": ("apply_vbcs", "time"), "update_mesh": ("update_mesh", "dt"),
+        "rotate_stress": ("rotate_stress", "dt")}
+
+
+@pytest.mark.parametrize("case", ["box-ep-tiny", "box-evp"])
+def test_by_function(case):
+    """The fine-grained twins, in the reference's call order, each compared with what the
+    reference function wrote (per-function rows of SURVEY.md section 8a)."""
+    d = ref_dump(case, [1, 20])
+    g = refmodel.model_from_dump(d)
+    dt = float(d["s0_dt"])
+    vals = {"dt": dt, "time": dt}
+    for fn, writes in STEP_CALLS:
+        if ("f_%s_%s" % (fn, writes[0])) not in d:
+            continue
+        t = TWIN[fn]
+        g.call(t[0], *[vals[a] for a in t[1:]])
+        names = [w for w in writes if w in FIELDS + ["ntmp", "edvoldt", "dpressure", "viscosity"]]
+        got = g.download_state(*names)
+        compare(got, d, "f_%s_" % fn, names)
+    g.close()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_twenty_steps(case):
+    """20 steps with compute_dt every 10 (dynearthsol.cxx:881-894) -- dt itself is compared."""
+    d = ref_dump(case, [1, 20])
+    g = refmodel.model_from_dump(d)
+    dt, time, steps = g.run(20, float(d["s0_dt"]))
+    assert abs(dt - float(d["s20_dt"])) <= 1e-12 * abs(dt), (dt, float(d["s20_dt"]))
+    got = g.download_state(*FIELDS)
+    compare(got, d, "s20_", FIELDS, tol=1e-9)
+    g.close()
+
+
+def test_plastic_yielding():
+    """Start from the reference's state at step 250, where ~480 of 2880 elements are on the
+    Mohr-Coulomb yield surface (eigen-decomposition, return mapping, rotation back), and
+    compare one and twenty steps later."""
+    d = ref_dump("box-ep", [250, 251, 270])
+    assert (d["s251_delta_plstrain"] > 0).sum() > 100
+    g = refmodel.model_from_dump(d, prefix="s250_")
+    dt = float(d["s250_dt"])
+    time = float(d["s250_time"])
+    g.step(dt, time + dt, 251)
+    got = g.download_state(*FIELDS)
+    compare(got, d, "s251_", FIELDS)
+    dt, time, steps = g.run(19, dt, time + dt, 251)
+    got = g.download_state(*FIELDS)
+    compare(got, d, "s270_", FIELDS, tol=1e-9)
+    g.close()
+
+
+def test_fused_equals_unfused():
+    """The deferred-tail schedule (tail(n-1) fused into head(n)) against flushing after
+    every step: bit-identical."""
+    d = ref_dump("box-ep", [1, 20])
+    dt = float(d["s0_dt"])
+    a = refmodel.model_from_dump(d)
+    b = refmodel.model_from_dump(d)
+    t = 0.0
+    for i in range(5):
+        t += dt
+        a.step(dt, t, i + 1)
+        b.step(dt, t, i + 1)
+        b.download_state("volume")      # forces the flush
+    ga, gb = a.download_state(*FIELDS), b.download_state(*FIELDS)
+    for k in FIELDS:
+        assert np.array_equal(ga[k], gb[k]), k
+    a.close(); b.close()
+
+
+def test_determinism():
+    d = ref_dump("box-ep", [1, 20])
+    outs = []
+    for _ in range(2):
+        g = refmodel.model_from_dump(d)
+        g.run(12, float(d["s0_dt"]))
+        outs.append(g.download_state(*FIELDS))
+        g.close()
+    for k in FIELDS:
+        assert np.array_equal(outs[0][k], outs[1][k]), k
