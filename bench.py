@@ -1,0 +1,381 @@
+#!/usr/bin/env python
+"""bench.py -- 3D tet element-steps/s of the explicit time-step core on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--size 50M|...]
+
+Workload (BASELINE.json configs[2], the configuration the metric is quoted on): the
+150 x 100 x 100 km box on the reference's regular hex->5-tet generator at resolution
+526.3158 m (285x190x190 cells, 51 442 500 tets, 10 433 566 nodes), Mohr-Coulomb
+elasto-plastic + thermal diffusion + mixed stress + surface diffusion, physics of
+benchmarks-cores/test-3d.cfg; synthetic mesh and initial fields (dynearthsol_b200/boxmesh.py).
+A "step" is one explicit time step (dynearthsol.cxx:768-894), compute_dt every 10 steps.
+
+value      device-resident: K steps timed with CUDA events on the launching stream.
+e2e        through the C-ABI with host buffers: upload of the evolving state from pinned host
+           memory + K steps + download of the output fields, all inside the timed region.
+roofline   dominant kernel: algorithmic bytes per launch / its average
+           launch duration (CUDA events, separate instrumented pass) vs the measured HBM peak.
+cpu_baseline / --impl reference: the UNMODIFIED reference (oracle/_ref/libdesref.so) on the
+           host cores, same physics, on a bounded sample (a smaller box it can initialise).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SIZES = {  # name: (xlength, ylength, zlength, resolution)
+    "50M": (150e3, 100e3, 100e3, 526.3158),
+    "200M": (150e3, 100e3, 100e3, 333.3333),
+    "6M": (150e3, 100e3, 100e3, 1063.83),
+    "1M": (150e3, 100e3, 100e3, 1923.1),
+    "100k": (150e3, 100e3, 100e3, 4166.7),
+}
+
+# Algorithmic (compulsory) bytes per element-step, SURVEY.md section 8(d), apportioned to the
+# six kernels of the schedule; r = nnode / nelem.
+def alg_bytes(r):
+    return {
+        "elem_a": 16 + 4 + 8 + 8 + 48 + 64 + 56 * r,           # conn, markers, volume W, radiogenic, strain_rate W, record W; coord+vel+T
+        "node_a": 64 + 32 + 56 * r,                             # record R, CSR; T rw, mass/tmass/volume_n/ntmp W, bcflag, idx
+        "elem_b": 16 + 4 + 96 + 96 + 16 + 8 + 8 + 8 + 8 + 8 * r,  # conn, markers, stress rw, strain rw, plstrain rw, dpl W, volume R, dpressure W, dp*vol W; ntmp
+        "node_b": 8 + 32 + 20 * r,                              # dp*vol R, CSR; volume_n, ntmp W, idx
+        "elem_c": 8 + 96 + 8 * r,                               # dpressure R, force record W; ntmp
+        "node_c": 96 + 32 + 136 * r,                            # force record R, CSR; coord rw, vel rw, force W, mass, bcflag, idx
+    }
+
+
+KCLASS_KEY = {"elem_a": "elem_a(", "node_a": "node_a(", "elem_b": "elem_b(", "node_b": "node_b(",
+              "elem_c": "elem_c(", "node_c": "node_c("}
+
+
+def read_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks and throttle reasons during the timed region."""
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.idx = gpu_index
+        self.rows = []
+        self.stop_flag = False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + q,
+                                  "--format=csv,noheader,nounits", "-lms", "100"],
+                                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            return
+        while not self.stop_flag:
+            line = p.stdout.readline()
+            if not line:
+                break
+            self.rows.append([x.strip() for x in line.split(",")])
+        p.terminate()
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names)
+                   if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def build_problem(size, order="reference", verbose=False):
+    """Mesh, topology, parameters and initial state for one box (host, numpy)."""
+    from dynearthsol_b200 import boxmesh as bm, core
+    xl, yl, zl, res = SIZES[size]
+    nx, ny, nz = bm.grid_dims(xl, yl, zl, res)
+    t0 = time.time()
+    coord, conn, bcflag = bm.regular_box(xl, yl, zl, nx, ny, nz, order=order)
+    sup = core.host_build_support(coord.shape[1], conn)
+    mesh = bm.boundary_topology(coord, conn, bcflag, support=sup)
+    phys = dict(bm.TEST3D_PHYSICS)
+    phys["zlength"] = zl
+    state, comp_p = bm.initial_fields(coord, conn, rho0=phys["rho0"][0], bulk_modulus=phys["bulk_modulus"][0],
+                                      gravity=phys["gravity"], xlength=xl, ylength=yl, zlength=zl,
+                                      resolution=res, weakzone=bm.TEST3D_WEAKZONE)
+    if verbose:
+        print("# mesh %dx%dx%d cells, %d tets, %d nodes, host setup %.1f s"
+              % (nx - 1, ny - 1, nz - 1, conn.shape[1], coord.shape[1], time.time() - t0), file=sys.stderr)
+    return dict(mesh=mesh, phys=phys, state=state, comp_p=comp_p, cells=(nx - 1, ny - 1, nz - 1),
+                nelem=conn.shape[1], nnode=coord.shape[1])
+
+
+def make_model(prob, device):
+    """Device model initialised the way init() does (dynearthsol.cxx:159-228): upload, apply_vbcs,
+    compute_dt, compute_mass."""
+    from dynearthsol_b200 import core
+    g = core.DesGpu(core.make_param(**prob["phys"]), device)
+    g.upload_mesh(prob["mesh"])
+    g.upload_elemmarkers(np.full(prob["nelem"], 4, dtype=np.int32))
+    g.set_compensation_pressure(prob["comp_p"])
+    g.upload_state(**prob["state"])
+    g.call("apply_vbcs", 0.0)
+    g.call("compute_mass")
+    dt = g.compute_dt()[0]
+    return g, dt
+
+
+def pin(a):
+    """A pinned-host copy of a numpy array (torch is only the pinned allocator here)."""
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return t.numpy(), t
+
+
+EVOLVING = ["coord", "vel", "temperature", "stress", "strain", "strain_rate", "plstrain",
+            "volume", "volume_old"]
+OUTPUT = ["coord", "vel", "temperature", "stress", "strain", "strain_rate", "plstrain",
+          "delta_plstrain", "force", "volume"]                        # what Output::_write reads
+
+
+def run_steps(g, n, dt, t, s):
+    return g.run(n, dt, t, s)
+
+
+def reference_cpu(steps, warmup, sample="100k"):
+    """The unmodified reference on the host cores, same physics, on a box it can initialise.
+    Returns (element_steps_per_s, cores, description).  Runs in a subprocess (the reference
+    keeps process-wide state)."""
+    lib = os.path.join(ROOT, "oracle", "_ref", "libdesref.so")
+    if not os.path.exists(lib):
+        return None, 0, "oracle/_ref/libdesref.so absent"
+    xl, yl, zl, res = SIZES[sample]
+    cfg = CFG_TEMPLATE % dict(xl=xl, yl=yl, zl=zl, res=res)
+    import tempfile
+    wd = tempfile.mkdtemp(prefix="desref_")
+    open(os.path.join(wd, "sample.cfg"), "w").write(cfg)
+    code = (
+        "import sys, json; sys.path.insert(0, %r)\n"
+        "from refharness import Ref\n"
+        "r = Ref(%r, workdir=%r)\n"
+        "r.step(%d)\n"
+        "t = r.step(%d)\n"
+        "print('RESULT', json.dumps({'t': t, 'nelem': r.int('nelem'), 'nnode': r.int('nnode')}))\n"
+    ) % (os.path.join(ROOT, "tests"), os.path.join(wd, "sample.cfg"), wd, warmup, steps)
+    cores = os.cpu_count() or 1
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    for line in out.stdout.splitlines():
+        if line.startswith("RESULT"):
+            r = json.loads(line[7:])
+            rate = r["nelem"] * steps / r["t"]
+            return rate, cores, ("unmodified reference (g++ -O2 -fopenmp), %d-tet box, same physics, "
+                                 "%d steps after %d warm-up, %d OpenMP threads"
+                                 % (r["nelem"], steps, warmup, cores))
+    return None, cores, "reference run failed: " + out.stderr[-200:]
+
+
+CFG_TEMPLATE = """[sim]
+modelname = sample
+max_steps = 10
+output_step_interval = 100000000
+is_outputting_averaged_fields = no
+has_initial_checkpoint = no
+[mesh]
+meshing_option = 1
+meshing_elem_shape = 1
+xlength = %(xl)r
+ylength = %(yl)r
+zlength = %(zl)r
+resolution = %(res)r
+quality_check_step_interval = 100000
+remeshing_option = 0
+[control]
+surface_process_option = 1
+surface_diffusivity = 1e-6
+dt_fraction = 1.0
+inertial_scaling = 1e4
+[bc]
+vbc_x0 = 1
+vbc_x1 = 1
+vbc_val_x0 = -1e-9
+vbc_val_x1 = 1e-9
+vbc_y0 = 1
+vbc_y1 = 1
+vbc_val_y0 = 0
+vbc_val_y1 = 0
+has_water_loading = no
+surface_temperature = 273
+mantle_temperature = 273
+[ic]
+weakzone_option = 1
+weakzone_azimuth = 15
+weakzone_inclination = -60
+weakzone_halfwidth = 1.2
+weakzone_depth_min = 0.5
+weakzone_depth_max = 1.0
+weakzone_xcenter = 0.5
+weakzone_ycenter = 0.5
+weakzone_zcenter = 0
+weakzone_plstrain = 0.5
+[mat]
+rheology_type = elasto-plastic
+rho0 = [2700]
+alpha = [0]
+bulk_modulus = [50e9]
+shear_modulus = [30e9]
+pls0 = [0]
+pls1 = [0.5]
+cohesion0 = [4.4e7]
+cohesion1 = [4e6]
+friction_angle0 = [30]
+friction_angle1 = [30]
+min_viscosity = 1e24
+"""
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--size", default=None, help="box size key: " + ", ".join(SIZES))
+    ap.add_argument("--order", default="reference", choices=["reference", "morton"])
+    ap.add_argument("--cpu-sample", default="100k")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--verbose", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    W = max(a.warmup, 3)
+    K = a.steps
+    metric = "3D tet element-steps/sec"
+    unit = "element-steps/s"
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        size = a.size or "50M"
+        cpu_steps = max(1, min(K, 20))
+        rate, cores, desc = reference_cpu(cpu_steps, min(W, 3), a.cpu_sample)
+        xl, yl, zl, res = SIZES[size]
+        line = {"impl": "reference", "metric": metric, "value": rate, "unit": unit, "n_gpus": a.gpus,
+                "steps": K, "warmup": W, "ms_per_step": None, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "box %s: test-3d.cfg Mohr-Coulomb + thermal + NMD + surface diffusion" % size,
+                           "sample": desc},
+                "cpu_baseline": {"value": rate, "unit": unit, "cores": cores, "kind": "reference", "sample": desc},
+                "e2e": {"value": rate, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        if rate is None:
+            line["unavailable"] = desc
+        print(json.dumps(line))
+        return
+
+    if world > 1:
+        from dynearthsol_b200 import multigpu
+        return multigpu.bench_main(a, rank, world, local_rank, W, K)
+
+    size = a.size or "50M"
+    prob = build_problem(size, a.order, a.verbose)
+    E, N = prob["nelem"], prob["nnode"]
+    g, dt0 = make_model(prob, local_rank)
+
+    # ---- device-resident timing -------------------------------------------------------
+    dt, t, s = g.run(W, dt0)
+    g.sync()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = g.launch_count()
+    g.event_record(0)
+    dt, t, s = g.run(K, dt, t, s)
+    g.event_record(1)
+    ms = g.event_elapsed_ms(0, 1)
+    launches = g.launch_count() - launches0
+    sampler.stop_flag = True
+    value = E * K / (ms * 1e-3)
+
+    # ---- per-kernel pass (CUDA events around every launch) -----------------------------
+    g.enable_kernel_timing(True)
+    nk = min(K, 20)
+    dt, t, s = g.run(nk, dt, t, s)
+    kt = g.kernel_times()
+    g.enable_kernel_timing(False)
+    r = N / E
+    ab = alg_bytes(r)
+    peak, peak_src = read_peaks()
+    per_kernel = {}
+    tot_ms = sum(m for _, m, _ in kt)
+    for key, pat in KCLASS_KEY.items():
+        for name, m, n in kt:
+            if name.startswith(pat):
+                avg = m / n
+                per_kernel[key] = {"avg_ms": avg, "launches_per_step": n / nk, "share": m / tot_ms,
+                                   "alg_bytes_per_elem": ab[key],
+                                   "achieved_gbs": ab[key] * E / (avg * 1e-3) / 1e9}
+    dom = max(per_kernel, key=lambda k: per_kernel[k]["share"])
+    step_alg = sum(ab.values())
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["achieved_gbs"], "peak": peak,
+                "unit": "GB/s", "frac": per_kernel[dom]["achieved_gbs"] / peak, "traffic": None,
+                "peak_source": peak_src,
+                "step": {"alg_bytes_per_elem_step": step_alg, "achieved_gbs": value * step_alg / 1e9,
+                         "frac": value * step_alg / 1e9 / peak},
+                "kernels": per_kernel}
+
+    # ---- end to end through the C-ABI with pinned host buffers -------------------------
+    e2e = None
+    if not a.no_e2e:
+        got = g.download_state(*EVOLVING)
+        up, keep = {}, []
+        for k in EVOLVING:
+            up[k], tk = pin(got[k]); keep.append(tk)
+        down = {}
+        for k in OUTPUT:
+            down[k], tk = pin(np.empty_like(g.download_state(k)[k])); keep.append(tk)
+        h2d = sum(v.nbytes for v in up.values())
+        d2h = sum(v.nbytes for v in down.values())
+        g.sync()
+        t0 = time.perf_counter()
+        g.upload_state(**up)
+        dt, t, s = g.run(K, dt, t, s)
+        g.download_into(**down)
+        g.sync()
+        te = time.perf_counter() - t0
+        e2e = {"value": E * K / te, "unit": unit, "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
+               "seconds": te, "note": "upload evolving state (pinned) + K steps + download output fields"}
+
+    # ---- CPU baseline: the unmodified reference on the host cores -----------------------
+    cpu = None
+    if not a.no_cpu:
+        rate, cores, desc = reference_cpu(10, 2, a.cpu_sample)
+        cpu = {"value": rate, "unit": unit, "cores": cores, "kind": "reference", "sample": desc}
+
+    sampler.join(timeout=2)
+    line = {"metric": metric, "value": value, "unit": unit, "n_gpus": 1, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "box %s (%dx%dx%d cells, %d tets, %d nodes): test-3d.cfg Mohr-Coulomb "
+                                   "elasto-plastic + thermal + mixed stress + surface diffusion, "
+                                   "compute_dt every 10 steps" % ((size,) + prob["cells"] + (E, N)),
+                       "element_order": a.order, "l2": "working set (%.1f GB) >> 126 MB L2" % (E * 1160 / 1e9),
+                       "parallelism": "1 GPU"},
+            "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,
+            "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line))
+    g.close()
+
+
+if __name__ == "__main__":
+    main()

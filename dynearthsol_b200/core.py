@@ -111,7 +111,8 @@ ABI_SYMBOLS = [
     "des_gpu_update_mesh", "des_gpu_compute_volume", "des_gpu_compute_mass",
     "des_gpu_rotate_stress", "des_gpu_residual_force",
     "des_gpu_launch_count", "des_gpu_enable_kernel_timing", "des_gpu_kernel_time",
-    "des_gpu_device_ptr",
+    "des_gpu_device_ptr", "des_host_build_support", "des_abi_sizeof",
+    "des_gpu_event_record", "des_gpu_event_elapsed_ms",
 ]
 
 _lib = None
@@ -154,8 +155,32 @@ def load_library():
     L.des_gpu_kernel_time.argtypes = [H, C.c_int, _DP, C.POINTER(C.c_longlong), C.POINTER(C.c_char_p)]
     L.des_gpu_device_ptr.argtypes = [H, C.c_char_p]
     L.des_gpu_device_ptr.restype = C.c_void_p
+    L.des_gpu_event_record.argtypes = [H, C.c_int]
+    L.des_gpu_event_elapsed_ms.argtypes = [H, C.c_int, C.c_int, _DP]
+    L.des_host_build_support.argtypes = [C.c_int, C.c_int, _IP, _IP, _IP, _IP]
+    L.des_abi_sizeof.argtypes = [C.c_int]
+    for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions)):
+        if L.des_abi_sizeof(i) != C.sizeof(st):
+            raise ImportError("ABI mismatch: %s is %d bytes in the library, %d in core.py"
+                              % (st.__name__, L.des_abi_sizeof(i), C.sizeof(st)))
     _lib = L
     return L
+
+
+def host_build_support(nnode, conn):
+    """create_support (mesh.cxx:3287-3329) through the library's host helper: conn is the
+    SoA [4, nelem] int32 connectivity; returns (idx, arr, lidx)."""
+    L = load_library()
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    E = conn.size // 4
+    idx = np.empty(nnode + 1, dtype=np.int32)
+    arr = np.empty(4 * E, dtype=np.int32)
+    lidx = np.empty(4 * E, dtype=np.int32)
+    rc = L.des_host_build_support(nnode, E, _ptr(conn, C.c_int), _ptr(idx, C.c_int),
+                                  _ptr(arr, C.c_int), _ptr(lidx, C.c_int))
+    if rc:
+        raise DesError(rc, "des_host_build_support")
+    return idx, arr, lidx
 
 
 def make_param(**kw):
@@ -311,6 +336,16 @@ class DesGpu:
         self._ck(self.lib.des_gpu_download_state(self.h, C.byref(st)))
         return out
 
+    def download_into(self, **bufs):
+        """download_state into caller-owned (e.g. pinned) float64 arrays."""
+        st = DesState()
+        sizes = self._sizes()
+        for k, a in bufs.items():
+            if a.dtype != np.float64 or not a.flags["C_CONTIGUOUS"] or a.size != sizes[k]:
+                raise ValueError("%s: need a contiguous float64 array of %d" % (k, sizes[k]))
+            setattr(st, k, _ptr(a, C.c_double))
+        self._ck(self.lib.des_gpu_download_state(self.h, C.byref(st)))
+
     def upload_elemmarkers(self, em):
         a = np.ascontiguousarray(em, dtype=np.int32).reshape(-1)
         if a.size != self.nelem * self.param.nmat:
@@ -378,6 +413,14 @@ class DesGpu:
             if n.value:
                 out.append((nm.value.decode(), ms.value, n.value))
         return out
+
+    def event_record(self, slot):
+        self._ck(self.lib.des_gpu_event_record(self.h, slot))
+
+    def event_elapsed_ms(self, a, b):
+        ms = C.c_double()
+        self._ck(self.lib.des_gpu_event_elapsed_ms(self.h, a, b, C.byref(ms)))
+        return ms.value
 
     def device_ptr(self, name):
         return self.lib.des_gpu_device_ptr(self.h, name.encode())

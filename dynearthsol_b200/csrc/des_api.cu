@@ -52,6 +52,7 @@ struct DesGpu {
     std::vector<EvPair> ev_pool; size_t ev_used = 0;
     double kc_ms[DES_NKCLASS]; long long kc_n[DES_NKCLASS];
     std::unordered_map<std::string, void *> named;
+    cudaEvent_t user_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 namespace {
@@ -371,6 +372,7 @@ int des_gpu_destroy(DesGpu *h)
     if (h->stage) cudaFree(h->stage);
     if (h->dt_partials) cudaFree(h->dt_partials);
     for (auto &p : h->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto &e : h->user_ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return DES_OK;
@@ -708,6 +710,41 @@ double des_dt_from_reductions(const DesParam *p, const DesDtReductions *r, doubl
     return dt;
 }
 
+// ---- host-side topology helpers ------------------------------------------------------------
+int des_host_build_support(int nnode, int nelem, const int *conn, int *idx, int *arr, int *lidx)
+{
+    if (nnode <= 0 || nelem <= 0 || !conn || !idx || !arr || !lidx) return DES_E_ARG;
+    if (size_t(nelem) * 4 >= (size_t(1) << 31)) return DES_E_ARG;
+    const size_t E = nelem;
+    for (int n = 0; n <= nnode; ++n) idx[n] = 0;
+    for (size_t e = 0; e < E; ++e)
+        for (int i = 0; i < 4; ++i) {
+            const int n = conn[i * E + e];
+            if (n < 0 || n >= nnode) return DES_E_ARG;
+            idx[n + 1]++;
+        }
+    for (int n = 1; n <= nnode; ++n) idx[n] += idx[n - 1];
+    std::vector<int> cursor(idx, idx + nnode);
+    for (size_t e = 0; e < E; ++e)
+        for (int i = 0; i < 4; ++i) {
+            const int slot = cursor[conn[i * E + e]]++;
+            arr[slot] = int(e);
+            lidx[slot] = i;
+        }
+    return DES_OK;
+}
+
+int des_abi_sizeof(int which)
+{
+    switch (which) {
+    case 0: return int(sizeof(DesParam));
+    case 1: return int(sizeof(DesMesh));
+    case 2: return int(sizeof(DesState));
+    case 3: return int(sizeof(DesDtReductions));
+    default: return -1;
+    }
+}
+
 // ---- instrumentation --------------------------------------------------------------------
 long long des_gpu_launch_count(const DesGpu *h) { return h ? h->launches : 0; }
 
@@ -728,6 +765,25 @@ int des_gpu_kernel_time(DesGpu *h, int which, double *ms, long long *launches, c
     if (ms) *ms = h->kc_ms[which];
     if (launches) *launches = h->kc_n[which];
     if (name) *name = kclass_name[which];
+    return DES_OK;
+}
+
+int des_gpu_event_record(DesGpu *h, int slot)
+{
+    if (!h || slot < 0 || slot >= 8) return DES_E_ARG;
+    CK(cudaSetDevice(h->device));
+    if (!h->user_ev[slot]) CK(cudaEventCreate(&h->user_ev[slot]));
+    CK(cudaEventRecord(h->user_ev[slot], h->stream));
+    return DES_OK;
+}
+
+int des_gpu_event_elapsed_ms(DesGpu *h, int a, int b, double *ms)
+{
+    if (!h || !ms || a < 0 || a >= 8 || b < 0 || b >= 8 || !h->user_ev[a] || !h->user_ev[b]) return DES_E_ARG;
+    CK(cudaEventSynchronize(h->user_ev[b]));
+    float f = 0;
+    CK(cudaEventElapsedTime(&f, h->user_ev[a], h->user_ev[b]));
+    *ms = f;
     return DES_OK;
 }
 

@@ -202,6 +202,16 @@ int des_gpu_compute_mass(DesGpu *h);                                /* geometry.
 int des_gpu_rotate_stress(DesGpu *h, double dt);                    /* fields.cxx:827 */
 int des_gpu_residual_force(DesGpu *h, double *l2);                  /* fields.cxx:700 */
 
+/* ---- host-side topology helpers (pure integer work, no GPU) ---------------------------- */
+/* create_support (mesh.cxx:3287-3329): node -> (element, local node) CSR with ascending
+ * element ids per node.  connectivity is conn_t SoA [4*nelem]; idx [nnode+1], arr and lidx
+ * [4*nelem] are caller-allocated.  Bit-identical to the reference's arrays. */
+int des_host_build_support(int nnode, int nelem, const int *connectivity,
+                           int *idx, int *arr, int *lidx);
+/* sizeof() of the ABI structs as compiled, so a foreign-language binding can verify its
+ * own layout: which = 0 DesParam, 1 DesMesh, 2 DesState, 3 DesDtReductions */
+int des_abi_sizeof(int which);
+
 /* ---- instrumentation ----------------------------------------------------------------- */
 /* kernels launched by this handle since create (bench.py's gpu_launches) */
 long long des_gpu_launch_count(const DesGpu *h);
@@ -210,6 +220,10 @@ long long des_gpu_launch_count(const DesGpu *h);
 #define DES_NKCLASS 16
 int des_gpu_enable_kernel_timing(DesGpu *h, int on);
 int des_gpu_kernel_time(DesGpu *h, int which, double *ms, long long *launches, const char **name);
+/* CUDA events on the handle's stream (the stream the kernels are launched on): record
+ * slot 0..7, then elapsed milliseconds between two recorded slots (synchronises). */
+int des_gpu_event_record(DesGpu *h, int slot);
+int des_gpu_event_elapsed_ms(DesGpu *h, int slot_a, int slot_b, double *ms);
 /* raw device pointer of a named internal array (for zero-copy harnesses that keep
  * inputs resident in HBM); NULL if unknown */
 void *des_gpu_device_ptr(DesGpu *h, const char *name);
