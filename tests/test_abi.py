@@ -1,0 +1,150 @@
+"""CPU checks of the drop-in boundary: libdes_b200.so loads, exports every symbol that
+include/des_gpu.h declares, agrees with the ctypes mirror on struct layout, refuses to run
+without a device (no CPU fallback), and its host-side integer/scalar helpers reproduce the
+reference's arrays from the committed golden fixture (tests/golden, made by tests/refdump.py
+from the unmodified reference)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, HERE, have_gpu
+from dynearthsol_b200 import core, boxmesh
+
+HEADER = os.path.join(ROOT, "include", "des_gpu.h")
+GOLDEN = os.path.join(HERE, "golden", "box-ep-tiny.npz")
+
+
+def header_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(des_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported():
+    L = core.load_library()
+    names = header_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(L, n), "libdes_b200.so does not export %s" % n
+    # the python mirror lists the same set
+    assert sorted(core.ABI_SYMBOLS) == names
+
+
+def test_struct_sizes_match():
+    L = core.load_library()
+    for i, st in enumerate((core.DesParam, core.DesMesh, core.DesState, core.DesDtReductions)):
+        assert L.des_abi_sizeof(i) == C.sizeof(st)
+    assert L.des_abi_sizeof(99) == -1
+
+
+def test_no_cpu_fallback():
+    """Without a CUDA device the product path must fail loudly (DES_E_NODEVICE)."""
+    if have_gpu():
+        pytest.skip("a GPU is present")
+    with pytest.raises(core.DesError) as ei:
+        core.DesGpu(core.make_param(), 0)
+    assert ei.value.code == 1
+
+
+def test_null_arguments_rejected():
+    L = core.load_library()
+    assert L.des_gpu_create(None, 0, None) == 3
+    assert L.des_gpu_step(None, 1.0, 0.0, 0) == 3
+    assert L.des_gpu_upload_mesh(None, None) == 3
+    assert L.des_gpu_destroy(None) == 0
+    assert L.des_host_build_support(0, 0, None, None, None, None) == 3
+
+
+def test_make_param_rejects_unknown_field():
+    with pytest.raises(TypeError):
+        core.make_param(not_a_field=1)
+
+
+def test_host_build_support_matches_reference():
+    """create_support (mesh.cxx:3287-3329): bit-identical idx/arr/lidx."""
+    d = np.load(GOLDEN)
+    N, E = int(d["p_nnode"]), int(d["p_nelem"])
+    idx, arr, lidx = core.host_build_support(N, d["mesh_connectivity"])
+    assert np.array_equal(idx, d["mesh_support_idx"])
+    assert np.array_equal(arr, d["mesh_support_arr"])
+    assert np.array_equal(lidx, d["mesh_support_lidx"])
+    # and the numpy builder used for the big synthetic boxes
+    idx2, arr2, lidx2 = boxmesh.build_support(N, d["mesh_connectivity"].reshape(4, E))
+    assert np.array_equal(idx2, idx) and np.array_equal(arr2, arr) and np.array_equal(lidx2, lidx)
+
+
+def test_host_build_support_rejects_bad_connectivity():
+    conn = np.array([[0], [1], [2], [7]], dtype=np.int32)      # node 7 out of range for nnode=4
+    with pytest.raises(core.DesError):
+        core.host_build_support(4, conn)
+
+
+def _dt_reductions_numpy(d, prefix):
+    """compute_dt's element loop (geometry.cxx:1511-1593) restated in numpy for the nmat=1 box."""
+    N, E = int(d["p_nnode"]), int(d["p_nelem"])
+    x = d[prefix + "coord"].reshape(3, N)
+    v = d[prefix + "vel"].reshape(3, N)
+    conn = d["mesh_connectivity"].reshape(4, E)
+    p = [x[:, conn[i]] for i in range(4)]
+
+    def area(a, b, c):
+        ab, ac = b - a, c - a
+        d0 = ab[1] * ac[2] - ab[2] * ac[1]
+        d1 = ab[2] * ac[0] - ab[0] * ac[2]
+        d2 = ab[0] * ac[1] - ab[1] * ac[0]
+        return np.sqrt(d0 * d0 + d1 * d1 + d2 * d2) / 2
+
+    maxa = np.maximum(np.maximum(area(p[0], p[1], p[2]), area(p[0], p[1], p[3])),
+                      np.maximum(area(p[2], p[3], p[0]), area(p[2], p[3], p[1])))
+    minh = 3 * d[prefix + "volume"] / maxa
+    ve = np.zeros((3, E))
+    for i in range(4):
+        ve += v[:, conn[i]] * 0.25
+    r = core.DesDtReductions()
+    shearm = float(d["p_shear_modulus"][0])
+    rho = float(d["p_rho0"][0])     # alpha = 0 in the fixture
+    r.minl = float(minh.min())
+    r.dt_maxwell = 0.5 * float(d["p_visc_min"]) / (1e-40 + shearm)
+    r.dt_diffusion = float((0.5 * minh * minh / float(d["p_therm_diff_max"])).min())
+    r.global_dt_min = float((minh / np.sqrt(shearm / rho) / 5.0).min())
+    r.global_max_vem = float(np.sqrt((ve * ve).sum(axis=0)).max())
+    r.max_surf_vel = float(d[prefix + "max_surf_vel"])
+    return r
+
+
+@pytest.mark.parametrize("prefix", ["s0_", "s10_"])
+def test_dt_from_reductions_matches_reference(prefix):
+    """Host scalar algebra of compute_dt (geometry.cxx:1597-1630) against the dt the reference
+    computed for the same state (dt is recomputed every 10 steps, dynearthsol.cxx:893)."""
+    import refmodel
+    d = np.load(GOLDEN)
+    L = core.load_library()
+    par = refmodel.param_from_dump(d)
+    r = _dt_reductions_numpy(d, prefix)
+    vmag = C.c_double()
+    dt = L.des_dt_from_reductions(C.byref(par), C.byref(r), C.byref(vmag))
+    ref = float(d[prefix + "dt"])
+    assert abs(dt - ref) <= 1e-14 * ref, (dt, ref)
+
+
+def test_golden_fixture_is_the_reference():
+    """When the reference library is present (this container; it also travels to the GPU box),
+    regenerate the fixture live and require the committed file to be bit-identical to it."""
+    from conftest import REFLIB, ref_dump
+    if not os.path.exists(REFLIB):
+        pytest.skip("oracle/_ref/libdesref.so absent")
+    live = ref_dump("box-ep-tiny", [1, 10])
+    gold = np.load(GOLDEN)
+    for k in gold.files:
+        assert k in live, k
+        a, b = live[k], gold[k]
+        if k == "mesh_bnormals":
+            # rows n0..n3 have no facets on a box; the reference leaves them uninitialised
+            a, b = a.reshape(3, 10)[:, :6], b.reshape(3, 10)[:, :6]
+        if k == "mesh_connectivity_surface":
+            # conn_t has 4 columns, the reference fills 3 (mesh.cxx:3249-3262)
+            a, b = a.reshape(4, -1)[:3], b.reshape(4, -1)[:3]
+        assert np.array_equal(a, b), "golden fixture differs from the live reference: " + k
