@@ -43,13 +43,18 @@ SIZES = {  # name: (xlength, ylength, zlength, resolution)
 # six kernels of the schedule; r = nnode / nelem.
 def alg_bytes(r):
     return {
-        "elem_a": 16 + 4 + 8 + 8 + 48 + 64 + 56 * r,           # conn, markers, volume W, radiogenic, strain_rate W, record W; coord+vel+T
+        "elem_a": 16 + 4 + 8 + 8 + 64 + 56 * r,                 # conn, markers, radiogenic, volume W, record W; coord+vel+T
         "node_a": 64 + 32 + 56 * r,                             # record R, CSR; T rw, mass/tmass/volume_n/ntmp W, bcflag, idx
-        "elem_b": 16 + 4 + 96 + 96 + 16 + 8 + 8 + 8 + 8 + 8 * r,  # conn, markers, stress rw, strain rw, plstrain rw, dpl W, volume R, dpressure W, dp*vol W; ntmp
+        "elem_b": 16 + 4 + 96 + 96 + 48 + 16 + 8 + 8 + 8 + 8 + 8 * r,  # conn, markers, stress rw, strain rw, strain_rate W, plstrain rw, dpl W, volume R, dpressure W, dp*vol W; ntmp
         "node_b": 8 + 32 + 20 * r,                              # dp*vol R, CSR; volume_n, ntmp W, idx
         "elem_c": 8 + 96 + 8 * r,                               # dpressure R, force record W; ntmp
         "node_c": 96 + 32 + 136 * r,                            # force record R, CSR; coord rw, vel rw, force W, mass, bcflag, idx
     }
+
+
+def alg_bytes_step(r):
+    """B_alg (EP + thermal + NMD, nmat=1) = 756 + 232 r."""
+    return 756.0 + 232.0 * r
 
 
 KCLASS_KEY = {"elem_a": "elem_a(", "node_a": "node_a(", "elem_b": "elem_b(", "node_b": "node_b(",
@@ -326,7 +331,7 @@ def main():
                                    "alg_bytes_per_elem": ab[key],
                                    "achieved_gbs": ab[key] * E / (avg * 1e-3) / 1e9}
     dom = max(per_kernel, key=lambda k: per_kernel[k]["share"])
-    step_alg = sum(ab.values())
+    step_alg = alg_bytes_step(r)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["achieved_gbs"], "peak": peak,
                 "unit": "GB/s", "frac": per_kernel[dom]["achieved_gbs"] / peak, "traffic": None,
                 "peak_source": peak_src,
@@ -369,7 +374,7 @@ def main():
             "config": {"workload": "box %s (%dx%dx%d cells, %d tets, %d nodes): test-3d.cfg Mohr-Coulomb "
                                    "elasto-plastic + thermal + mixed stress + surface diffusion, "
                                    "compute_dt every 10 steps" % ((size,) + prob["cells"] + (E, N)),
-                       "element_order": a.order, "l2": "working set (%.1f GB) >> 126 MB L2" % (E * 1160 / 1e9),
+                       "element_order": a.order, "schedule": os.environ.get("DES_SCHEDULE", "2"), "l2": "working set (%.1f GB) >> 126 MB L2" % (E * 1160 / 1e9),
                        "parallelism": "1 GPU"},
             "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu}

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libdes_b200.so")
+LIB_PATH = os.environ.get("DES_LIB") or os.path.join(_HERE, "csrc", "libdes_b200.so")   # DES_LIB: A/B builds
 
 DES_MAX_MAT = 16
 DES_NBDRY = 10

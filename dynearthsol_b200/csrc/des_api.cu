@@ -13,7 +13,7 @@
 #include <algorithm>
 #include <limits>
 
-#include "des_kernels.cuh"
+#include "des_kernels2.cuh"
 
 namespace {
 
@@ -43,6 +43,8 @@ struct DesGpu {
     double compensation_pressure = 0;
     double last_dt = 0;                 // dt of the last step (for max_surf_vel)
     bool surf_ran = false;
+    bool node_staged = false;           // DES_NODE_STAGED=1: shared-memory staged node gathers
+    int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
     long long launches = 0;
     // staging
     void *stage = nullptr; size_t stage_bytes = 0;
@@ -99,6 +101,14 @@ struct LaunchScope {
 
 #define LAUNCH(cls, kern, n, bs, ...) do { if ((n) > 0) { LaunchScope ls_(h, cls); auto kfn_ = kern; \
     kfn_<<<DES_GRID((n), (bs)), (bs), 0, h->stream>>>(__VA_ARGS__); } } while (0)
+
+// launch with an explicit grid and dynamic shared memory (the staged node gathers)
+#define LAUNCH_G(cls, kern, grid, bs, smem, ...) do { if ((grid) > 0) { LaunchScope ls_(h, cls); auto kfn_ = kern; \
+    kfn_<<<(grid), (bs), (smem), h->stream>>>(__VA_ARGS__); } } while (0)
+
+// kernel template<bool SINGLE, bool X>: SINGLE (one material) keeps marker counts in registers
+#define LAUNCH_M(cls, kern, X, n, bs, ...) do { if (h->hp.nmat == 1) LAUNCH(cls, (kern<true, X>), n, bs, __VA_ARGS__); \
+    else LAUNCH(cls, (kern<false, X>), n, bs, __VA_ARGS__); } while (0)
 
 template <class T>
 int dalloc(DesGpu *h, T **p, size_t n, const char *name = nullptr)
@@ -353,6 +363,8 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
     DesGpu *h = new DesGpu;
     h->device = device;
     h->hp = *param;
+    if (const char *sv = getenv("DES_NODE_STAGED")) h->node_staged = atoi(sv) != 0;
+    if (const char *sv = getenv("DES_SCHEDULE")) h->schedule = (atoi(sv) == 1) ? 1 : 2;
     memset(&h->D, 0, sizeof(h->D));
     memset(h->kc_ms, 0, sizeof(h->kc_ms));
     memset(h->kc_n, 0, sizeof(h->kc_n));
@@ -445,7 +457,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
       CK(cudaMemsetAsync(r, 0, sizeof(double) * E, h->stream)); }
     if ((rc = dalloc(h, &D.ca, size_t(E) * 8, "ca"))) return rc;
     if ((rc = dalloc(h, &D.etmp, E, "etmp"))) return rc;
-    if ((rc = dalloc(h, &D.fc, size_t(E) * 12, "fc"))) return rc;
+    if ((rc = dalloc(h, &D.fc, size_t(E) * DES_FC_STRIDE, "fc"))) return rc;
     CK(cudaMemsetAsync(D.strain_rate, 0, sizeof(double) * 6 * E, h->stream));
     CK(cudaMemsetAsync(D.strain, 0, sizeof(double) * 6 * E, h->stream));
     CK(cudaMemsetAsync(D.stress, 0, sizeof(double) * 6 * E, h->stream));
@@ -622,27 +634,78 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
     const int N = D.nnode, E = D.nelem;
     const int mm = h->hp.has_moving_mesh;
 
-    // E-A / N-A
+    const int hf = head_flags(h);
+    if (h->schedule == 1) {
+    // ---- schedule v1 (des_kernels.cuh): rotation in E-A, strain rate stored by E-A ----
     if (h->tail_pending) {
-        LAUNCH(KC_ELEM_A, (k_elem_a<true, true>), E, 256, h->P, D, h->dt_prev, tail_flags(h), head_flags(h));
-        if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, true>), N, 256, h->P, D, dt, head_flags(h));
-        else    LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, head_flags(h));
+        LAUNCH(KC_ELEM_A, (k_elem_a<true, true>), E, 256, h->P, D, h->dt_prev, tail_flags(h), hf);
+        if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, true>), N, 256, h->P, D, dt, hf);
+        else    LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
         h->tail_pending = false;
     }
     else {
-        LAUNCH(KC_ELEM_A, (k_elem_a<false, true>), E, 256, h->P, D, 0.0, 0, head_flags(h));
-        LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, head_flags(h));
+        LAUNCH(KC_ELEM_A, (k_elem_a<false, true>), E, 256, h->P, D, 0.0, 0, hf);
+        LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
     }
-    // E-B / N-B
     LAUNCH(KC_ELEM_B, k_elem_b, E, 128, h->P, D, dt, 0);
     if (h->hp.is_using_mixed_stress) LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
-    // E-C / N-C
     LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
-    if (h->hp.is_using_mixed_stress) LAUNCH(KC_ELEM_C, (k_elem_c<true>), E, 256, h->P, D);
-    else                             LAUNCH(KC_ELEM_C, (k_elem_c<false>), E, 256, h->P, D);
+    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
+    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
     int bc_z1 = h->hp.vbc_types[5];
     if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
     LAUNCH(KC_NODE_C, k_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
+    }
+    else {
+    // ---- schedule v2 (des_kernels2.cuh) -------------------------------------------------
+    const int ngrid = DES_GRID(N, DES_NODE_BLOCK);
+    const bool tail = h->tail_pending;
+    const bool tail_mass = tail && mm;
+    const bool rot = tail && (h->hp.rheol_type & DES_RH_ELASTIC);
+    const bool staged = h->node_staged;
+    // E-A / N-A
+    if (tail_mass) {
+        LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, 256, h->P, D, 3, hf);
+        if (staged) LAUNCH_G(KC_NODE_A, (k2_node_a<true, 4>), ngrid, DES_NODE_BLOCK,
+                             5 * 4 * DES_NODE_BLOCK * sizeof(double), h->P, D, dt, hf);
+        else LAUNCH(KC_NODE_A, (k3_node_a<true>), N, 256, h->P, D, dt, hf);
+    }
+    else {
+        LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, 256, h->P, D, 0, hf);
+        if (staged) LAUNCH_G(KC_NODE_A, (k2_node_a<false, 4>), ngrid, DES_NODE_BLOCK,
+                             2 * 4 * DES_NODE_BLOCK * sizeof(double), h->P, D, dt, hf);
+        else LAUNCH(KC_NODE_A, (k3_node_a<false>), N, 256, h->P, D, dt, hf);
+    }
+    h->tail_pending = false;
+    // E-B / N-B
+    {
+        const double dtr = rot ? h->dt_prev : 0.0;
+#define EB_CASE(S, R) switch (h->hp.rheol_type) { \
+        case DES_RH_ELASTIC: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_ELASTIC>), E, 128, h->P, D, dt, dtr); break; \
+        case DES_RH_MAXWELL: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_MAXWELL>), E, 128, h->P, D, dt, dtr); break; \
+        case DES_RH_EP:      LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EP>), E, 128, h->P, D, dt, dtr); break; \
+        default:             LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EVP>), E, 128, h->P, D, dt, dtr); break; }
+        const bool single = h->hp.nmat == 1;
+        if (single && rot) EB_CASE(true, true)
+        else if (single) EB_CASE(true, false)
+        else if (rot) EB_CASE(false, true)
+        else EB_CASE(false, false)
+#undef EB_CASE
+    }
+    if (h->hp.is_using_mixed_stress) {
+        if (staged) LAUNCH_G(KC_NODE_B, (k2_node_b<8>), ngrid, DES_NODE_BLOCK, 8 * DES_NODE_BLOCK * sizeof(double), D);
+        else LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
+    }
+    // E-C / N-C
+    LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
+    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
+    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
+    int bc_z1 = h->hp.vbc_types[5];
+    if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
+    if (staged) LAUNCH_G(KC_NODE_C, (k2_node_c<4>), ngrid, DES_NODE_BLOCK, 3 * 4 * DES_NODE_BLOCK * sizeof(double),
+                         h->P, D, dt, bc_z1, mm ? 15 : 7);
+    else LAUNCH(KC_NODE_C, k3_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
+    }
     // update_mesh remainder
     if (mm) {
         int rc = run_surface(h, dt, false);
@@ -660,11 +723,14 @@ int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out)
 {
     if (!h || !out) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
-    int rc = flush_tail(h);
-    if (rc) return rc;
     {
+        // the deferred end-of-step work does not have to be flushed for this: the only
+        // thing compute_dt reads from it is volume, which k_dt then evaluates itself
+        // (tet_volume of the current coordinates == what compute_volume will store)
+        const int fresh_volume = (h->tail_pending && h->hp.has_moving_mesh) ? 1 : 0;
         LaunchScope ls(h, KC_DT);
-        k_dt<<<h->dt_blocks, 256, 0, h->stream>>>(h->P, h->D, h->dt_partials);
+        if (h->hp.nmat == 1) k_dt<true><<<h->dt_blocks, 256, 0, h->stream>>>(h->P, h->D, h->dt_partials, fresh_volume);
+        else k_dt<false><<<h->dt_blocks, 256, 0, h->stream>>>(h->P, h->D, h->dt_partials, fresh_volume);
     }
     std::vector<DtPartial> part(h->dt_blocks);
     unsigned long long bits = 0;

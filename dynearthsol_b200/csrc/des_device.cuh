@@ -49,6 +49,28 @@ struct DevParams {
     double memo_angle[DES_MAX_MEMO], memo_sin[DES_MAX_MEMO], memo_tan[DES_MAX_MEMO];
 };
 
+// 256-bit global loads/stores (LDG.E.ENL2.256 / STG.E.ENL2.256 on sm_100a): a 32-byte node or
+// contribution record is ONE L1TEX wavefront per lane instead of two 128-bit halves.
+__device__ __forceinline__ double4 ld256_nc(const void *p)      // read-only in this kernel
+{
+    double4 r;
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ double4 ld256(const void *p)
+{
+    double4 r;
+    asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void st256(void *p, const double4 &r)
+{
+    asm volatile("st.global.v4.f64 [%4], {%0,%1,%2,%3};"
+                 :: "d"(r.x), "d"(r.y), "d"(r.z), "d"(r.w), "l"(p) : "memory");
+}
+
 // constants.hpp:75-79 (3D)
 __constant__ int c_node_of_facet[4][3] = {{1,2,3},{0,3,2},{0,1,3},{0,2,1}};
 
@@ -182,7 +204,7 @@ __device__ __forceinline__ void load_markers(const int *__restrict__ elemmarkers
 }
 
 // MatProps::rho, matprops.cxx:642-664 (does NOT skip absent materials)
-__device__ __forceinline__ double mat_rho(const DevParams &P, const Markers &mk,
+__device__ __forceinline__ double mat_rho(const DevParams &P, int nmat, const Markers &mk,
                                           double T0, double T1, double T2, double T3)
 {
     const double celsius0 = 273;
@@ -192,7 +214,7 @@ __device__ __forceinline__ double mat_rho(const DevParams &P, const Markers &mk,
     double TinCelsius = T - celsius0;
     double result = 0;
     int n = 0;
-    for (int m = 0; m < P.nmat; ++m) {
+    for (int m = 0; m < nmat; ++m) {
         result += P.rho0[m] * (1 - P.alpha[m] * TinCelsius) * mk.cnt[m];
         n += mk.cnt[m];
     }
@@ -201,7 +223,7 @@ __device__ __forceinline__ double mat_rho(const DevParams &P, const Markers &mk,
 
 // MatProps::visc, matprops.cxx:333-377.  `s` is the PRE-update stress, `edot` the
 // anti-locked strain rate of this step (rheology.cxx:786-799 runs before :877).
-__device__ __forceinline__ double mat_visc(const DevParams &P, const Markers &mk,
+__device__ __forceinline__ double mat_visc(const DevParams &P, int nmat, const Markers &mk,
                                            double T0, double T1, double T2, double T3,
                                            const double *s, const double *edot_t)
 {
@@ -214,7 +236,7 @@ __device__ __forceinline__ double mat_visc(const DevParams &P, const Markers &mk
     edot = fmax(edot, min_strain_rate);
     double result = 0;
     int n = 0;
-    for (int m = 0; m < P.nmat; ++m) {
+    for (int m = 0; m < nmat; ++m) {
         const int marker_count = mk.cnt[m];
         if (marker_count == 0) continue;
         double visc0 = 0.25 * pow(edot, P.visc_pow_edot[m]) * P.visc_coef_term[m]
@@ -243,13 +265,13 @@ __device__ __forceinline__ double memo_tan(const DevParams &P, double angle_deg)
 }
 
 // MatProps::plastic_weakening + plastic_props, matprops.cxx:380-418,589-606
-__device__ __forceinline__ void plastic_props(const DevParams &P, const Markers &mk, double pls,
+__device__ __forceinline__ void plastic_props(const DevParams &P, int nmat, const Markers &mk, double pls,
                                               double &amc, double &anphi, double &anpsi,
                                               double &hardn, double &ten_max)
 {
     double c = 0, f = 0, d = 0, h = 0;
     int n = 0;
-    for (int m = 0; m < P.nmat; ++m) {
+    for (int m = 0; m < nmat; ++m) {
         int k = mk.cnt[m];
         if (k == 0) continue;
         n += k;
@@ -586,12 +608,30 @@ __device__ __noinline__ void rh_plastic_return(double bulkm, double shearm, doub
 }
 
 // elasto_plastic (3D Mohr-Coulomb with tension cut-off), rheology.cxx:314-484
+//
+// The reference runs a Cardano eigenvalue PREFILTER (rheology.cxx:351-361) whose only effect
+// is to skip the accurate eigen-decomposition for elements that are clearly elastic; an
+// element the prefilter lets through and the accurate test (fs > 0 && ft < 0, :383) then
+// finds elastic comes out exactly like a skipped one (s = elastic trial, depls = 0).  The
+// outcome therefore only requires that no truly yielding element is skipped, and any
+// conservative test may run first.  QUICK test: with m = tr(s)/3 and a = 2 sqrt(J2/3) every
+// eigenvalue lies in [m - a, m + a], so fs >= (m - a) - (m + a) anphi + amc and
+// ft <= m + a - ten_max; elements beyond the reference's own 1e-2 band (widened to the
+// bounds' magnitudes) on both are skipped without any transcendental.  Everything else runs
+// the reference's Cardano prefilter and accurate path unchanged.
 __device__ __forceinline__ void rh_elasto_plastic(double bulkm, double shearm, double amc, double anphi,
                                                   double anpsi, double hardn, double ten_max,
                                                   const double *de, double &depls, double *s)
 {
     rh_elastic(bulkm, shearm, de, s);
     depls = 0;
+    {
+        const double m = (s[0] + s[1] + s[2]) / 3;
+        const double a = 2 * sqrt(second_invariant2(s) / 3);
+        const double big = fabs(m) + a;
+        const double bandq = 1e-2 * (big + anphi * big + fabs(amc));
+        if ((m - a) - (m + a) * anphi + amc > bandq && (m + a) - ten_max < -bandq) return;
+    }
     {   // eigenvalue-only prefilter, rheology.cxx:351-361 (band 1e-2)
         double pf[3];
         Sym3 A = { s[0], s[1], s[2], s[3], s[4], s[5] };

@@ -38,7 +38,7 @@ struct Dev {
     // element -> node contribution records
     double *ca;                 // [E][8] {tdiff0..3, tr(edot)*vol, m, tm, vol}
     double *etmp;               // [E]    dpressure*vol
-    double *fc;                 // [E][4][3] element forces, local node major
+    double *fc;                 // [E][4][DES_FC_STRIDE/4] element forces, local node major
     // stress boundary conditions (apply_stress_bcs)
     int nsbc_facets;
     const int *sbc_felem, *sbc_ffacet, *sbc_fbdry;  // [nsbc_facets]
@@ -60,6 +60,14 @@ struct Dev {
 
 #define DES_GRID(n, b) (((n) + (b) - 1) / (b))
 
+// Element-force record: DES_FC_STRIDE doubles per element, DES_FC_STRIDE/4 per local node.
+// 16 pads each node's {fx,fy,fz} to one aligned 32-byte sector, so the node gather is a
+// single 256-bit load (one L1TEX wavefront) at the price of 32 B more per element each way.
+#ifndef DES_FC_STRIDE
+#define DES_FC_STRIDE 12
+#endif
+#define DES_FC_OFF(ent) (size_t((ent) >> 2) * DES_FC_STRIDE + ((ent) & 3) * (DES_FC_STRIDE / 4))
+
 // ---------------------------------------------------------------------------------------
 // E-A
 // ---------------------------------------------------------------------------------------
@@ -78,6 +86,7 @@ k_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
     // head_flags: 1 T-diffusion contributions, 2 strain rate, 4 tr(edot)*vol
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= D.nelem) return;
+    const int nmat = P.nmat;
     const int E = D.nelem;
     const int4 c = D.conn[e];
     const double4 a0 = D.xT[c.x], a1 = D.xT[c.y], a2 = D.xT[c.z], a3 = D.xT[c.w];
@@ -98,8 +107,8 @@ k_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
     const double vz[4] = {v0.z, v1.z, v2.z, v3.z};
 
     Markers mk;
-    load_markers(D.elemmarkers, e, P.nmat, mk);
-    const double rho = mat_rho(P, mk, a0.w, a1.w, a2.w, a3.w);
+    load_markers(D.elemmarkers, e, nmat, mk);
+    const double rho = mat_rho(P, nmat, mk, a0.w, a1.w, a2.w, a3.w);
 
     double rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     rec[7] = vol;
@@ -107,10 +116,10 @@ k_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
     if (TAIL) {
         if (tail_flags & 2) {
             // compute_mass element loop, geometry.cxx:1794-1840
-            const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, P.nmat);
+            const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, nmat);
             double rho_m = P.is_quasi_static ? bulkm / (P.pseudo_speed * P.pseudo_speed) : rho;
             rec[5] = rho_m * vol / 4;
-            const double cp = arith_mean(P.heat_capacity, mk.cnt, P.nmat);
+            const double cp = arith_mean(P.heat_capacity, mk.cnt, nmat);
             rec[6] = rho * cp * vol / 4;
         }
         if (tail_flags & 4) {
@@ -136,7 +145,7 @@ k_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
     if (HEAD) {
         if (head_flags & 1) {
             // update_temperature element loop, fields.cxx:210-239
-            const double k = arith_mean(P.therm_cond, mk.cnt, P.nmat);
+            const double k = arith_mean(P.therm_cond, mk.cnt, nmat);
             const double kv = k * vol;
             const double rh = D.radiogenic[e] * vol * rho / 4;
             const double T[4] = {a0.w, a1.w, a2.w, a3.w};
@@ -224,6 +233,7 @@ k_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
     // edv_mode: 0 = edvoldt from ntmp (fused), 1 = same and store it, 2 = load D.edvoldt (twin)
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= D.nelem) return;
+    const int nmat = P.nmat;
     const int E = D.nelem;
     const int4 c = D.conn[e];
 
@@ -259,9 +269,9 @@ k_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
     for (int i = 0; i < 6; ++i) D.strain[size_t(i) * E + e] = es[i];
 
     Markers mk;
-    load_markers(D.elemmarkers, e, P.nmat, mk);
-    const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, P.nmat);
-    const double shearm = harm_mean(P.shear_modulus, mk.cnt, P.nmat);
+    load_markers(D.elemmarkers, e, nmat, mk);
+    const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, nmat);
+    const double shearm = harm_mean(P.shear_modulus, mk.cnt, nmat);
     const double vol = D.volume[e];
     double dpl = 0.;
 
@@ -270,7 +280,7 @@ k_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
         rh_elastic(bulkm, shearm, de, s);
         break;
     case DES_RH_MAXWELL: {
-        const double visc = mat_visc(P, mk, D.xT[c.x].w, D.xT[c.y].w, D.xT[c.z].w, D.xT[c.w].w, s, edot);
+        const double visc = mat_visc(P, nmat, mk, D.xT[c.x].w, D.xT[c.y].w, D.xT[c.z].w, D.xT[c.w].w, s, edot);
         D.viscosity[e] = visc;
         const double dv = vol / D.volume_old[e] - 1;
         rh_maxwell(bulkm, shearm, visc, dt, dv, de, s);
@@ -279,7 +289,7 @@ k_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
     case DES_RH_EP: {
         double depls = 0, amc, anphi, anpsi, hardn, ten_max;
         const double pls = D.plstrain[e];
-        plastic_props(P, mk, pls, amc, anphi, anpsi, hardn, ten_max);
+        plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
         rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, s);
         D.plstrain[e] = pls + depls;
         dpl = depls;
@@ -287,7 +297,7 @@ k_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
     }
     case DES_RH_EVP: {
         double depls = 0;
-        const double visc = mat_visc(P, mk, D.xT[c.x].w, D.xT[c.y].w, D.xT[c.z].w, D.xT[c.w].w, s, edot);
+        const double visc = mat_visc(P, nmat, mk, D.xT[c.x].w, D.xT[c.y].w, D.xT[c.z].w, D.xT[c.w].w, s, edot);
         D.viscosity[e] = visc;
         const double dv = vol / D.volume_old[e] - 1;
         double sv[6];
@@ -297,7 +307,7 @@ k_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
 
         double amc, anphi, anpsi, hardn, ten_max;
         const double pls = D.plstrain[e];
-        plastic_props(P, mk, pls, amc, anphi, anpsi, hardn, ten_max);
+        plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
         double sp[6];
         for (int i = 0; i < 6; ++i) sp[i] = s[i];
         rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, sp);
@@ -342,12 +352,14 @@ k_node_b(const __grid_constant__ Dev D)
 // E-C: third loop of NMD_stress (geometry.cxx:315-331) + update_force element loop
 // (fields.cxx:622-653)
 // ---------------------------------------------------------------------------------------
-template <bool MIXED>
+// SINGLE: one material (nmat == 1) -- the marker counts live in registers, not local memory
+template <bool SINGLE, bool MIXED>
 __global__ void __launch_bounds__(256)
 k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= D.nelem) return;
+    const int nmat = SINGLE ? 1 : P.nmat;
     const int E = D.nelem;
     const int4 c = D.conn[e];
     double s[6];
@@ -362,7 +374,7 @@ k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
         #pragma unroll
         for (int i = 0; i < 3; ++i) { s[i] += ddp; D.stress[size_t(i) * E + e] = s[i]; }
     }
-    const double4 a0 = D.xT[c.x], a1 = D.xT[c.y], a2 = D.xT[c.z], a3 = D.xT[c.w];
+    const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
     const double vol = D.volume[e];
     double sx[4], sy[4], sz[4];
     shape_fn(a0, a1, a2, a3, vol, sx, sy, sz);
@@ -370,12 +382,11 @@ k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
     double buoy = 0;
     if (P.gravity != 0) {
         Markers mk;
-        load_markers(D.elemmarkers, e, P.nmat, mk);
-        const double rho = mat_rho(P, mk, a0.w, a1.w, a2.w, a3.w);
-        const double phi = arith_mean(P.porosity, mk.cnt, P.nmat);
+        load_markers(D.elemmarkers, e, nmat, mk);
+        const double rho = mat_rho(P, nmat, mk, a0.w, a1.w, a2.w, a3.w);
+        const double phi = arith_mean(P.porosity, mk.cnt, nmat);
         buoy = (rho * (1 - phi) + 1000.0 * phi) * P.gravity / 4;
     }
-    double2 *out = reinterpret_cast<double2 *>(D.fc + size_t(e) * 12);
     double f[12];
     #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -383,8 +394,15 @@ k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
         f[i*3 + 1] = (s[3]*sx[i] + s[1]*sy[i] + s[5]*sz[i]) * vol;
         f[i*3 + 2] = (s[4]*sx[i] + s[5]*sy[i] + s[2]*sz[i] + buoy) * vol;
     }
+#if DES_FC_STRIDE == 16
+    double *out = D.fc + size_t(e) * 16;
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) st256(out + 4 * i, make_double4(f[i*3], f[i*3 + 1], f[i*3 + 2], 0.0));
+#else
+    double2 *out = reinterpret_cast<double2 *>(D.fc + size_t(e) * 12);
     #pragma unroll
     for (int i = 0; i < 6; ++i) out[i] = make_double2(f[2*i], f[2*i + 1]);
+#endif
 }
 
 // ---------------------------------------------------------------------------------------
@@ -395,6 +413,7 @@ k_sbc_facets(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
 {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= D.nsbc_facets) return;
+    const int nmat = P.nmat;
     const int e = D.sbc_felem[n], f = D.sbc_ffacet[n], ib = D.sbc_fbdry[n];
     const int4 c4 = D.conn[e];
     const int cn[4] = {c4.x, c4.y, c4.z, c4.w};
@@ -413,8 +432,8 @@ k_sbc_facets(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
     double p;
     if (ib == 4 && P.has_winkler_foundation) {
         Markers mk;
-        load_markers(D.elemmarkers, e, P.nmat, mk);
-        const double rho = mat_rho(P, mk, D.xT[cn[0]].w, D.xT[cn[1]].w, D.xT[cn[2]].w, D.xT[cn[3]].w);
+        load_markers(D.elemmarkers, e, nmat, mk);
+        const double rho = mat_rho(P, nmat, mk, D.xT[cn[0]].w, D.xT[cn[1]].w, D.xT[cn[2]].w, D.xT[cn[3]].w);
         p = compensation_pressure - (rho + P.winkler_delta_rho) * P.gravity * (zcenter + P.zlength);
     }
     else if (ib == 5 && P.has_water_loading) {
@@ -455,7 +474,7 @@ k_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
         const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
         for (int k = beg; k < end; ++k) {
             const int ent = D.sup_ent[k];
-            const double *tr = D.fc + size_t(ent >> 2) * 12 + (ent & 3) * 3;
+            const double *tr = D.fc + DES_FC_OFF(ent);
             f[0] -= tr[0]; f[1] -= tr[1]; f[2] -= tr[2];
         }
         if (flag & P.sbc_mask) {
@@ -616,9 +635,11 @@ __device__ __forceinline__ double warp_max(double v)
     return v;
 }
 
+template <bool SINGLE>
 __global__ void __launch_bounds__(256)
-k_dt(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, DtPartial *partials)
+k_dt(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, DtPartial *partials, int fresh_volume)
 {
+    const int nmat = SINGLE ? 1 : P.nmat;
     double minl = DBL_MAX, dtm = DBL_MAX, dtd = DBL_MAX, gmin = DBL_MAX, vem = 0.0;
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < D.nelem; e += gridDim.x * blockDim.x) {
         const int4 c = D.conn[e];
@@ -634,14 +655,15 @@ k_dt(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, DtParti
         vem = fmax(vem, max_vem);
         const double maxa = fmax(fmax(tri_area(a, b, cc), tri_area(a, b, d)),
                                  fmax(tri_area(cc, d, a), tri_area(cc, d, b)));
-        const double minh = 3 * D.volume[e] / maxa;
+        const double vol = fresh_volume ? tet_volume(a, b, cc, d) : D.volume[e];
+        const double minh = 3 * vol / maxa;
         Markers mk;
-        load_markers(D.elemmarkers, e, P.nmat, mk);
-        const double shearm = harm_mean(P.shear_modulus, mk.cnt, P.nmat);
+        load_markers(D.elemmarkers, e, nmat, mk);
+        const double shearm = harm_mean(P.shear_modulus, mk.cnt, nmat);
         dtm = fmin(dtm, 0.5 * P.visc_min / (1e-40 + shearm));
         if (P.has_thermal_diffusion) dtd = fmin(dtd, 0.5 * minh * minh / P.therm_diff_max);
         minl = fmin(minl, minh);
-        const double rho = mat_rho(P, mk, a.w, b.w, cc.w, d.w);
+        const double rho = mat_rho(P, nmat, mk, a.w, b.w, cc.w, d.w);
         gmin = fmin(gmin, minh / sqrt(shearm / rho) / 5.0);
     }
     __shared__ DtPartial sh[8];

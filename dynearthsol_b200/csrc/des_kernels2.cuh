@@ -1,0 +1,568 @@
+// Schedule v2 of the fused explicit step (sm_100a, FP64) -- see DESIGN.md section 4.
+//
+//   E-A  k2_elem_a<TAIL>      tail(n-1): volume, mass contributions
+//                             head(n)  : T-diffusion contributions, tr(edot)*vol
+//   N-A  k2_node_a<MASS>      staged CSR gather: volume_n/mass/tmass, T update, dvoldt
+//   E-B  k2_elem_b<ROT>       tail(n-1): Jaumann rotation of stress and strain (dt_prev)
+//                             head(n)  : strain rate, edvoldt, anti-locking, strain, rheology,
+//                                        plstrain, dpressure*vol
+//   N-B  k2_node_b            staged CSR gather: dp_nd
+//   E-C  k_elem_c<MIXED>      (des_kernels.cuh) NMD correction, element forces
+//   N-C  k2_node_c            staged CSR gather of forces, stress bcs, damping, v, vbc, x
+//
+// Differences from v1 (des_kernels.cuh, kept as the un-fused twins and the flush path):
+//  * strain rate and spin are computed where they are consumed (E-B), so strain_rate is
+//    written once per step and stress/strain cross HBM once per direction in E-B instead
+//    of once more for the rotation in E-A;
+//  * the node gathers stage their support entries through shared memory: a block's CSR
+//    range is contiguous, every thread issues CPT independent (entry -> record) loads per
+//    chunk, then each node sums ITS entries from shared memory in ascending element order
+//    (the reference's order, fields.cxx:659-676) -- memory-level parallelism no longer
+//    depends on one dependent chain per node, and fewer nodes in flight keep the
+//    element records L2-resident between their four readers.
+#pragma once
+#include "des_kernels.cuh"
+
+// ---------------------------------------------------------------------------------------
+// E-A (v2)
+// ---------------------------------------------------------------------------------------
+template <bool SINGLE, bool TAIL>
+__global__ void __launch_bounds__(256)
+k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int tail_flags, int head_flags)
+{
+    // tail_flags: 1 volume, 2 mass contributions;  head_flags: 1 T-diffusion, 4 tr(edot)*vol
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= D.nelem) return;
+    const int nmat = SINGLE ? 1 : P.nmat;
+    const int4 c = D.conn[e];
+    const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
+
+    double vol;
+    if (TAIL && (tail_flags & 1)) {
+        vol = tet_volume(a0, a1, a2, a3);       // compute_volume, geometry.cxx:180-197
+        D.volume[e] = vol;
+    }
+    else
+        vol = D.volume[e];
+
+    double sx[4], sy[4], sz[4];
+    shape_fn(a0, a1, a2, a3, vol, sx, sy, sz);
+
+    Markers mk;
+    load_markers(D.elemmarkers, e, nmat, mk);
+    const double rho = mat_rho(P, nmat, mk, a0.w, a1.w, a2.w, a3.w);
+
+    double rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    rec[7] = vol;
+    if (TAIL && (tail_flags & 2)) {
+        // compute_mass element loop, geometry.cxx:1794-1840
+        const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, nmat);
+        double rho_m = P.is_quasi_static ? bulkm / (P.pseudo_speed * P.pseudo_speed) : rho;
+        rec[5] = rho_m * vol / 4;
+        const double cp = arith_mean(P.heat_capacity, mk.cnt, nmat);
+        rec[6] = rho * cp * vol / 4;
+    }
+    if (head_flags & 1) {
+        // update_temperature element loop, fields.cxx:210-239
+        const double k = arith_mean(P.therm_cond, mk.cnt, nmat);
+        const double kv = k * vol;
+        const double rh = D.radiogenic[e] * vol * rho / 4;
+        const double T[4] = {a0.w, a1.w, a2.w, a3.w};
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            double diffusion = 0.;
+            #pragma unroll
+            for (int j = 0; j < 4; ++j)
+                diffusion += (sx[i] * sx[j] + sy[i] * sy[j] + sz[i] * sz[j]) * T[j];
+            rec[i] = diffusion * kv - rh;
+        }
+    }
+    if (head_flags & 4) {
+        // diagonal of update_strain_rate (fields.cxx:414-476) -> compute_dvoldt element
+        // loop (geometry.cxx:217-225)
+        const double4 v0 = ld256_nc(D.vv + c.x), v1 = ld256_nc(D.vv + c.y), v2 = ld256_nc(D.vv + c.z), v3 = ld256_nc(D.vv + c.w);
+        double s[3];
+        s[0] = 0; s[0] += v0.x * sx[0]; s[0] += v1.x * sx[1]; s[0] += v2.x * sx[2]; s[0] += v3.x * sx[3];
+        s[1] = 0; s[1] += v0.y * sy[0]; s[1] += v1.y * sy[1]; s[1] += v2.y * sy[2]; s[1] += v3.y * sy[3];
+        s[2] = 0; s[2] += v0.z * sz[0]; s[2] += v1.z * sz[1]; s[2] += v2.z * sz[2]; s[2] += v3.z * sz[3];
+        rec[4] = trace3(s) * vol;
+    }
+    double2 *r = reinterpret_cast<double2 *>(D.ca + size_t(e) * 8);
+    if (head_flags & 1) { r[0] = make_double2(rec[0], rec[1]); r[1] = make_double2(rec[2], rec[3]); }
+    if (TAIL) { r[2] = make_double2(rec[4], rec[5]); r[3] = make_double2(rec[6], rec[7]); }
+    else if (head_flags & 4) D.ca[size_t(e) * 8 + 4] = rec[4];
+}
+
+// ---------------------------------------------------------------------------------------
+// staged CSR gather
+// ---------------------------------------------------------------------------------------
+// A block owns NB = blockDim.x consecutive nodes, whose support entries are the contiguous
+// CSR range [K0, K1).  The range is walked in chunks of CPT*NB entries: every thread loads
+// CPT entries and their NV record values (all independent -> CPT*NV loads in flight per
+// thread) into shared memory (SoA, [NV][CHUNK]); after a barrier each node consumes the part
+// of its own range that lies in the chunk, in ascending entry order.
+#define DES_NODE_BLOCK 256
+
+// N-A: MASS == compute_mass node loop (geometry.cxx:1843-1864); head == update_temperature
+// node loop (fields.cxx:244-262) and compute_dvoldt node loop (geometry.cxx:231-238).
+template <bool MASS, int CPT>
+__global__ void __launch_bounds__(DES_NODE_BLOCK)
+k2_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int head_flags)
+{
+    constexpr int NB = DES_NODE_BLOCK, CHUNK = CPT * NB, NV = MASS ? 5 : 2;
+    extern __shared__ double sm[];          // [NV][CHUNK]
+    const int tid = threadIdx.x;
+    const int n0 = blockIdx.x * NB, n = n0 + tid, N = D.nnode;
+    const int K0 = D.sup_idx[n0], K1 = D.sup_idx[min(n0 + NB, N)];
+    int beg = 0, end = 0;
+    if (n < N) { beg = D.sup_idx[n]; end = D.sup_idx[n + 1]; }
+    double vn = 0, m = 0, tm = 0, tdot = 0, dvol = 0;
+    for (int kc = K0; kc < K1; kc += CHUNK) {
+        const int len = min(CHUNK, K1 - kc);
+        int ent[CPT];
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int i = tid + j * NB;
+            ent[j] = (i < len) ? D.sup_ent[kc + i] : -1;
+        }
+        double2 hi0[CPT], hi1[CPT]; double lo[CPT];
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            if (ent[j] >= 0) {
+                const double *r = D.ca + size_t(ent[j] >> 2) * 8;
+                lo[j] = r[ent[j] & 3];
+                hi0[j] = *reinterpret_cast<const double2 *>(r + 4);     // {tr(edot)*vol, m}
+                if (MASS) hi1[j] = *reinterpret_cast<const double2 *>(r + 6);   // {tm, vol}
+            }
+        }
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int i = tid + j * NB;
+            if (ent[j] >= 0) {
+                sm[i] = lo[j];
+                sm[CHUNK + i] = hi0[j].x;
+                if (MASS) { sm[2 * CHUNK + i] = hi0[j].y; sm[3 * CHUNK + i] = hi1[j].x; sm[4 * CHUNK + i] = hi1[j].y; }
+            }
+        }
+        __syncthreads();
+        const int a = max(beg, kc) - kc, b = min(end, kc + len) - kc;
+        for (int i = a; i < b; ++i) {
+            tdot += sm[i]; dvol += sm[CHUNK + i];
+            if (MASS) { m += sm[2 * CHUNK + i]; tm += sm[3 * CHUNK + i]; vn += sm[4 * CHUNK + i]; }
+        }
+        __syncthreads();
+    }
+    if (n >= N) return;
+    if (MASS) {
+        D.volume_n[n] = vn;
+        D.mass[n] = m;
+        if (!P.has_thermal_diffusion) tm = 0;   // geometry.cxx:1836-1837,1859-1860
+        D.tmass[n] = tm;
+    }
+    else {
+        vn = D.volume_n[n];
+        tm = D.tmass[n];
+    }
+    if (head_flags & 1) {
+        double T;
+        if (D.bcflag[n] & BOUNDZ1) T = P.surface_temperature;
+        else T = D.xT[n].w - dt * tdot / tm;
+        D.xT[n].w = T;
+    }
+    if (head_flags & 4) D.ntmp[n] = dvol / vn;
+}
+
+// N-B: NMD_stress node loop, geometry.cxx:301-309
+template <int CPT>
+__global__ void __launch_bounds__(DES_NODE_BLOCK)
+k2_node_b(const __grid_constant__ Dev D)
+{
+    constexpr int NB = DES_NODE_BLOCK, CHUNK = CPT * NB;
+    extern __shared__ double sm[];          // [CHUNK]
+    const int tid = threadIdx.x;
+    const int n0 = blockIdx.x * NB, n = n0 + tid, N = D.nnode;
+    const int K0 = D.sup_idx[n0], K1 = D.sup_idx[min(n0 + NB, N)];
+    int beg = 0, end = 0;
+    if (n < N) { beg = D.sup_idx[n]; end = D.sup_idx[n + 1]; }
+    double acc = 0;
+    for (int kc = K0; kc < K1; kc += CHUNK) {
+        const int len = min(CHUNK, K1 - kc);
+        int ent[CPT];
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int i = tid + j * NB;
+            ent[j] = (i < len) ? D.sup_ent[kc + i] : -1;
+        }
+        double v[CPT];
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) if (ent[j] >= 0) v[j] = D.etmp[ent[j] >> 2];
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) if (ent[j] >= 0) sm[tid + j * NB] = v[j];
+        __syncthreads();
+        const int a = max(beg, kc) - kc, b = min(end, kc + len) - kc;
+        for (int i = a; i < b; ++i) acc += sm[i];
+        __syncthreads();
+    }
+    if (n < N) D.ntmp[n] = acc / D.volume_n[n];
+}
+
+// N-C: update_force node loop (fields.cxx:658-676), apply_stress_bcs node loops
+// (bc.cxx:783-823), apply_damping (fields.cxx:483-579), update_velocity (:734-737),
+// apply_vbcs (bc.cxx:396-651), update_coordinate (fields.cxx:774-778).  mode as k_node_c;
+// bit 1 (update_force) is always set here.
+template <int CPT>
+__global__ void __launch_bounds__(DES_NODE_BLOCK)
+k2_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int bc_z1, int mode)
+{
+    constexpr int NB = DES_NODE_BLOCK, CHUNK = CPT * NB;
+    extern __shared__ double sm[];          // [3][CHUNK]
+    const int tid = threadIdx.x;
+    const int n0 = blockIdx.x * NB, n = n0 + tid, N = D.nnode;
+    const int K0 = D.sup_idx[n0], K1 = D.sup_idx[min(n0 + NB, N)];
+    int beg = 0, end = 0;
+    if (n < N) { beg = D.sup_idx[n]; end = D.sup_idx[n + 1]; }
+    double f[3] = {0, 0, 0};
+    for (int kc = K0; kc < K1; kc += CHUNK) {
+        const int len = min(CHUNK, K1 - kc);
+        int ent[CPT];
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int i = tid + j * NB;
+            ent[j] = (i < len) ? D.sup_ent[kc + i] : -1;
+        }
+        double t0[CPT], t1[CPT], t2[CPT];
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            if (ent[j] >= 0) {
+                const double *tr = D.fc + DES_FC_OFF(ent[j]);
+                t0[j] = tr[0]; t1[j] = tr[1]; t2[j] = tr[2];
+            }
+        }
+        #pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+            const int i = tid + j * NB;
+            if (ent[j] >= 0) { sm[i] = t0[j]; sm[CHUNK + i] = t1[j]; sm[2 * CHUNK + i] = t2[j]; }
+        }
+        __syncthreads();
+        const int a = max(beg, kc) - kc, b = min(end, kc + len) - kc;
+        for (int i = a; i < b; ++i) { f[0] -= sm[i]; f[1] -= sm[CHUNK + i]; f[2] -= sm[2 * CHUNK + i]; }
+        __syncthreads();
+    }
+    if (n >= N) return;
+    const unsigned flag = D.bcflag[n];
+    double4 x = D.xT[n];
+    const double4 v4 = D.vv[n];
+    double v[3] = {v4.x, v4.y, v4.z};
+    if (flag & P.sbc_mask) {
+        const int row = D.sbc_row[n];
+        if (row >= 0) {
+            for (int k = D.sbc_idx[row]; k < D.sbc_idx[row + 1]; ++k) {
+                const int se = D.sbc_ent[k];
+                const double *tr = D.sbc_ftr + size_t(se / 3) * 9 + (se % 3) * 3;
+                f[0] -= tr[0]; f[1] -= tr[1]; f[2] -= tr[2];
+            }
+        }
+    }
+    if (P.has_elastic_foundation && (flag & BOUNDZ0))
+        f[2] -= P.elastic_foundation_constant * (x.z - D.coord0[n].z);
+    #pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        f[j] = damp(P, f[j], v[j]);
+        D.force[size_t(j) * N + n] = f[j];
+    }
+    if (mode & 2) {
+        const double mass = D.mass[n];
+        #pragma unroll
+        for (int j = 0; j < 3; ++j) v[j] += dt * f[j] / mass;
+    }
+    if ((mode & 4) && (flag & BOUND_ANY)) vbc_node(P, flag, v, bc_z1, D.edge_slot, D.edge_vec);
+    if (mode & 6) D.vv[n] = make_double4(v[0], v[1], v[2], 0.0);
+    if (mode & 8) {
+        x.x += v[0] * dt; x.y += v[1] * dt; x.z += v[2] * dt;
+        D.xT[n] = x;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// E-B (v2): rotate_stress of the step that ended (fields.cxx:851-898) + update_strain_rate
+// (fields.cxx:414-476) + compute_edvoldt (geometry.cxx:263-272) + update_stress
+// (rheology.cxx:727-1026) + first loop of NMD_stress (geometry.cxx:293-295).
+// The coordinates, velocities and volume the rotation needs (end of step n-1) are the ones
+// the strain rate of step n needs, so one shape-function evaluation serves both.
+// ---------------------------------------------------------------------------------------
+template <bool SINGLE, bool ROT, int RHEOL>
+__global__ void __launch_bounds__(128)
+k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= D.nelem) return;
+    const int nmat = SINGLE ? 1 : P.nmat;
+    const int E = D.nelem;
+    const int4 c = D.conn[e];
+    const double vol = D.volume[e];
+    // the streaming (coalesced) loads are issued before the dependent gathers
+    double s[6], es[6];
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        s[i] = D.stress[size_t(i) * E + e];
+        es[i] = D.strain[size_t(i) * E + e];
+    }
+
+    double edot[6], w3 = 0, w4 = 0, w5 = 0;
+    double T0, T1, T2, T3;
+    double edvoldt;
+    {
+        const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
+        const double4 v0 = ld256_nc(D.vv + c.x), v1 = ld256_nc(D.vv + c.y), v2 = ld256_nc(D.vv + c.z), v3 = ld256_nc(D.vv + c.w);
+        {
+            double dj = 0;
+            dj += D.ntmp[c.x]; dj += D.ntmp[c.y]; dj += D.ntmp[c.z]; dj += D.ntmp[c.w];
+            edvoldt = dj / 4;
+        }
+        T0 = a0.w; T1 = a1.w; T2 = a2.w; T3 = a3.w;
+        double sx[4], sy[4], sz[4];
+        shape_fn(a0, a1, a2, a3, vol, sx, sy, sz);
+        const double vx[4] = {v0.x, v1.x, v2.x, v3.x};
+        const double vy[4] = {v0.y, v1.y, v2.y, v3.y};
+        const double vz[4] = {v0.z, v1.z, v2.z, v3.z};
+        if (ROT) {
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) w3 += 0.5 * (vx[i] * sy[i] - vy[i] * sx[i]);
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) w4 += 0.5 * (vx[i] * sz[i] - vz[i] * sx[i]);
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) w5 += 0.5 * (vy[i] * sz[i] - vz[i] * sy[i]);
+        }
+        #pragma unroll
+        for (int k = 0; k < 6; ++k) edot[k] = 0;
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) edot[0] += vx[i] * sx[i];
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) edot[1] += vy[i] * sy[i];
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) edot[2] += vz[i] * sz[i];
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) edot[3] += 0.5 * (vx[i] * sy[i] + vy[i] * sx[i]);
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) edot[4] += 0.5 * (vx[i] * sz[i] + vz[i] * sx[i]);
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) edot[5] += 0.5 * (vy[i] * sz[i] + vz[i] * sy[i]);
+    }
+
+    if (ROT) {
+        jaumann3(s, dt_rot, w3, w4, w5);
+        jaumann3(es, dt_rot, w3, w4, w5);
+    }
+    const double old_s = trace3(s);
+
+    // anti-mesh-locking correction, rheology.cxx:786-793
+    {
+        const double div = trace3(edot);
+        for (int i = 0; i < 3; ++i) edot[i] += (edvoldt - div) / 3;
+    }
+    double de[6];
+    for (int i = 0; i < 6; ++i) es[i] += edot[i] * dt;
+    for (int i = 0; i < 6; ++i) de[i] = edot[i] * dt;
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) D.strain_rate[size_t(i) * E + e] = edot[i];
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) D.strain[size_t(i) * E + e] = es[i];
+
+    Markers mk;
+    load_markers(D.elemmarkers, e, nmat, mk);
+    const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, nmat);
+    const double shearm = harm_mean(P.shear_modulus, mk.cnt, nmat);
+    double dpl = 0.;
+
+    switch (RHEOL) {
+    case DES_RH_ELASTIC:
+        rh_elastic(bulkm, shearm, de, s);
+        break;
+    case DES_RH_MAXWELL: {
+        const double visc = mat_visc(P, nmat, mk, T0, T1, T2, T3, s, edot);
+        D.viscosity[e] = visc;
+        const double dv = vol / D.volume_old[e] - 1;
+        rh_maxwell(bulkm, shearm, visc, dt, dv, de, s);
+        break;
+    }
+    case DES_RH_EP: {
+        double depls = 0, amc, anphi, anpsi, hardn, ten_max;
+        const double pls = D.plstrain[e];
+        plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
+        rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, s);
+        D.plstrain[e] = pls + depls;
+        dpl = depls;
+        break;
+    }
+    case DES_RH_EVP: {
+        double depls = 0;
+        const double visc = mat_visc(P, nmat, mk, T0, T1, T2, T3, s, edot);
+        D.viscosity[e] = visc;
+        const double dv = vol / D.volume_old[e] - 1;
+        double sv[6];
+        for (int i = 0; i < 6; ++i) sv[i] = s[i];
+        rh_maxwell(bulkm, shearm, visc, dt, dv, de, sv);
+        const double svII = second_invariant2(sv);
+
+        double amc, anphi, anpsi, hardn, ten_max;
+        const double pls = D.plstrain[e];
+        plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
+        double sp[6];
+        for (int i = 0; i < 6; ++i) sp[i] = s[i];
+        rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, sp);
+        const double spII = second_invariant2(sp);
+        if (svII < spII) {
+            for (int i = 0; i < 6; ++i) s[i] = sv[i];
+        }
+        else {
+            for (int i = 0; i < 6; ++i) s[i] = sp[i];
+            D.plstrain[e] = pls + depls;
+            dpl = depls;
+        }
+        break;
+    }
+    default: break;
+    }
+    D.delta_plstrain[e] = dpl;
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) D.stress[size_t(i) * E + e] = s[i];
+    if (P.is_using_mixed_stress) {
+        const double dp = trace3(s) - old_s;
+        D.dpressure[e] = dp;
+        D.etmp[e] = dp * vol;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// direct node gathers with wide loads (one thread per node, entries walked in ascending
+// element order, 4 entries' loads in flight per trip).  Per entry: N-A reads one 32-byte
+// sector {tr(edot)*vol, m, tm, vol} + one double; N-C reads one 32-byte sector {fx,fy,fz,-}
+// when DES_FC_STRIDE == 16.  The L1TEX wavefront count per entry -- what bounded the v1
+// gathers (l1tex 94 % busy, DRAM 28 %) -- drops from 5 to 2 (N-A) and from 3 to 1 (N-C).
+// ---------------------------------------------------------------------------------------
+template <bool MASS>
+__global__ void __launch_bounds__(256)
+k3_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int head_flags)
+{
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= D.nnode) return;
+    const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
+    double vn = 0, m = 0, tm = 0, tdot = 0, dvol = 0;
+    int k = beg;
+    for (; k + 4 <= end; k += 4) {
+        int ent[4]; double lo[4]; double4 hi[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) ent[j] = D.sup_ent[k + j];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double *r = D.ca + size_t(ent[j] >> 2) * 8;
+            lo[j] = r[ent[j] & 3];
+            hi[j] = ld256_nc(r + 4);
+        }
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            tdot += lo[j]; dvol += hi[j].x;
+            if (MASS) { m += hi[j].y; tm += hi[j].z; vn += hi[j].w; }
+        }
+    }
+    for (; k < end; ++k) {
+        const int ent = D.sup_ent[k];
+        const double *r = D.ca + size_t(ent >> 2) * 8;
+        const double lo = r[ent & 3];
+        const double4 hi = ld256_nc(r + 4);
+        tdot += lo; dvol += hi.x;
+        if (MASS) { m += hi.y; tm += hi.z; vn += hi.w; }
+    }
+    if (MASS) {
+        D.volume_n[n] = vn;
+        D.mass[n] = m;
+        if (!P.has_thermal_diffusion) tm = 0;   // geometry.cxx:1836-1837,1859-1860
+        D.tmass[n] = tm;
+    }
+    else {
+        vn = D.volume_n[n];
+        tm = D.tmass[n];
+    }
+    if (head_flags & 1) {
+        double T;
+        if (D.bcflag[n] & BOUNDZ1) T = P.surface_temperature;
+        else T = D.xT[n].w - dt * tdot / tm;
+        D.xT[n].w = T;
+    }
+    if (head_flags & 4) D.ntmp[n] = dvol / vn;
+}
+
+__global__ void __launch_bounds__(256)
+k3_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int bc_z1, int mode)
+{
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= D.nnode) return;
+    const int N = D.nnode;
+    const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
+    double f[3] = {0, 0, 0};
+    int k = beg;
+#if DES_FC_STRIDE == 16
+    for (; k + 4 <= end; k += 4) {
+        int ent[4]; double4 t[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) ent[j] = D.sup_ent[k + j];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) t[j] = ld256_nc(D.fc + DES_FC_OFF(ent[j]));
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) { f[0] -= t[j].x; f[1] -= t[j].y; f[2] -= t[j].z; }
+    }
+    for (; k < end; ++k) {
+        const double4 t = ld256_nc(D.fc + DES_FC_OFF(D.sup_ent[k]));
+        f[0] -= t.x; f[1] -= t.y; f[2] -= t.z;
+    }
+#else
+    for (; k + 4 <= end; k += 4) {
+        int ent[4]; double t0[4], t1[4], t2[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) ent[j] = D.sup_ent[k + j];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double *tr = D.fc + DES_FC_OFF(ent[j]);
+            t0[j] = tr[0]; t1[j] = tr[1]; t2[j] = tr[2];
+        }
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) { f[0] -= t0[j]; f[1] -= t1[j]; f[2] -= t2[j]; }
+    }
+    for (; k < end; ++k) {
+        const double *tr = D.fc + DES_FC_OFF(D.sup_ent[k]);
+        f[0] -= tr[0]; f[1] -= tr[1]; f[2] -= tr[2];
+    }
+#endif
+    const unsigned flag = D.bcflag[n];
+    double4 x = ld256(D.xT + n);
+    const double4 v4 = ld256(D.vv + n);
+    double v[3] = {v4.x, v4.y, v4.z};
+    if (flag & P.sbc_mask) {
+        const int row = D.sbc_row[n];
+        if (row >= 0) {
+            for (int q = D.sbc_idx[row]; q < D.sbc_idx[row + 1]; ++q) {
+                const int se = D.sbc_ent[q];
+                const double *tr = D.sbc_ftr + size_t(se / 3) * 9 + (se % 3) * 3;
+                f[0] -= tr[0]; f[1] -= tr[1]; f[2] -= tr[2];
+            }
+        }
+    }
+    if (P.has_elastic_foundation && (flag & BOUNDZ0))
+        f[2] -= P.elastic_foundation_constant * (x.z - D.coord0[n].z);
+    #pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        f[j] = damp(P, f[j], v[j]);
+        D.force[size_t(j) * N + n] = f[j];
+    }
+    if (mode & 2) {
+        const double mass = D.mass[n];
+        #pragma unroll
+        for (int j = 0; j < 3; ++j) v[j] += dt * f[j] / mass;
+    }
+    if ((mode & 4) && (flag & BOUND_ANY)) vbc_node(P, flag, v, bc_z1, D.edge_slot, D.edge_vec);
+    if (mode & 6) st256(D.vv + n, make_double4(v[0], v[1], v[2], 0.0));
+    if (mode & 8) {
+        x.x += v[0] * dt; x.y += v[1] * dt; x.z += v[2] * dt;
+        st256(D.xT + n, x);
+    }
+}

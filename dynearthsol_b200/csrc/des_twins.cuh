@@ -71,7 +71,7 @@ __global__ void k_tw_residual(const __grid_constant__ Dev D, double *acc)
         const int end = D.sup_idx[n + 1];
         if (end > D.sup_idx[n]) {
             const int ent = D.sup_ent[end - 1];
-            const double *tr = D.fc + size_t(ent >> 2) * 12 + (ent & 3) * 3;
+            const double *tr = D.fc + DES_FC_OFF(ent);
             for (int j = 0; j < 3; ++j) l2 += tr[j] * tr[j] / num;
         }
     }
@@ -146,7 +146,7 @@ int des_gpu_update_force(DesGpu *h)
 {
     int rc = twin_ready(h); if (rc) return rc;
     LAUNCH(KC_TWIN, k_sbc_facets, h->D.nsbc_facets, 128, h->P, h->D, h->compensation_pressure);
-    LAUNCH(KC_TWIN, (k_elem_c<false>), h->D.nelem, 256, h->P, h->D);
+    LAUNCH_M(KC_TWIN, k_elem_c, false, h->D.nelem, 256, h->P, h->D);
     LAUNCH(KC_TWIN, k_node_c, h->D.nnode, 256, h->P, h->D, 0.0, 0, 1);
     CK(cudaGetLastError());
     return DES_OK;
