@@ -117,6 +117,87 @@ def regular_box(xlength, ylength, zlength, nx, ny, nz, renumber=True, order="ref
     return np.ascontiguousarray(coord), np.ascontiguousarray(conn.astype(np.int32)), bcflag
 
 
+def regular_box_part(xlength, ylength, zlength, nx, ny, nz, rank, boxes):
+    """The part of the regular box that rank `rank` holds when the node index space is split
+    into `boxes` (partition.grid_boxes): the elements touching a node the rank owns, and their
+    nodes, generated directly -- the global mesh is never built.  Node coordinates, the
+    parity-alternating 5-tet split and the relative order of nodes and elements are those of
+    regular_box(), so the local mesh is the restriction of the global one.
+
+    Returns coord [3,N], conn [4,E] (local indices), bcflag [N], node_key [N] (global
+    lexicographic node id, int64) and owner [N] (owning rank of every local node)."""
+    from . import partition
+    (ia, ib), (ja, jb), (ka, kb) = boxes[rank]
+    i0, i1 = max(ia - 1, 0), min(ib, nx - 1)        # local node index ranges, inclusive
+    j0, j1 = max(ja - 1, 0), min(jb, ny - 1)
+    k0, k1 = max(ka - 1, 0), min(kb, nz - 1)
+    nxl, nyl, nzl = i1 - i0 + 1, j1 - j0 + 1, k1 - k0 + 1
+    dx = xlength / (nx - 1)
+    dy = ylength / (ny - 1)
+    dz = -zlength / (nz - 1)
+    ii, jj, kk = np.meshgrid(np.arange(i0, i1 + 1, dtype=np.int32), np.arange(j0, j1 + 1, dtype=np.int32),
+                             np.arange(k0, k1 + 1, dtype=np.int32), indexing="ij")
+    ii = ii.reshape(-1); jj = jj.reshape(-1); kk = kk.reshape(-1)
+    coord = np.empty((3, ii.size), dtype=np.float64)
+    coord[0] = ii * dx
+    coord[1] = jj * dy
+    coord[2] = kk * dz
+    bcflag = np.zeros(ii.size, dtype=np.uint32)
+    bcflag[ii == 0] |= 1
+    bcflag[ii == nx - 1] |= 2
+    bcflag[jj == 0] |= 4
+    bcflag[jj == ny - 1] |= 8
+    bcflag[kk == nz - 1] |= 16
+    bcflag[kk == 0] |= 32
+    node_key = (ii.astype(np.int64) * ny + jj) * nz + kk
+    owner = partition.owner_of_grid_nodes(ii, jj, kk, boxes)
+    del ii, jj, kk
+
+    ci, cj, ck = np.meshgrid(np.arange(i0, i1, dtype=np.int32), np.arange(j0, j1, dtype=np.int32),
+                             np.arange(k0, k1, dtype=np.int32), indexing="ij")
+    ci = ci.reshape(-1); cj = cj.reshape(-1); ck = ck.reshape(-1)
+    ncell = ci.size
+    idx0 = (ci - i0) * (nyl * nzl) + (cj - j0) * nzl + (ck - k0)
+    verts = np.empty((8, ncell), dtype=np.int32)
+    verts[0] = idx0
+    verts[1] = idx0 + nzl
+    verts[2] = idx0 + nzl + nyl * nzl
+    verts[3] = idx0 + nyl * nzl
+    verts[4:8] = verts[0:4] + 1
+    odd = ((ci + cj + ck) % 2).astype(bool)
+    del ci, cj, ck, idx0
+    conn = np.empty((4, ncell, 5), dtype=np.int32)
+    cells = np.arange(ncell)
+    for n in range(5):
+        for v in range(4):
+            conn[v, :, n] = np.where(odd, verts[TETS_ODD[n, v], cells], verts[TETS_EVEN[n, v], cells])
+    del verts, odd, cells
+    conn = conn.reshape(4, ncell * 5)
+    # keep the elements that touch an owned node, and the nodes they use
+    mine = owner == rank
+    keep = mine[conn[0]] | mine[conn[1]] | mine[conn[2]] | mine[conn[3]]
+    conn = conn[:, keep]
+    used = np.zeros(coord.shape[1], dtype=bool)
+    used[conn.reshape(-1)] = True
+    nd = np.nonzero(used)[0]
+    remap = np.full(coord.shape[1], -1, dtype=np.int32)
+    remap[nd] = np.arange(nd.size, dtype=np.int32)
+    conn = remap[conn]
+    coord = coord[:, nd]; bcflag = bcflag[nd]; node_key = node_key[nd]; owner = owner[nd]
+    # renumbering_mesh: the same keys and stable sorts as regular_box()
+    f = 1e-3
+    wn = coord[0] + f * coord[1] + f * f * coord[2]
+    we = wn[conn[0]] + wn[conn[1]] + wn[conn[2]] + wn[conn[3]]
+    nd_idx = np.argsort(wn, kind="stable").astype(np.int32)
+    el_idx = np.argsort(we, kind="stable")
+    nd_inv = np.empty(nd_idx.size, dtype=np.int32)
+    nd_inv[nd_idx] = np.arange(nd_idx.size, dtype=np.int32)
+    coord = coord[:, nd_idx]
+    conn = nd_inv[conn[:, el_idx]]
+    return (np.ascontiguousarray(coord), np.ascontiguousarray(conn.astype(np.int32)), bcflag[nd_idx],
+            node_key[nd_idx], owner[nd_idx])
+
+
 def _part1by2(x):
     x = x.astype(np.int64) & 0x1fffff
     x = (x | (x << 32)) & 0x1f00000000ffff

@@ -113,6 +113,8 @@ ABI_SYMBOLS = [
     "des_gpu_launch_count", "des_gpu_enable_kernel_timing", "des_gpu_kernel_time",
     "des_gpu_device_ptr", "des_host_build_support", "des_abi_sizeof",
     "des_gpu_event_record", "des_gpu_event_elapsed_ms",
+    "des_gpu_step_segment", "des_gpu_set_stream", "des_gpu_set_halo", "des_gpu_halo_buffers",
+    "des_gpu_halo_width", "des_gpu_halo_pack", "des_gpu_halo_unpack",
 ]
 
 _lib = None
@@ -157,6 +159,13 @@ def load_library():
     L.des_gpu_device_ptr.restype = C.c_void_p
     L.des_gpu_event_record.argtypes = [H, C.c_int]
     L.des_gpu_event_elapsed_ms.argtypes = [H, C.c_int, C.c_int, _DP]
+    L.des_gpu_step_segment.argtypes = [H, C.c_int, C.c_double, C.c_double]
+    L.des_gpu_set_stream.argtypes = [H, C.c_void_p, C.c_int]
+    L.des_gpu_set_halo.argtypes = [H, C.c_int, _IP, C.c_int, _IP]
+    L.des_gpu_halo_buffers.argtypes = [H, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+    L.des_gpu_halo_width.argtypes = [C.c_int]
+    L.des_gpu_halo_pack.argtypes = [H, C.c_int]
+    L.des_gpu_halo_unpack.argtypes = [H, C.c_int]
     L.des_host_build_support.argtypes = [C.c_int, C.c_int, _IP, _IP, _IP, _IP]
     L.des_abi_sizeof.argtypes = [C.c_int]
     for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions)):
@@ -358,6 +367,29 @@ class DesGpu:
     # ---- stepping -----------------------------------------------------------------------
     def step(self, dt, time=0.0, steps=0):
         self._ck(self.lib.des_gpu_step(self.h, float(dt), float(time), int(steps)))
+
+    def step_segment(self, seg, dt, time=0.0):
+        self._ck(self.lib.des_gpu_step_segment(self.h, int(seg), float(dt), float(time)))
+
+    def set_stream(self, stream_ptr):
+        """Run on the caller's CUDA stream (an integer cudaStream_t; 0 = legacy default stream)."""
+        self._ck(self.lib.des_gpu_set_stream(self.h, C.c_void_p(stream_ptr), 0))
+
+    def set_halo(self, send_nodes, recv_nodes):
+        s = np.ascontiguousarray(send_nodes, dtype=np.int32)
+        r = np.ascontiguousarray(recv_nodes, dtype=np.int32)
+        self._ck(self.lib.des_gpu_set_halo(self.h, s.size, _ptr(s, C.c_int), r.size, _ptr(r, C.c_int)))
+
+    def halo_buffers(self):
+        a, b = C.c_void_p(), C.c_void_p()
+        self._ck(self.lib.des_gpu_halo_buffers(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def halo_pack(self, phase):
+        self._ck(self.lib.des_gpu_halo_pack(self.h, int(phase)))
+
+    def halo_unpack(self, phase):
+        self._ck(self.lib.des_gpu_halo_unpack(self.h, int(phase)))
 
     def compute_dt_reductions(self):
         r = DesDtReductions()

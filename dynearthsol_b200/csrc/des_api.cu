@@ -43,6 +43,12 @@ struct DesGpu {
     double compensation_pressure = 0;
     double last_dt = 0;                 // dt of the last step (for max_surf_vel)
     bool surf_ran = false;
+    // multi-GPU ghost exchange (des_gpu_set_halo)
+    int nsend = 0, nrecv = 0;
+    int *send_idx = nullptr, *recv_idx = nullptr, *top_of_node = nullptr;
+    double *send_buf = nullptr, *recv_buf = nullptr;
+    bool own_stream = true;
+    bool seg_rot = false;               // rotation pending for segment 1 of the current step
     bool node_staged = false;           // DES_NODE_STAGED=1: shared-memory staged node gathers
     int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
     long long launches = 0;
@@ -158,6 +164,9 @@ void free_mesh(DesGpu *h)
     for (void *p : h->mesh_allocs) cudaFree(p);
     h->mesh_allocs.clear();
     h->named.clear();
+    h->nsend = h->nrecv = 0;
+    h->send_idx = h->recv_idx = h->top_of_node = nullptr;
+    h->send_buf = h->recv_buf = nullptr;
     memset(&h->D, 0, sizeof(h->D));
     h->have_mesh = h->have_state = false;
     h->tail_pending = false;
@@ -385,7 +394,7 @@ int des_gpu_destroy(DesGpu *h)
     if (h->dt_partials) cudaFree(h->dt_partials);
     for (auto &p : h->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto &e : h->user_ev) if (e) cudaEventDestroy(e);
-    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->stream && h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
     return DES_OK;
 }
@@ -624,45 +633,30 @@ int des_gpu_sync(DesGpu *h)
 }
 
 // -----------------------------------------------------------------------------------------
-int des_gpu_step(DesGpu *h, double dt, double time, int steps)
+// One step is three segments separated by the two nodal barriers inside it, plus a tail;
+// a multi-GPU host exchanges ghost-node values between them (des_gpu_halo_*):
+//   segment 0: E-A, N-A                     -> ghosts need {temperature, dvoldt}
+//   segment 1: E-B, N-B                     -> ghosts need {dp_nd}
+//   segment 2: stress-bc facets, E-C, N-C     -> ghosts need {coord, vel}
+//   segment 3: surface diffusion (reads the neighbours' NEW coordinates) -> ghosts need {z, dh}
+//   segment 4: edvacc_surf, correct_surface_element, volume swap; defers volume/mass/rotation
+int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
 {
-    (void)steps;
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
+    if (seg < 0 || seg > 4) return fail(h, DES_E_ARG, "segment must be 0..4");
+    if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
     Dev &D = h->D;
     const int N = D.nnode, E = D.nelem;
     const int mm = h->hp.has_moving_mesh;
-
     const int hf = head_flags(h);
-    if (h->schedule == 1) {
-    // ---- schedule v1 (des_kernels.cuh): rotation in E-A, strain rate stored by E-A ----
-    if (h->tail_pending) {
-        LAUNCH(KC_ELEM_A, (k_elem_a<true, true>), E, 256, h->P, D, h->dt_prev, tail_flags(h), hf);
-        if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, true>), N, 256, h->P, D, dt, hf);
-        else    LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
-        h->tail_pending = false;
-    }
-    else {
-        LAUNCH(KC_ELEM_A, (k_elem_a<false, true>), E, 256, h->P, D, 0.0, 0, hf);
-        LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
-    }
-    LAUNCH(KC_ELEM_B, k_elem_b, E, 128, h->P, D, dt, 0);
-    if (h->hp.is_using_mixed_stress) LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
-    LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
-    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
-    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
-    int bc_z1 = h->hp.vbc_types[5];
-    if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
-    LAUNCH(KC_NODE_C, k_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
-    }
-    else {
-    // ---- schedule v2 (des_kernels2.cuh) -------------------------------------------------
     const int ngrid = DES_GRID(N, DES_NODE_BLOCK);
+    const bool staged = h->node_staged;
+    if (seg == 0) {
     const bool tail = h->tail_pending;
     const bool tail_mass = tail && mm;
-    const bool rot = tail && (h->hp.rheol_type & DES_RH_ELASTIC);
-    const bool staged = h->node_staged;
+    h->seg_rot = tail && (h->hp.rheol_type & DES_RH_ELASTIC);
     // E-A / N-A
     if (tail_mass) {
         LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, 256, h->P, D, 3, hf);
@@ -677,6 +671,9 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
         else LAUNCH(KC_NODE_A, (k3_node_a<false>), N, 256, h->P, D, dt, hf);
     }
     h->tail_pending = false;
+    }
+    else if (seg == 1) {
+    const bool rot = h->seg_rot;
     // E-B / N-B
     {
         const double dtr = rot ? h->dt_prev : 0.0;
@@ -696,6 +693,8 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
         if (staged) LAUNCH_G(KC_NODE_B, (k2_node_b<8>), ngrid, DES_NODE_BLOCK, 8 * DES_NODE_BLOCK * sizeof(double), D);
         else LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
     }
+    }
+    else if (seg == 2) {
     // E-C / N-C
     LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
     if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
@@ -705,6 +704,66 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
     if (staged) LAUNCH_G(KC_NODE_C, (k2_node_c<4>), ngrid, DES_NODE_BLOCK, 3 * 4 * DES_NODE_BLOCK * sizeof(double),
                          h->P, D, dt, bc_z1, mm ? 15 : 7);
     else LAUNCH(KC_NODE_C, k3_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
+    }
+    else if (seg == 3) {
+    if (mm && h->hp.surface_process_option == 1 && D.ntop > 0) {
+        CK(cudaMemsetAsync(D.maxdh_bits, 0, sizeof(unsigned long long), h->stream));
+        LAUNCH(KC_SURFACE, k_surf_facets, D.etop, 128, D);
+        LAUNCH(KC_SURFACE, k_surf_nodes, D.ntop, 128, h->P, D, dt);
+        h->surf_ran = true;
+    }
+    }
+    else {
+    if (mm) {
+        if (h->hp.surface_process_option == 1 && D.ntop > 0) LAUNCH(KC_SURFACE, k_surf_edvacc, D.etop, 128, D);
+        LAUNCH(KC_SURFACE, k_surf_correct_elems, D.ntop_elems, 128, D);
+        std::swap(D.volume, D.volume_old);      // dynearthsol.cxx:466-470
+    }
+    h->tail_pending = true;
+    h->dt_prev = dt;
+    h->last_dt = dt;
+    }
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
+int des_gpu_step(DesGpu *h, double dt, double time, int steps)
+{
+    (void)steps;
+    if (!h) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
+    if (h->schedule != 1) {
+        for (int seg = 0; seg < 5; ++seg) {
+            int rc = des_gpu_step_segment(h, seg, dt, time);
+            if (rc) return rc;
+        }
+        return DES_OK;
+    }
+    Dev &D = h->D;
+    const int N = D.nnode, E = D.nelem;
+    const int mm = h->hp.has_moving_mesh;
+    const int hf = head_flags(h);
+    {
+    // ---- schedule v1 (des_kernels.cuh): rotation in E-A, strain rate stored by E-A ----
+    if (h->tail_pending) {
+        LAUNCH(KC_ELEM_A, (k_elem_a<true, true>), E, 256, h->P, D, h->dt_prev, tail_flags(h), hf);
+        if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, true>), N, 256, h->P, D, dt, hf);
+        else    LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
+        h->tail_pending = false;
+    }
+    else {
+        LAUNCH(KC_ELEM_A, (k_elem_a<false, true>), E, 256, h->P, D, 0.0, 0, hf);
+        LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
+    }
+    LAUNCH(KC_ELEM_B, k_elem_b, E, 128, h->P, D, dt, 0);
+    if (h->hp.is_using_mixed_stress) LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
+    LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
+    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
+    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
+    int bc_z1 = h->hp.vbc_types[5];
+    if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
+    LAUNCH(KC_NODE_C, k_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
     }
     // update_mesh remainder
     if (mm) {
@@ -774,6 +833,78 @@ double des_dt_from_reductions(const DesParam *p, const DesDtReductions *r, doubl
     double dt_hydro = std::numeric_limits<double>::max();
     double dt = std::min({dt_elastic, r->dt_maxwell, dt_advection, r->dt_diffusion, dt_hydro}) * p->dt_fraction;
     return dt;
+}
+
+// ---- multi-GPU ghost exchange -------------------------------------------------------------
+int des_gpu_set_stream(DesGpu *h, void *stream, int own)
+{
+    if (!h) return DES_E_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    drain_events(h);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    if (!own) { h->stream = static_cast<cudaStream_t>(stream); h->own_stream = false; }   // 0 = legacy default stream
+    else {
+        CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        h->own_stream = true;
+    }
+    return DES_OK;
+}
+
+int des_gpu_set_halo(DesGpu *h, int nsend, const int *send_nodes, int nrecv, const int *recv_nodes)
+{
+    if (!h || nsend < 0 || nrecv < 0 || (nsend && !send_nodes) || (nrecv && !recv_nodes)) return DES_E_ARG;
+    if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    CK(cudaSetDevice(h->device));
+    for (int i = 0; i < nsend; ++i)
+        if (send_nodes[i] < 0 || send_nodes[i] >= h->D.nnode) return fail(h, DES_E_ARG, "send node out of range");
+    for (int i = 0; i < nrecv; ++i)
+        if (recv_nodes[i] < 0 || recv_nodes[i] >= h->D.nnode) return fail(h, DES_E_ARG, "recv node out of range");
+    int rc;
+    const int *p;
+    if ((rc = upload_new(h, &p, send_nodes, size_t(nsend)))) return rc;
+    h->send_idx = const_cast<int *>(p);
+    if ((rc = upload_new(h, &p, recv_nodes, size_t(nrecv)))) return rc;
+    h->recv_idx = const_cast<int *>(p);
+    if ((rc = dalloc(h, &h->send_buf, size_t(nsend) * 7, "halo_send"))) return rc;
+    if ((rc = dalloc(h, &h->recv_buf, size_t(nrecv) * 7, "halo_recv"))) return rc;
+    {
+        std::vector<unsigned char> gh(size_t(h->D.nnode), 0);
+        for (int i = 0; i < nrecv; ++i) gh[recv_nodes[i]] = 1;
+        if ((rc = upload_new(h, &h->D.ghost, gh.data(), gh.size()))) return rc;
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if ((rc = dalloc(h, &h->top_of_node, size_t(h->D.nnode)))) return rc;
+    CK(cudaMemsetAsync(h->top_of_node, 0xff, sizeof(int) * h->D.nnode, h->stream));
+    LAUNCH(KC_PACK, k_top_of_node, h->D.ntop, 128, h->D.ntop, h->D.top_nodes, h->top_of_node);
+    CK(cudaStreamSynchronize(h->stream));
+    h->nsend = nsend; h->nrecv = nrecv;
+    return DES_OK;
+}
+
+int des_gpu_halo_buffers(DesGpu *h, void **send_buf, void **recv_buf)
+{
+    if (!h || !send_buf || !recv_buf) return DES_E_ARG;
+    *send_buf = h->send_buf; *recv_buf = h->recv_buf;
+    return DES_OK;
+}
+
+int des_gpu_halo_width(int phase) { return (phase < 0 || phase > 3) ? -1 : halo_width(phase); }
+
+int des_gpu_halo_pack(DesGpu *h, int phase)
+{
+    if (!h || phase < 0 || phase > 3) return DES_E_ARG;
+    LAUNCH(KC_PACK, k_halo_pack, h->nsend, 256, phase, h->nsend, h->send_idx, h->D, h->top_of_node, h->send_buf);
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
+int des_gpu_halo_unpack(DesGpu *h, int phase)
+{
+    if (!h || phase < 0 || phase > 3) return DES_E_ARG;
+    LAUNCH(KC_PACK, k_halo_unpack, h->nrecv, 256, phase, h->nrecv, h->recv_idx, h->D, h->top_of_node, h->recv_buf);
+    CK(cudaGetLastError());
+    return DES_OK;
 }
 
 // ---- host-side topology helpers ------------------------------------------------------------

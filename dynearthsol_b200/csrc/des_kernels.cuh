@@ -56,6 +56,8 @@ struct Dev {
     const int *top_elems;
     double *dh, *dhacc, *edvacc_surf, *s_area, *s_slope;   // [ntop],[N],[etop],[etop],[etop][3]
     unsigned long long *maxdh_bits;
+    // multi-GPU: 1 for ghost nodes (values received from the owner), NULL on a single GPU
+    const unsigned char *ghost;
 };
 
 #define DES_GRID(n, b) (((n) + (b) - 1) / (b))
@@ -571,7 +573,9 @@ __global__ void k_surf_nodes(const __grid_constant__ DevParams P, const __grid_c
     D.dh[i] = dh;
     D.xT[n].z += dh;
     D.dhacc[n] += dh;
-    atomicMax(D.maxdh_bits, (unsigned long long)__double_as_longlong(fabs(dh)));
+    // a ghost's dh is a partial sum (it is overwritten by the owner's): keep it out of max|dh|
+    if (!D.ghost || !D.ghost[n])
+        atomicMax(D.maxdh_bits, (unsigned long long)__double_as_longlong(fabs(dh)));
 }
 
 // edvacc_surf loop, bc.cxx:1787-1797 (after the coordinate update)

@@ -566,3 +566,61 @@ k3_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
         st256(D.xT + n, x);
     }
 }
+
+// ---------------------------------------------------------------------------------------
+// ghost-node exchange buffers (multi-GPU): entry j of a list <-> node idx[j]; AoS per entry
+// so that each neighbour's entries are one contiguous message.
+//   phase 0 (after N-A): {temperature, dvoldt}            2 doubles
+//   phase 1 (after N-B): {dp_nd}                          1 double
+//   phase 2 (after N-C): {x, y, z, vx, vy, vz}            6 doubles
+//   phase 3 (after surface diffusion): {z, dh}            2 doubles
+// ---------------------------------------------------------------------------------------
+__host__ __device__ inline int halo_width(int phase) { return phase == 0 ? 2 : (phase == 1 ? 1 : (phase == 2 ? 6 : 2)); }
+
+__global__ void k_top_of_node(int ntop, const int *top_nodes, int *top_of_node)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < ntop) top_of_node[top_nodes[i]] = i;
+}
+
+__global__ void k_halo_pack(int phase, int n, const int *__restrict__ idx, const __grid_constant__ Dev D,
+                            const int *__restrict__ top_of_node, double *__restrict__ buf)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int node = idx[j];
+    if (phase == 0) { buf[2 * j] = D.xT[node].w; buf[2 * j + 1] = D.ntmp[node]; }
+    else if (phase == 1) buf[j] = D.ntmp[node];
+    else if (phase == 2) {
+        const double4 x = D.xT[node], v = D.vv[node];
+        double *b = buf + size_t(j) * 6;
+        b[0] = x.x; b[1] = x.y; b[2] = x.z; b[3] = v.x; b[4] = v.y; b[5] = v.z;
+    }
+    else {
+        const int t = top_of_node[node];
+        buf[2 * j] = D.xT[node].z;
+        buf[2 * j + 1] = (t >= 0) ? D.dh[t] : 0.0;
+    }
+}
+
+__global__ void k_halo_unpack(int phase, int n, const int *__restrict__ idx, const __grid_constant__ Dev D,
+                              const int *__restrict__ top_of_node, const double *__restrict__ buf)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int node = idx[j];
+    if (phase == 0) { D.xT[node].w = buf[2 * j]; D.ntmp[node] = buf[2 * j + 1]; }
+    else if (phase == 1) D.ntmp[node] = buf[j];
+    else if (phase == 2) {
+        const double *b = buf + size_t(j) * 6;
+        double4 x = D.xT[node];
+        x.x = b[0]; x.y = b[1]; x.z = b[2];
+        D.xT[node] = x;
+        D.vv[node] = make_double4(b[3], b[4], b[5], 0.0);
+    }
+    else {
+        D.xT[node].z = buf[2 * j];
+        const int t = top_of_node[node];
+        if (t >= 0) D.dh[t] = buf[2 * j + 1];
+    }
+}

@@ -177,6 +177,15 @@ int des_gpu_set_compensation_pressure(DesGpu *h, double p);
  * increment at dynearthsol.cxx:773-774.  Asynchronous; the end-of-step element work
  * (volume, mass, rotation) may be deferred and fused with the next step's first kernel. */
 int des_gpu_step(DesGpu *h, double dt, double time, int steps);
+/* The same step in five segments, for hosts that exchange ghost-node values between the
+ * nodal barriers of a step (multi-GPU, see des_gpu_set_halo): 0 = temperature/strain-rate
+ * trace and nodal gathers up to compute_dvoldt (fields.cxx:197-262, geometry.cxx:203-246);
+ * 1 = compute_edvoldt, update_stress and NMD_stress's nodal loop (rheology.cxx:703,
+ * geometry.cxx:282-309); 2 = NMD correction, update_force, update_velocity, apply_vbcs,
+ * update_coordinate (fields.cxx:609-784); 3 = simple_diffusion (bc.cxx:916-1112), which
+ * reads the neighbours' new coordinates; 4 = the rest of update_mesh (bc.cxx:1655-1707,
+ * dynearthsol.cxx:466-470).  des_gpu_step(h, dt, time, steps) == segments 0..4 in order. */
+int des_gpu_step_segment(DesGpu *h, int segment, double dt, double time);
 /* compute_dt (dynearthsol.cxx:643,893; geometry.cxx:1480): device reductions only */
 int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out);
 /* host scalar algebra of geometry.cxx:1597-1630 (no GPU work); returns dt, <=0 on error */
@@ -201,6 +210,30 @@ int des_gpu_compute_volume(DesGpu *h);                              /* geometry.
 int des_gpu_compute_mass(DesGpu *h);                                /* geometry.cxx:1743 */
 int des_gpu_rotate_stress(DesGpu *h, double dt);                    /* fields.cxx:827 */
 int des_gpu_residual_force(DesGpu *h, double *l2);                  /* fields.cxx:700 */
+
+/* ---- multi-GPU: one handle per device, elements partitioned, ghost nodes exchanged --------
+ * The reference has no distributed mode; this is the boundary a host (one process per GPU
+ * over torch.distributed/NCCL in dynearthsol_b200/multigpu.py, or one thread per device in
+ * a C++ driver) uses.  Each handle holds a sub-mesh: the elements touching the nodes the rank
+ * owns, plus the other ("ghost") nodes of those elements.  Owned nodes see their complete
+ * support in the reference's ascending element order, so results are bit-identical to one
+ * GPU; ghost nodes receive their values from the owner after each nodal barrier.
+ *   des_gpu_set_stream   own == 0: run this handle's kernels on the caller's CUDA stream
+ *                        (cudaStream_t; 0 is the legacy default stream), so the caller's
+ *                        collectives order with them; own != 0: back to a private stream
+ *   des_gpu_set_halo     local indices of owned nodes other ranks need (send) and of ghost
+ *                        nodes (recv), each concatenated over neighbours in message order
+ *   des_gpu_halo_buffers device pointers of the packed send / receive buffers
+ *   des_gpu_halo_width   doubles per entry in phase 0 {T, dvoldt}, 1 {dp_nd},
+ *                        2 {x, y, z, vx, vy, vz}, 3 {z, dh}
+ *   des_gpu_halo_pack / _unpack   gather into / scatter from the buffers, after segment
+ *                        `phase` of des_gpu_step_segment */
+int des_gpu_set_stream(DesGpu *h, void *cuda_stream, int own);
+int des_gpu_set_halo(DesGpu *h, int nsend, const int *send_nodes, int nrecv, const int *recv_nodes);
+int des_gpu_halo_buffers(DesGpu *h, void **send_buf, void **recv_buf);
+int des_gpu_halo_width(int phase);
+int des_gpu_halo_pack(DesGpu *h, int phase);
+int des_gpu_halo_unpack(DesGpu *h, int phase);
 
 /* ---- host-side topology helpers (pure integer work, no GPU) ---------------------------- */
 /* create_support (mesh.cxx:3287-3329): node -> (element, local node) CSR with ascending
