@@ -1,0 +1,265 @@
+// See des_bridge.hpp.  Compiled with the reference's flags (-DTHREED -DSOA) against its headers.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "constants.hpp"
+#include "parameters.hpp"
+#include "matprops.hpp"
+#include "markerset.hpp"
+#include "des_bridge.hpp"
+
+#ifndef THREED
+#error "the B200 explicit core is 3D only (SURVEY.md section 2: 2D is out of scope)"
+#endif
+
+struct DesBridge {
+    DesGpu *h = nullptr;
+    DesParam p;
+    std::string err;
+    std::vector<int> flat_markers;
+    std::vector<std::vector<int> > flat_facets;
+};
+
+namespace {
+
+template <class V> void copy_mat(double *dst, const V &src, int nmat)
+{
+    for (int m = 0; m < nmat && m < DES_MAX_MAT; ++m)
+        dst[m] = src[src.size() == 1 ? 0 : m];
+}
+
+void fill_param(DesParam &q, const Param &param, const Variables &var)
+{
+    std::memset(&q, 0, sizeof(q));
+    const Control &c = param.control;
+    q.gravity = c.gravity;
+    q.inertial_scaling = c.inertial_scaling;
+    q.damping_factor = c.damping_factor;
+    q.surface_diffusivity = var.surfinfo.surf_diff;
+    q.surf_base_level = c.surf_base_level;
+    q.dt_fraction = c.dt_fraction;
+    q.fixed_dt = c.fixed_dt;
+    q.characteristic_speed = c.characteristic_speed;
+    q.damping_option = c.damping_option;
+    q.is_quasi_static = c.is_quasi_static;
+    q.has_thermal_diffusion = c.has_thermal_diffusion;
+    q.is_using_mixed_stress = c.is_using_mixed_stress;
+    q.surface_process_option = c.surface_process_option;
+    q.ref_pressure_option = c.ref_pressure_option;
+    q.has_moving_mesh = c.has_moving_mesh;
+    q.has_body_force_adjustment = param.ic.has_body_force_adjustment;
+    const BC &bc = param.bc;
+    q.has_winkler_foundation = bc.has_winkler_foundation;
+    q.has_water_loading = bc.has_water_loading;
+    q.has_elastic_foundation = bc.has_elastic_foundation;
+    q.winkler_delta_rho = bc.winkler_delta_rho;
+    q.elastic_foundation_constant = bc.elastic_foundation_constant;
+    q.sea_water_density = bc.sea_water_density;
+    q.surface_temperature = bc.surface_temperature;
+    for (int i = 0; i < DES_NBDRY; ++i) { q.vbc_types[i] = var.vbc_types[i]; q.vbc_values[i] = var.vbc_values[i]; }
+    q.vbc_val_lateral[0] = bc.vbc_val_x0_l; q.vbc_val_lateral[1] = bc.vbc_val_x1_l;
+    q.vbc_val_lateral[2] = bc.vbc_val_y0_l; q.vbc_val_lateral[3] = bc.vbc_val_y1_l;
+    q.vbc_val_z1_loading_period = var.vbc_val_z1_loading_period;
+    for (int i = 0; i < 6; ++i) q.stress_bc_types[i] = var.stress_bc_types[i];
+    q.max_vbc_val = var.max_vbc_val;
+    q.zlength = param.mesh.zlength;
+    const Mat &m = param.mat;
+    q.rheol_type = m.rheol_type;
+    q.nmat = m.nmat;
+    q.mattype_ref = m.mattype_ref;
+    q.visc_min = m.visc_min; q.visc_max = m.visc_max;
+    q.tension_max = m.tension_max; q.therm_diff_max = m.therm_diff_max;
+    copy_mat(q.rho0, m.rho0, m.nmat); copy_mat(q.alpha, m.alpha, m.nmat);
+    copy_mat(q.bulk_modulus, m.bulk_modulus, m.nmat); copy_mat(q.shear_modulus, m.shear_modulus, m.nmat);
+    copy_mat(q.visc_exponent, m.visc_exponent, m.nmat); copy_mat(q.visc_coefficient, m.visc_coefficient, m.nmat);
+    copy_mat(q.visc_activation_energy, m.visc_activation_energy, m.nmat);
+    copy_mat(q.visc_activation_volume, m.visc_activation_volume, m.nmat);
+    copy_mat(q.heat_capacity, m.heat_capacity, m.nmat); copy_mat(q.therm_cond, m.therm_cond, m.nmat);
+    copy_mat(q.pls0, m.pls0, m.nmat); copy_mat(q.pls1, m.pls1, m.nmat);
+    copy_mat(q.cohesion0, m.cohesion0, m.nmat); copy_mat(q.cohesion1, m.cohesion1, m.nmat);
+    copy_mat(q.friction_angle0, m.friction_angle0, m.nmat); copy_mat(q.friction_angle1, m.friction_angle1, m.nmat);
+    copy_mat(q.dilation_angle0, m.dilation_angle0, m.nmat); copy_mat(q.dilation_angle1, m.dilation_angle1, m.nmat);
+    copy_mat(q.porosity, m.porosity, m.nmat);
+}
+
+int fail(DesBridge *b, int rc, const char *what)
+{
+    b->err = std::string(what) + ": " + (b->h ? des_gpu_last_error(b->h) : "no device model");
+    std::fprintf(stderr, "des_bridge: %s (code %d)\n", b->err.c_str(), rc);
+    return rc;
+}
+
+void flatten_markers(DesBridge *b, const Param &param, const Variables &var)
+{
+    const int nmat = param.mat.nmat;
+    b->flat_markers.resize(size_t(var.nelem) * nmat);
+    for (int e = 0; e < var.nelem; ++e)
+        for (int m = 0; m < nmat; ++m)
+            b->flat_markers[size_t(e) * nmat + m] = (*var.elemmarkers)[e][m];
+}
+
+// every field array of Variables the device owns a copy of (SURVEY.md section 8b classes)
+void state_pointers(DesState &s, const Variables &var, bool all)
+{
+    std::memset(&s, 0, sizeof(s));
+    s.coord = var.coord->data(); s.vel = var.vel->data();
+    s.temperature = var.temperature->data();
+    s.stress = var.stress->data(); s.strain = var.strain->data(); s.strain_rate = var.strain_rate->data();
+    s.plstrain = var.plstrain->data(); s.delta_plstrain = var.delta_plstrain->data();
+    s.volume = var.volume->data();
+    s.viscosity = var.viscosity->data();
+    s.force = var.force->data();
+    if (all) {
+        s.coord0 = var.coord0->data();
+        s.volume_old = var.volume_old->data();
+        s.dpressure = var.dpressure->data(); s.edvoldt = var.edvoldt->data();
+        s.radiogenic_source = var.radiogenic_source->data();
+        s.volume_n = var.volume_n->data(); s.mass = var.mass->data(); s.tmass = var.tmass->data();
+        s.dhacc = var.surfinfo.dhacc->data();
+        s.edvacc_surf = var.surfinfo.edvacc_surf->data();
+    }
+}
+
+} // namespace
+
+int des_bridge_upload(DesBridge *b, const Param &param, const Variables &var)
+{
+    DesMesh m;
+    std::memset(&m, 0, sizeof(m));
+    m.nnode = var.nnode; m.nelem = var.nelem;
+    m.connectivity = var.connectivity->data();
+    m.bcflag = var.bcflag->data();
+    m.support_idx = var.support.idx_data.data();
+    m.support_arr = var.support.arr_data.data();
+    m.support_lidx = var.support.lidx_data.data();
+    b->flat_facets.assign(DES_NBDRY, std::vector<int>());
+    for (int i = 0; i < DES_NBDRY; ++i) {
+        const auto &bf = *var.bfacets[i];
+        std::vector<int> &f = b->flat_facets[i];
+        f.resize(bf.size() * 2);
+        for (size_t k = 0; k < bf.size(); ++k) { f[2*k] = bf[k].first; f[2*k + 1] = bf[k].second; }
+        m.nbfacets[i] = int(bf.size());
+        m.bfacets[i] = f.data();
+        m.nbnodes[i] = int(var.bnodes[i]->size());
+        m.bnodes[i] = var.bnodes[i]->data();
+    }
+    m.bnormals = var.bnormals->data();
+    m.n_edge_vec = int(var.edge_vec.size());
+    m.edge_vec = var.edge_vec.data();
+    m.edge_slot = var.edge_slot;
+    m.ntop_elems = var.ntop_elems;
+    m.top_elems = var.top_elems->data();
+    m.ntop = var.surfinfo.ntop;
+    m.top_nodes = var.surfinfo.top_nodes->data();
+    m.etop = var.surfinfo.etop;
+    m.support_surf_idx = var.surfinfo.support_surf.idx_data.data();
+    m.support_surf_arr = var.surfinfo.support_surf.arr_data.data();
+    m.elem_and_nodes = var.surfinfo.elem_and_nodes->data();
+    m.connectivity_surface = var.connectivity_surface->data();
+    int rc = des_gpu_upload_mesh(b->h, &m);
+    if (rc) return fail(b, rc, "upload_mesh");
+    flatten_markers(b, param, var);
+    if ((rc = des_gpu_upload_elemmarkers(b->h, b->flat_markers.data()))) return fail(b, rc, "upload_elemmarkers");
+    des_gpu_set_compensation_pressure(b->h, var.compensation_pressure);
+    DesState s;
+    state_pointers(s, var, true);
+    if ((rc = des_gpu_upload_state(b->h, &s))) return fail(b, rc, "upload_state");
+    return 0;
+}
+
+DesBridge *des_bridge_create(const Param &param, const Variables &var, int device)
+{
+    DesBridge *b = new DesBridge;
+    fill_param(b->p, param, var);
+    int rc = des_gpu_create(&b->p, device, &b->h);
+    if (rc) {
+        std::fprintf(stderr, "des_bridge: des_gpu_create failed (code %d): %s\n", rc,
+                     b->h ? des_gpu_last_error(b->h) : "no CUDA device");
+        if (b->h) des_gpu_destroy(b->h);
+        delete b;
+        return nullptr;     // there is no CPU fallback: the caller must stop
+    }
+    if (des_bridge_upload(b, param, var)) { des_bridge_destroy(b); return nullptr; }
+    return b;
+}
+
+int des_bridge_step(DesBridge *b, const Param &param, Variables &var)
+{
+    // On quality-check steps surface_processes() also moves markers on the host, in the middle
+    // of update_mesh (bc.cxx:1829-1843): break the step there.
+    const bool marker_step = param.control.has_moving_mesh && var.steps != 0 &&
+        var.steps % param.mesh.quality_check_step_interval == 0;
+    if (!marker_step) {
+        int rc = des_gpu_step(b->h, var.dt, var.time, var.steps);
+        if (rc) return fail(b, rc, "step");
+        return 0;
+    }
+    int rc;
+    for (int seg = 0; seg <= 4; ++seg)
+        if ((rc = des_gpu_step_segment(b->h, seg, var.dt, var.time))) return fail(b, rc, "step_segment");
+    DesState s;
+    std::memset(&s, 0, sizeof(s));
+    s.coord = var.coord->data();
+    s.volume = var.volume->data();          // pre-swap: top elements already hold the new volume
+    s.dhacc = var.surfinfo.dhacc->data();
+    s.edvacc_surf = var.surfinfo.edvacc_surf->data();
+    if ((rc = des_gpu_download_state(b->h, &s))) return fail(b, rc, "download_state");
+    var.markersets[0]->correct_surface_marker(param, var, *var.surfinfo.dhacc, *var.elemmarkers,
+                                              *var.markers_in_elem);
+    for (int i = 0; i < var.surfinfo.ntop; i++)
+        (*var.surfinfo.dhacc)[(*var.surfinfo.top_nodes)[i]] = 0.;
+    var.markersets[0]->set_surface_marker(param, var, param.mesh.smallest_size, param.mat.mattype_sed,
+                                          *var.surfinfo.edvacc_surf, *var.elemmarkers, *var.markers_in_elem);
+    std::memset(&s, 0, sizeof(s));
+    s.dhacc = var.surfinfo.dhacc->data();
+    s.edvacc_surf = var.surfinfo.edvacc_surf->data();
+    if ((rc = des_gpu_upload_state(b->h, &s))) return fail(b, rc, "upload_state");
+    if ((rc = des_bridge_markers_changed(b, param, var))) return rc;
+    if ((rc = des_gpu_step_segment(b->h, 5, var.dt, var.time))) return fail(b, rc, "step_segment");
+    return 0;
+}
+
+double des_bridge_compute_dt(DesBridge *b, const Param &param, Variables &var)
+{
+    (void)param;
+    DesDtReductions r;
+    int rc = des_gpu_compute_dt(b->h, &r);
+    if (rc) { fail(b, rc, "compute_dt"); return -1; }
+    var.surfinfo.max_surf_vel = r.max_surf_vel;
+    var.global_dt_min = r.global_dt_min;
+    return des_dt_from_reductions(&b->p, &r, &var.max_global_vel_mag);
+}
+
+int des_bridge_download(DesBridge *b, Variables &var, int what)
+{
+    DesState s;
+    if (what & DES_DL_ALL) state_pointers(s, var, true);
+    else if (what & DES_DL_OUTPUT) state_pointers(s, var, false);
+    else {
+        std::memset(&s, 0, sizeof(s));
+        s.coord = var.coord->data(); s.volume = var.volume->data();
+        s.temperature = var.temperature->data();
+    }
+    int rc = des_gpu_download_state(b->h, &s);
+    if (rc) return fail(b, rc, "download_state");
+    return 0;
+}
+
+int des_bridge_markers_changed(DesBridge *b, const Param &param, const Variables &var)
+{
+    flatten_markers(b, param, var);
+    int rc = des_gpu_upload_elemmarkers(b->h, b->flat_markers.data());
+    if (rc) return fail(b, rc, "upload_elemmarkers");
+    return 0;
+}
+
+const char *des_bridge_last_error(const DesBridge *b) { return b ? b->err.c_str() : "null bridge"; }
+
+void des_bridge_destroy(DesBridge *b)
+{
+    if (!b) return;
+    if (b->h) des_gpu_destroy(b->h);
+    delete b;
+}

@@ -1,0 +1,41 @@
+// Bridge between the reference's C++ driver and the C-ABI of include/des_gpu.h.
+//
+// This is the file a DynEarthSol maintainer adds next to dynearthsol.cxx: it marshals
+// `Param` / `Variables` (parameters.hpp:160-832) into the POD structs of des_gpu.h and
+// back.  It is compiled against the reference's own headers and re-reads every host pointer
+// from `Variables` on each call (remesh() re-news nearly every array, fields.cxx:125-194,
+// and update_mesh swaps volume/volume_old each step, dynearthsol.cxx:466-470).
+// See INTEGRATION.md for the call-site swaps in dynearthsol.cxx.
+#ifndef DES_BRIDGE_HPP
+#define DES_BRIDGE_HPP
+
+#include "parameters.hpp"
+#include "../include/des_gpu.h"
+
+// what des_bridge_download brings back into `Variables`
+enum {
+    DES_DL_OUTPUT = 1,      // everything Output::_write reads (output.cxx:95-274)
+    DES_DL_GEOMETRY = 2,    // coord, volume, temperature: bad_mesh_quality, phase_changes
+    DES_DL_ALL = 4          // every evolving + derived array (before remesh / checkpoint)
+};
+
+struct DesBridge;
+
+// after init() / restart(): creates the device model (device `device`) and uploads mesh + state
+DesBridge *des_bridge_create(const Param &param, const Variables &var, int device);
+// after every remesh() (dynearthsol.cxx:950): new topology and all fields
+int des_bridge_upload(DesBridge *b, const Param &param, const Variables &var);
+// the block dynearthsol.cxx:776-876 (refresh_elem_cache ... rotate_stress); var.steps,
+// var.time already incremented by the caller as in the reference (:773-774)
+int des_bridge_step(DesBridge *b, const Param &param, Variables &var);
+// compute_dt (dynearthsol.cxx:893): device reductions + the reference's scalar algebra;
+// also sets var.max_global_vel_mag, var.global_dt_min, var.surfinfo.max_surf_vel
+double des_bridge_compute_dt(DesBridge *b, const Param &param, Variables &var);
+// device -> the reference's own arrays, before host code reads them
+int des_bridge_download(DesBridge *b, Variables &var, int what);
+// elemmarkers changed on the host (phase_changes, surface markers): dynearthsol.cxx:887
+int des_bridge_markers_changed(DesBridge *b, const Param &param, const Variables &var);
+const char *des_bridge_last_error(const DesBridge *b);
+void des_bridge_destroy(DesBridge *b);
+
+#endif

@@ -639,13 +639,15 @@ int des_gpu_sync(DesGpu *h)
 //   segment 1: E-B, N-B                     -> ghosts need {dp_nd}
 //   segment 2: stress-bc facets, E-C, N-C     -> ghosts need {coord, vel}
 //   segment 3: surface diffusion (reads the neighbours' NEW coordinates) -> ghosts need {z, dh}
-//   segment 4: edvacc_surf, correct_surface_element, volume swap; defers volume/mass/rotation
+//   segment 4: edvacc_surf, correct_surface_element (the host's surface-marker routines run
+//              here on quality-check steps, bc.cxx:1829-1843, between segments 4 and 5)
+//   segment 5: volume swap; defers compute_volume / compute_mass / rotate_stress (no kernel)
 int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
 {
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
-    if (seg < 0 || seg > 4) return fail(h, DES_E_ARG, "segment must be 0..4");
+    if (seg < 0 || seg > 5) return fail(h, DES_E_ARG, "segment must be 0..5");
     if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
     Dev &D = h->D;
     const int N = D.nnode, E = D.nelem;
@@ -713,12 +715,14 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
         h->surf_ran = true;
     }
     }
-    else {
+    else if (seg == 4) {
     if (mm) {
         if (h->hp.surface_process_option == 1 && D.ntop > 0) LAUNCH(KC_SURFACE, k_surf_edvacc, D.etop, 128, D);
         LAUNCH(KC_SURFACE, k_surf_correct_elems, D.ntop_elems, 128, D);
-        std::swap(D.volume, D.volume_old);      // dynearthsol.cxx:466-470
     }
+    }
+    else {
+    if (mm) std::swap(D.volume, D.volume_old);      // dynearthsol.cxx:466-470
     h->tail_pending = true;
     h->dt_prev = dt;
     h->last_dt = dt;
@@ -734,7 +738,7 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
     if (h->schedule != 1) {
-        for (int seg = 0; seg < 5; ++seg) {
+        for (int seg = 0; seg < 6; ++seg) {
             int rc = des_gpu_step_segment(h, seg, dt, time);
             if (rc) return rc;
         }

@@ -95,6 +95,7 @@ class DistModel:
         if g.param.surface_process_option == 1 and g.param.has_moving_mesh:
             self.exchange(3)
         g.step_segment(4, dt, time)
+        g.step_segment(5, dt, time)
 
     def compute_dt(self):
         """Local reductions, min/max over ranks, then the reference's scalar algebra

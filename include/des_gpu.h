@@ -177,14 +177,17 @@ int des_gpu_set_compensation_pressure(DesGpu *h, double p);
  * increment at dynearthsol.cxx:773-774.  Asynchronous; the end-of-step element work
  * (volume, mass, rotation) may be deferred and fused with the next step's first kernel. */
 int des_gpu_step(DesGpu *h, double dt, double time, int steps);
-/* The same step in five segments, for hosts that exchange ghost-node values between the
+/* The same step in six segments, for hosts that exchange ghost-node values between the
  * nodal barriers of a step (multi-GPU, see des_gpu_set_halo): 0 = temperature/strain-rate
  * trace and nodal gathers up to compute_dvoldt (fields.cxx:197-262, geometry.cxx:203-246);
  * 1 = compute_edvoldt, update_stress and NMD_stress's nodal loop (rheology.cxx:703,
  * geometry.cxx:282-309); 2 = NMD correction, update_force, update_velocity, apply_vbcs,
  * update_coordinate (fields.cxx:609-784); 3 = simple_diffusion (bc.cxx:916-1112), which
- * reads the neighbours' new coordinates; 4 = the rest of update_mesh (bc.cxx:1655-1707,
- * dynearthsol.cxx:466-470).  des_gpu_step(h, dt, time, steps) == segments 0..4 in order. */
+ * reads the neighbours' new coordinates; 4 = edvacc_surf and correct_surface_element
+ * (bc.cxx:1655-1707,1787-1797) -- on quality-check steps the host's surface-marker routines
+ * (bc.cxx:1829-1843) run after it on downloaded coord/volume/dhacc/edvacc_surf; 5 = the
+ * volume swap (dynearthsol.cxx:466-470), no kernel.
+ * des_gpu_step(h, dt, time, steps) == segments 0..5 in order. */
 int des_gpu_step_segment(DesGpu *h, int segment, double dt, double time);
 /* compute_dt (dynearthsol.cxx:643,893; geometry.cxx:1480): device reductions only */
 int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out);

@@ -247,7 +247,7 @@ def test_parts_on_one_gpu_bit_identical(nparts):
     t = 0.0
     for s in range(1, 13):
         t += dt
-        for seg in range(5):
+        for seg in range(6):
             for g in gs:
                 g.step_segment(seg, dt, t)
             if seg < 4:
