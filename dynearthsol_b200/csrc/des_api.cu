@@ -49,7 +49,6 @@ struct DesGpu {
     double *send_buf = nullptr, *recv_buf = nullptr;
     bool own_stream = true;
     bool seg_rot = false;               // rotation pending for segment 1 of the current step
-    bool node_staged = false;           // DES_NODE_STAGED=1: shared-memory staged node gathers
     int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
     long long launches = 0;
     // staging
@@ -108,7 +107,7 @@ struct LaunchScope {
 #define LAUNCH(cls, kern, n, bs, ...) do { if ((n) > 0) { LaunchScope ls_(h, cls); auto kfn_ = kern; \
     kfn_<<<DES_GRID((n), (bs)), (bs), 0, h->stream>>>(__VA_ARGS__); } } while (0)
 
-// launch with an explicit grid and dynamic shared memory (the staged node gathers)
+// launch with an explicit grid and dynamic shared memory
 #define LAUNCH_G(cls, kern, grid, bs, smem, ...) do { if ((grid) > 0) { LaunchScope ls_(h, cls); auto kfn_ = kern; \
     kfn_<<<(grid), (bs), (smem), h->stream>>>(__VA_ARGS__); } } while (0)
 
@@ -372,7 +371,6 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
     DesGpu *h = new DesGpu;
     h->device = device;
     h->hp = *param;
-    if (const char *sv = getenv("DES_NODE_STAGED")) h->node_staged = atoi(sv) != 0;
     if (const char *sv = getenv("DES_SCHEDULE")) h->schedule = (atoi(sv) == 1) ? 1 : 2;
     memset(&h->D, 0, sizeof(h->D));
     memset(h->kc_ms, 0, sizeof(h->kc_ms));
@@ -653,24 +651,18 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
     const int N = D.nnode, E = D.nelem;
     const int mm = h->hp.has_moving_mesh;
     const int hf = head_flags(h);
-    const int ngrid = DES_GRID(N, DES_NODE_BLOCK);
-    const bool staged = h->node_staged;
     if (seg == 0) {
     const bool tail = h->tail_pending;
     const bool tail_mass = tail && mm;
     h->seg_rot = tail && (h->hp.rheol_type & DES_RH_ELASTIC);
     // E-A / N-A
     if (tail_mass) {
-        LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, 256, h->P, D, 3, hf);
-        if (staged) LAUNCH_G(KC_NODE_A, (k2_node_a<true, 4>), ngrid, DES_NODE_BLOCK,
-                             5 * 4 * DES_NODE_BLOCK * sizeof(double), h->P, D, dt, hf);
-        else LAUNCH(KC_NODE_A, (k3_node_a<true>), N, 256, h->P, D, dt, hf);
+        LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, DES_EA_BLOCK, h->P, D, 3, hf);
+        LAUNCH(KC_NODE_A, (k3_node_a<true>), N, 256, h->P, D, dt, hf);
     }
     else {
-        LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, 256, h->P, D, 0, hf);
-        if (staged) LAUNCH_G(KC_NODE_A, (k2_node_a<false, 4>), ngrid, DES_NODE_BLOCK,
-                             2 * 4 * DES_NODE_BLOCK * sizeof(double), h->P, D, dt, hf);
-        else LAUNCH(KC_NODE_A, (k3_node_a<false>), N, 256, h->P, D, dt, hf);
+        LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, DES_EA_BLOCK, h->P, D, 0, hf);
+        LAUNCH(KC_NODE_A, (k3_node_a<false>), N, 256, h->P, D, dt, hf);
     }
     h->tail_pending = false;
     }
@@ -692,8 +684,7 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
 #undef EB_CASE
     }
     if (h->hp.is_using_mixed_stress) {
-        if (staged) LAUNCH_G(KC_NODE_B, (k2_node_b<8>), ngrid, DES_NODE_BLOCK, 8 * DES_NODE_BLOCK * sizeof(double), D);
-        else LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
+        LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
     }
     }
     else if (seg == 2) {
@@ -703,9 +694,7 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
     else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
     int bc_z1 = h->hp.vbc_types[5];
     if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
-    if (staged) LAUNCH_G(KC_NODE_C, (k2_node_c<4>), ngrid, DES_NODE_BLOCK, 3 * 4 * DES_NODE_BLOCK * sizeof(double),
-                         h->P, D, dt, bc_z1, mm ? 15 : 7);
-    else LAUNCH(KC_NODE_C, k3_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
+    LAUNCH(KC_NODE_C, k3_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
     }
     else if (seg == 3) {
     if (mm && h->hp.surface_process_option == 1 && D.ntop > 0) {

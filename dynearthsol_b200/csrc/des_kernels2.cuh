@@ -2,32 +2,33 @@
 //
 //   E-A  k2_elem_a<TAIL>      tail(n-1): volume, mass contributions
 //                             head(n)  : T-diffusion contributions, tr(edot)*vol
-//   N-A  k2_node_a<MASS>      staged CSR gather: volume_n/mass/tmass, T update, dvoldt
+//   N-A  k3_node_a<MASS>      CSR gather: volume_n/mass/tmass, T update, dvoldt
 //   E-B  k2_elem_b<ROT>       tail(n-1): Jaumann rotation of stress and strain (dt_prev)
 //                             head(n)  : strain rate, edvoldt, anti-locking, strain, rheology,
 //                                        plstrain, dpressure*vol
-//   N-B  k2_node_b            staged CSR gather: dp_nd
+//   N-B  k_node_b             (des_kernels.cuh) CSR gather: dp_nd
 //   E-C  k_elem_c<MIXED>      (des_kernels.cuh) NMD correction, element forces
-//   N-C  k2_node_c            staged CSR gather of forces, stress bcs, damping, v, vbc, x
+//   N-C  k3_node_c            CSR gather of forces, stress bcs, damping, v, vbc, x
 //
 // Differences from v1 (des_kernels.cuh, kept as the un-fused twins and the flush path):
 //  * strain rate and spin are computed where they are consumed (E-B), so strain_rate is
 //    written once per step and stress/strain cross HBM once per direction in E-B instead
 //    of once more for the rotation in E-A;
-//  * the node gathers stage their support entries through shared memory: a block's CSR
-//    range is contiguous, every thread issues CPT independent (entry -> record) loads per
-//    chunk, then each node sums ITS entries from shared memory in ascending element order
-//    (the reference's order, fields.cxx:659-676) -- memory-level parallelism no longer
-//    depends on one dependent chain per node, and fewer nodes in flight keep the
-//    element records L2-resident between their four readers.
+//  * the node gathers read each support entry's record with one 256-bit load (+ one double)
+//    and keep four entries in flight per trip; they sum in ascending element order (the
+//    reference's order, fields.cxx:659-676).  Three alternatives were built, measured and
+//    dropped (profiles/experiments/): staging a block's entries through
+//    shared memory, a warp-interleaved copy of the support list, and staging an element
+//    tile's distinct nodes in shared memory for the element kernels.
 #pragma once
 #include "des_kernels.cuh"
 
 // ---------------------------------------------------------------------------------------
 // E-A (v2)
 // ---------------------------------------------------------------------------------------
+#define DES_EA_BLOCK 128      // measured: 128-thread blocks are 7 % faster than 256 here (72 registers)
 template <bool SINGLE, bool TAIL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(DES_EA_BLOCK)
 k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int tail_flags, int head_flags)
 {
     // tail_flags: 1 volume, 2 mass contributions;  head_flags: 1 T-diffusion, 4 tr(edot)*vol
@@ -91,196 +92,6 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
     if (head_flags & 1) { r[0] = make_double2(rec[0], rec[1]); r[1] = make_double2(rec[2], rec[3]); }
     if (TAIL) { r[2] = make_double2(rec[4], rec[5]); r[3] = make_double2(rec[6], rec[7]); }
     else if (head_flags & 4) D.ca[size_t(e) * 8 + 4] = rec[4];
-}
-
-// ---------------------------------------------------------------------------------------
-// staged CSR gather
-// ---------------------------------------------------------------------------------------
-// A block owns NB = blockDim.x consecutive nodes, whose support entries are the contiguous
-// CSR range [K0, K1).  The range is walked in chunks of CPT*NB entries: every thread loads
-// CPT entries and their NV record values (all independent -> CPT*NV loads in flight per
-// thread) into shared memory (SoA, [NV][CHUNK]); after a barrier each node consumes the part
-// of its own range that lies in the chunk, in ascending entry order.
-#define DES_NODE_BLOCK 256
-
-// N-A: MASS == compute_mass node loop (geometry.cxx:1843-1864); head == update_temperature
-// node loop (fields.cxx:244-262) and compute_dvoldt node loop (geometry.cxx:231-238).
-template <bool MASS, int CPT>
-__global__ void __launch_bounds__(DES_NODE_BLOCK)
-k2_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int head_flags)
-{
-    constexpr int NB = DES_NODE_BLOCK, CHUNK = CPT * NB, NV = MASS ? 5 : 2;
-    extern __shared__ double sm[];          // [NV][CHUNK]
-    const int tid = threadIdx.x;
-    const int n0 = blockIdx.x * NB, n = n0 + tid, N = D.nnode;
-    const int K0 = D.sup_idx[n0], K1 = D.sup_idx[min(n0 + NB, N)];
-    int beg = 0, end = 0;
-    if (n < N) { beg = D.sup_idx[n]; end = D.sup_idx[n + 1]; }
-    double vn = 0, m = 0, tm = 0, tdot = 0, dvol = 0;
-    for (int kc = K0; kc < K1; kc += CHUNK) {
-        const int len = min(CHUNK, K1 - kc);
-        int ent[CPT];
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            const int i = tid + j * NB;
-            ent[j] = (i < len) ? D.sup_ent[kc + i] : -1;
-        }
-        double2 hi0[CPT], hi1[CPT]; double lo[CPT];
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            if (ent[j] >= 0) {
-                const double *r = D.ca + size_t(ent[j] >> 2) * 8;
-                lo[j] = r[ent[j] & 3];
-                hi0[j] = *reinterpret_cast<const double2 *>(r + 4);     // {tr(edot)*vol, m}
-                if (MASS) hi1[j] = *reinterpret_cast<const double2 *>(r + 6);   // {tm, vol}
-            }
-        }
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            const int i = tid + j * NB;
-            if (ent[j] >= 0) {
-                sm[i] = lo[j];
-                sm[CHUNK + i] = hi0[j].x;
-                if (MASS) { sm[2 * CHUNK + i] = hi0[j].y; sm[3 * CHUNK + i] = hi1[j].x; sm[4 * CHUNK + i] = hi1[j].y; }
-            }
-        }
-        __syncthreads();
-        const int a = max(beg, kc) - kc, b = min(end, kc + len) - kc;
-        for (int i = a; i < b; ++i) {
-            tdot += sm[i]; dvol += sm[CHUNK + i];
-            if (MASS) { m += sm[2 * CHUNK + i]; tm += sm[3 * CHUNK + i]; vn += sm[4 * CHUNK + i]; }
-        }
-        __syncthreads();
-    }
-    if (n >= N) return;
-    if (MASS) {
-        D.volume_n[n] = vn;
-        D.mass[n] = m;
-        if (!P.has_thermal_diffusion) tm = 0;   // geometry.cxx:1836-1837,1859-1860
-        D.tmass[n] = tm;
-    }
-    else {
-        vn = D.volume_n[n];
-        tm = D.tmass[n];
-    }
-    if (head_flags & 1) {
-        double T;
-        if (D.bcflag[n] & BOUNDZ1) T = P.surface_temperature;
-        else T = D.xT[n].w - dt * tdot / tm;
-        D.xT[n].w = T;
-    }
-    if (head_flags & 4) D.ntmp[n] = dvol / vn;
-}
-
-// N-B: NMD_stress node loop, geometry.cxx:301-309
-template <int CPT>
-__global__ void __launch_bounds__(DES_NODE_BLOCK)
-k2_node_b(const __grid_constant__ Dev D)
-{
-    constexpr int NB = DES_NODE_BLOCK, CHUNK = CPT * NB;
-    extern __shared__ double sm[];          // [CHUNK]
-    const int tid = threadIdx.x;
-    const int n0 = blockIdx.x * NB, n = n0 + tid, N = D.nnode;
-    const int K0 = D.sup_idx[n0], K1 = D.sup_idx[min(n0 + NB, N)];
-    int beg = 0, end = 0;
-    if (n < N) { beg = D.sup_idx[n]; end = D.sup_idx[n + 1]; }
-    double acc = 0;
-    for (int kc = K0; kc < K1; kc += CHUNK) {
-        const int len = min(CHUNK, K1 - kc);
-        int ent[CPT];
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            const int i = tid + j * NB;
-            ent[j] = (i < len) ? D.sup_ent[kc + i] : -1;
-        }
-        double v[CPT];
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) if (ent[j] >= 0) v[j] = D.etmp[ent[j] >> 2];
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) if (ent[j] >= 0) sm[tid + j * NB] = v[j];
-        __syncthreads();
-        const int a = max(beg, kc) - kc, b = min(end, kc + len) - kc;
-        for (int i = a; i < b; ++i) acc += sm[i];
-        __syncthreads();
-    }
-    if (n < N) D.ntmp[n] = acc / D.volume_n[n];
-}
-
-// N-C: update_force node loop (fields.cxx:658-676), apply_stress_bcs node loops
-// (bc.cxx:783-823), apply_damping (fields.cxx:483-579), update_velocity (:734-737),
-// apply_vbcs (bc.cxx:396-651), update_coordinate (fields.cxx:774-778).  mode as k_node_c;
-// bit 1 (update_force) is always set here.
-template <int CPT>
-__global__ void __launch_bounds__(DES_NODE_BLOCK)
-k2_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int bc_z1, int mode)
-{
-    constexpr int NB = DES_NODE_BLOCK, CHUNK = CPT * NB;
-    extern __shared__ double sm[];          // [3][CHUNK]
-    const int tid = threadIdx.x;
-    const int n0 = blockIdx.x * NB, n = n0 + tid, N = D.nnode;
-    const int K0 = D.sup_idx[n0], K1 = D.sup_idx[min(n0 + NB, N)];
-    int beg = 0, end = 0;
-    if (n < N) { beg = D.sup_idx[n]; end = D.sup_idx[n + 1]; }
-    double f[3] = {0, 0, 0};
-    for (int kc = K0; kc < K1; kc += CHUNK) {
-        const int len = min(CHUNK, K1 - kc);
-        int ent[CPT];
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            const int i = tid + j * NB;
-            ent[j] = (i < len) ? D.sup_ent[kc + i] : -1;
-        }
-        double t0[CPT], t1[CPT], t2[CPT];
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            if (ent[j] >= 0) {
-                const double *tr = D.fc + DES_FC_OFF(ent[j]);
-                t0[j] = tr[0]; t1[j] = tr[1]; t2[j] = tr[2];
-            }
-        }
-        #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-            const int i = tid + j * NB;
-            if (ent[j] >= 0) { sm[i] = t0[j]; sm[CHUNK + i] = t1[j]; sm[2 * CHUNK + i] = t2[j]; }
-        }
-        __syncthreads();
-        const int a = max(beg, kc) - kc, b = min(end, kc + len) - kc;
-        for (int i = a; i < b; ++i) { f[0] -= sm[i]; f[1] -= sm[CHUNK + i]; f[2] -= sm[2 * CHUNK + i]; }
-        __syncthreads();
-    }
-    if (n >= N) return;
-    const unsigned flag = D.bcflag[n];
-    double4 x = D.xT[n];
-    const double4 v4 = D.vv[n];
-    double v[3] = {v4.x, v4.y, v4.z};
-    if (flag & P.sbc_mask) {
-        const int row = D.sbc_row[n];
-        if (row >= 0) {
-            for (int k = D.sbc_idx[row]; k < D.sbc_idx[row + 1]; ++k) {
-                const int se = D.sbc_ent[k];
-                const double *tr = D.sbc_ftr + size_t(se / 3) * 9 + (se % 3) * 3;
-                f[0] -= tr[0]; f[1] -= tr[1]; f[2] -= tr[2];
-            }
-        }
-    }
-    if (P.has_elastic_foundation && (flag & BOUNDZ0))
-        f[2] -= P.elastic_foundation_constant * (x.z - D.coord0[n].z);
-    #pragma unroll
-    for (int j = 0; j < 3; ++j) {
-        f[j] = damp(P, f[j], v[j]);
-        D.force[size_t(j) * N + n] = f[j];
-    }
-    if (mode & 2) {
-        const double mass = D.mass[n];
-        #pragma unroll
-        for (int j = 0; j < 3; ++j) v[j] += dt * f[j] / mass;
-    }
-    if ((mode & 4) && (flag & BOUND_ANY)) vbc_node(P, flag, v, bc_z1, D.edge_slot, D.edge_vec);
-    if (mode & 6) D.vv[n] = make_double4(v[0], v[1], v[2], 0.0);
-    if (mode & 8) {
-        x.x += v[0] * dt; x.y += v[1] * dt; x.z += v[2] * dt;
-        D.xT[n] = x;
-    }
 }
 
 // ---------------------------------------------------------------------------------------
