@@ -50,6 +50,7 @@ struct DesGpu {
     bool own_stream = true;
     bool seg_rot = false;               // rotation pending for segment 1 of the current step
     int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
+    int pf_elems = DES_PF_DEFAULT;      // L2 prefetch distance of the element kernels (DES_PF_ELEMS overrides)
     long long launches = 0;
     // staging
     void *stage = nullptr; size_t stage_bytes = 0;
@@ -167,6 +168,7 @@ void free_mesh(DesGpu *h)
     h->send_idx = h->recv_idx = h->top_of_node = nullptr;
     h->send_buf = h->recv_buf = nullptr;
     memset(&h->D, 0, sizeof(h->D));
+    h->D.pf = h->pf_elems;
     h->have_mesh = h->have_state = false;
     h->tail_pending = false;
     h->surf_ran = false;
@@ -372,7 +374,9 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
     h->device = device;
     h->hp = *param;
     if (const char *sv = getenv("DES_SCHEDULE")) h->schedule = (atoi(sv) == 1) ? 1 : 2;
+    if (const char *sv = getenv("DES_PF_ELEMS")) h->pf_elems = atoi(sv) > 0 ? atoi(sv) : 0;
     memset(&h->D, 0, sizeof(h->D));
+    h->D.pf = h->pf_elems;
     memset(h->kc_ms, 0, sizeof(h->kc_ms));
     memset(h->kc_n, 0, sizeof(h->kc_n));
     int rc = fill_dev_params(h);

@@ -58,6 +58,14 @@ __device__ __forceinline__ double4 ld256_nc(const void *p)      // read-only in 
                  : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
     return r;
 }
+// L2 prefetch hint (no register, no scoreboard entry): used for the rows a later block streams
+__device__ __forceinline__ void pf_l2(const void *p)
+{
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+}
+#ifndef DES_PF_DEFAULT
+#define DES_PF_DEFAULT 65536
+#endif
 __device__ __forceinline__ double4 ld256(const void *p)
 {
     double4 r;

@@ -58,6 +58,9 @@ struct Dev {
     unsigned long long *maxdh_bits;
     // multi-GPU: 1 for ghost nodes (values received from the owner), NULL on a single GPU
     const unsigned char *ghost;
+    // L2 prefetch distance of the element kernels, in elements (0 = off): thread e asks L2 for
+    // the streamed rows of element e + pf, so that block finds them in L2 instead of HBM
+    int pf;
 };
 
 #define DES_GRID(n, b) (((n) + (b) - 1) / (b))
@@ -363,28 +366,45 @@ k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
     if (e >= D.nelem) return;
     const int nmat = SINGLE ? 1 : P.nmat;
     const int E = D.nelem;
+    // all loads first: the stores of the corrected stress diagonal below would otherwise
+    // fence the coordinate gathers behind the dp_nd gathers (one more dependent round trip)
     const int4 c = D.conn[e];
     double s[6];
     #pragma unroll
     for (int i = 0; i < 6; ++i) s[i] = D.stress[size_t(i) * E + e];
+    const double vol = D.volume[e];
+    Markers mk;
+    if (P.gravity != 0) load_markers(D.elemmarkers, e, nmat, mk);
+    double dp_orig = 0, dpn0 = 0, dpn1 = 0, dpn2 = 0, dpn3 = 0;
+    if (MIXED) {
+        dp_orig = D.dpressure[e];
+        dpn0 = D.ntmp[c.x]; dpn1 = D.ntmp[c.y]; dpn2 = D.ntmp[c.z]; dpn3 = D.ntmp[c.w];
+    }
+    const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
+    if (D.pf) {
+        const int ep = e + D.pf;
+        if (ep < E) {
+            pf_l2(D.conn + ep);
+            pf_l2(D.volume + ep);
+            if (SINGLE) pf_l2(D.elemmarkers + ep);
+            #pragma unroll
+            for (int i = 0; i < 6; ++i) pf_l2(D.stress + size_t(i) * E + ep);
+            if (MIXED) pf_l2(D.dpressure + ep);
+        }
+    }
     if (MIXED) {
         double dp = 0;
-        dp += D.ntmp[c.x]; dp += D.ntmp[c.y]; dp += D.ntmp[c.z]; dp += D.ntmp[c.w];
+        dp += dpn0; dp += dpn1; dp += dpn2; dp += dpn3;
         const double dp_el = dp / 4;
-        const double dp_orig = D.dpressure[e];
         const double ddp = (-dp_orig + dp_el) / 3;
         #pragma unroll
         for (int i = 0; i < 3; ++i) { s[i] += ddp; D.stress[size_t(i) * E + e] = s[i]; }
     }
-    const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
-    const double vol = D.volume[e];
     double sx[4], sy[4], sz[4];
     shape_fn(a0, a1, a2, a3, vol, sx, sy, sz);
 
     double buoy = 0;
     if (P.gravity != 0) {
-        Markers mk;
-        load_markers(D.elemmarkers, e, nmat, mk);
         const double rho = mat_rho(P, nmat, mk, a0.w, a1.w, a2.w, a3.w);
         const double phi = arith_mean(P.porosity, mk.cnt, nmat);
         buoy = (rho * (1 - phi) + 1000.0 * phi) * P.gravity / 4;

@@ -35,22 +35,39 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= D.nelem) return;
     const int nmat = SINGLE ? 1 : P.nmat;
+    // every load of the kernel is issued here, before the first use of any of them: the
+    // mid-kernel store of volume[e] (which may alias, as far as the compiler knows) and the
+    // flag branches otherwise serialise them into five dependent memory round trips
+    // (conn -> xT -> markers -> radiogenic -> vv in the SASS of the previous version)
     const int4 c = D.conn[e];
+    Markers mk;
+    load_markers(D.elemmarkers, e, nmat, mk);
+    double radiogenic = 0, vol = 0;
+    if (head_flags & 1) radiogenic = D.radiogenic[e];
+    if (!(TAIL && (tail_flags & 1))) vol = D.volume[e];
     const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
+    double4 v0 = make_double4(0, 0, 0, 0), v1 = v0, v2 = v0, v3 = v0;
+    if (head_flags & 4) {
+        v0 = ld256_nc(D.vv + c.x); v1 = ld256_nc(D.vv + c.y); v2 = ld256_nc(D.vv + c.z); v3 = ld256_nc(D.vv + c.w);
+    }
 
-    double vol;
+    if (D.pf) {
+        const int ep = e + D.pf;
+        if (ep < D.nelem) {
+            pf_l2(D.conn + ep);
+            if (SINGLE) pf_l2(D.elemmarkers + ep);
+            if (head_flags & 1) pf_l2(D.radiogenic + ep);
+        }
+    }
+
     if (TAIL && (tail_flags & 1)) {
         vol = tet_volume(a0, a1, a2, a3);       // compute_volume, geometry.cxx:180-197
         D.volume[e] = vol;
     }
-    else
-        vol = D.volume[e];
 
     double sx[4], sy[4], sz[4];
     shape_fn(a0, a1, a2, a3, vol, sx, sy, sz);
 
-    Markers mk;
-    load_markers(D.elemmarkers, e, nmat, mk);
     const double rho = mat_rho(P, nmat, mk, a0.w, a1.w, a2.w, a3.w);
 
     double rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -67,7 +84,7 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
         // update_temperature element loop, fields.cxx:210-239
         const double k = arith_mean(P.therm_cond, mk.cnt, nmat);
         const double kv = k * vol;
-        const double rh = D.radiogenic[e] * vol * rho / 4;
+        const double rh = radiogenic * vol * rho / 4;
         const double T[4] = {a0.w, a1.w, a2.w, a3.w};
         #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -81,7 +98,6 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
     if (head_flags & 4) {
         // diagonal of update_strain_rate (fields.cxx:414-476) -> compute_dvoldt element
         // loop (geometry.cxx:217-225)
-        const double4 v0 = ld256_nc(D.vv + c.x), v1 = ld256_nc(D.vv + c.y), v2 = ld256_nc(D.vv + c.z), v3 = ld256_nc(D.vv + c.w);
         double s[3];
         s[0] = 0; s[0] += v0.x * sx[0]; s[0] += v1.x * sx[1]; s[0] += v2.x * sx[2]; s[0] += v3.x * sx[3];
         s[1] = 0; s[1] += v0.y * sy[0]; s[1] += v1.y * sy[1]; s[1] += v2.y * sy[2]; s[1] += v3.y * sy[3];
@@ -111,7 +127,14 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     const int E = D.nelem;
     const int4 c = D.conn[e];
     const double vol = D.volume[e];
-    // the streaming (coalesced) loads are issued before the dependent gathers
+    // the streaming (coalesced) loads are issued before the dependent gathers -- all of them,
+    // including the ones the rheology needs after the strain stores (the compiler cannot
+    // move a load above a store that may alias)
+    Markers mk;
+    load_markers(D.elemmarkers, e, nmat, mk);
+    double pls = 0, vol_old = 1;
+    if (RHEOL == DES_RH_EP || RHEOL == DES_RH_EVP) pls = D.plstrain[e];
+    if (RHEOL == DES_RH_MAXWELL || RHEOL == DES_RH_EVP) vol_old = D.volume_old[e];
     double s[6], es[6];
     #pragma unroll
     for (int i = 0; i < 6; ++i) {
@@ -129,6 +152,21 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
             double dj = 0;
             dj += D.ntmp[c.x]; dj += D.ntmp[c.y]; dj += D.ntmp[c.z]; dj += D.ntmp[c.w];
             edvoldt = dj / 4;
+        }
+        if (D.pf) {
+            const int ep = e + D.pf;
+            if (ep < E) {
+                pf_l2(D.conn + ep);
+                pf_l2(D.volume + ep);
+                if (SINGLE) pf_l2(D.elemmarkers + ep);
+                #pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    pf_l2(D.stress + size_t(i) * E + ep);
+                    pf_l2(D.strain + size_t(i) * E + ep);
+                }
+                if (RHEOL == DES_RH_EP || RHEOL == DES_RH_EVP) pf_l2(D.plstrain + ep);
+                if (RHEOL == DES_RH_MAXWELL || RHEOL == DES_RH_EVP) pf_l2(D.volume_old + ep);
+            }
         }
         T0 = a0.w; T1 = a1.w; T2 = a2.w; T3 = a3.w;
         double sx[4], sy[4], sz[4];
@@ -179,8 +217,6 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     #pragma unroll
     for (int i = 0; i < 6; ++i) D.strain[size_t(i) * E + e] = es[i];
 
-    Markers mk;
-    load_markers(D.elemmarkers, e, nmat, mk);
     const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, nmat);
     const double shearm = harm_mean(P.shear_modulus, mk.cnt, nmat);
     double dpl = 0.;
@@ -192,13 +228,12 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     case DES_RH_MAXWELL: {
         const double visc = mat_visc(P, nmat, mk, T0, T1, T2, T3, s, edot);
         D.viscosity[e] = visc;
-        const double dv = vol / D.volume_old[e] - 1;
+        const double dv = vol / vol_old - 1;
         rh_maxwell(bulkm, shearm, visc, dt, dv, de, s);
         break;
     }
     case DES_RH_EP: {
         double depls = 0, amc, anphi, anpsi, hardn, ten_max;
-        const double pls = D.plstrain[e];
         plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
         rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, s);
         D.plstrain[e] = pls + depls;
@@ -209,14 +244,13 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
         double depls = 0;
         const double visc = mat_visc(P, nmat, mk, T0, T1, T2, T3, s, edot);
         D.viscosity[e] = visc;
-        const double dv = vol / D.volume_old[e] - 1;
+        const double dv = vol / vol_old - 1;
         double sv[6];
         for (int i = 0; i < 6; ++i) sv[i] = s[i];
         rh_maxwell(bulkm, shearm, visc, dt, dv, de, sv);
         const double svII = second_invariant2(sv);
 
         double amc, anphi, anpsi, hardn, ten_max;
-        const double pls = D.plstrain[e];
         plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
         double sp[6];
         for (int i = 0; i < 6; ++i) sp[i] = s[i];
