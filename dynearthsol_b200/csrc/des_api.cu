@@ -424,15 +424,30 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
         LAUNCH(KC_PACK, k_pack_conn, E, 256, E, st, conn);
         D.conn = conn;
         CK(cudaStreamSynchronize(h->stream));
-        int *ent; if ((rc = dalloc(h, &ent, size_t(E) * 4, "sup_ent"))) return rc;
+    }
+    // support -> packed entries, each node's list padded to a multiple of four (sentinel -1)
+    if (m->support_idx[N] != 4 * E) return fail(h, DES_E_ARG, "support_idx[nnode] != 4*nelem");
+    {
+        std::vector<int> pidx(size_t(N) + 1);
+        long long tot = 0;
+        for (int n = 0; n < N; ++n) {
+            pidx[n] = int(tot);
+            tot += (m->support_idx[n + 1] - m->support_idx[n] + 3) & ~3;
+            if (tot >= (1ll << 31)) return fail(h, DES_E_ARG, "padded support list overflows int32");
+        }
+        pidx[N] = int(tot);
+        if ((rc = upload_new(h, &D.sup_idx, pidx.data(), size_t(N) + 1, "sup_idx"))) return rc;
+        if ((rc = ensure_stage(h, (size_t(E) * 8 + size_t(N) + 1) * sizeof(int)))) return rc;
+        int *st = static_cast<int *>(h->stage);
+        int *ent; if ((rc = dalloc(h, &ent, size_t(tot), "sup_ent"))) return rc;
+        CK(cudaMemsetAsync(ent, 0xFF, size_t(tot) * sizeof(int), h->stream));
         if ((rc = h2d(h, st, m->support_arr, size_t(E) * 4))) return rc;
         if ((rc = h2d(h, st + size_t(E) * 4, m->support_lidx, size_t(E) * 4))) return rc;
-        LAUNCH(KC_PACK, k_pack_support, E * 4, 256, E * 4, st, st + size_t(E) * 4, ent);
+        if ((rc = h2d(h, st + size_t(E) * 8, m->support_idx, size_t(N) + 1))) return rc;
+        LAUNCH(KC_PACK, k_pack_support, N, 256, N, st + size_t(E) * 8, D.sup_idx, st, st + size_t(E) * 4, ent);
         D.sup_ent = ent;
         CK(cudaStreamSynchronize(h->stream));
     }
-    if (m->support_idx[N] != 4 * E) return fail(h, DES_E_ARG, "support_idx[nnode] != 4*nelem");
-    if ((rc = upload_new(h, &D.sup_idx, m->support_idx, size_t(N) + 1, "sup_idx"))) return rc;
     if ((rc = upload_new(h, &D.bcflag, m->bcflag, size_t(N), "bcflag"))) return rc;
     {
         int *mk; if ((rc = dalloc(h, &mk, size_t(E) * h->hp.nmat, "elemmarkers"))) return rc;
@@ -467,6 +482,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     { double *r; if ((rc = dalloc(h, &r, E, "radiogenic"))) return rc; D.radiogenic = r;
       CK(cudaMemsetAsync(r, 0, sizeof(double) * E, h->stream)); }
     if ((rc = dalloc(h, &D.ca, size_t(E) * 8, "ca"))) return rc;
+    D.ca_hi = D.ca + size_t(E) * 4;
     if ((rc = dalloc(h, &D.etmp, E, "etmp"))) return rc;
     if ((rc = dalloc(h, &D.fc, size_t(E) * DES_FC_STRIDE, "fc"))) return rc;
     CK(cudaMemsetAsync(D.strain_rate, 0, sizeof(double) * 6 * E, h->stream));

@@ -20,8 +20,9 @@ struct Dev {
     // topology
     const int4 *conn;           // [E]
     const unsigned *bcflag;     // [N]
-    const int *sup_idx;         // [N+1]
-    const int *sup_ent;         // [4E] packed (elem << 2 | local node), ascending elem per node
+    const int *sup_idx;         // [N+1] offsets into sup_ent, each a multiple of 4
+    const int *sup_ent;         // packed (elem << 2 | local node), ascending elem per node; each node's list
+                                // is padded with -1 to a multiple of 4 entries (one 128-bit load per 4)
     const int *elemmarkers;     // [E*nmat]
     // node fields
     double4 *xT;                // {x, y, z, temperature}
@@ -36,7 +37,8 @@ struct Dev {
     double *dpressure, *edvoldt, *viscosity;
     const double *radiogenic;
     // element -> node contribution records
-    double *ca;                 // [E][8] {tdiff0..3, tr(edot)*vol, m, tm, vol}
+    double *ca;                 // [E][4] {tdiff0..3}: T-diffusion contribution per local node
+    double *ca_hi;              // [E][4] {tr(edot)*vol, m, tm, vol}  (both halves: one 256-bit store per element)
     double *etmp;               // [E]    dpressure*vol
     double *fc;                 // [E][4][DES_FC_STRIDE/4] element forces, local node major
     // stress boundary conditions (apply_stress_bcs)
@@ -179,11 +181,11 @@ k_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
         }
     }
 
-    double2 *r = reinterpret_cast<double2 *>(D.ca + size_t(e) * 8);
-    if (HEAD && (head_flags & 1)) { r[0] = make_double2(rec[0], rec[1]); r[1] = make_double2(rec[2], rec[3]); }
-    if (HEAD && TAIL) { r[2] = make_double2(rec[4], rec[5]); r[3] = make_double2(rec[6], rec[7]); }
-    else if (HEAD) { if (head_flags & 4) D.ca[size_t(e) * 8 + 4] = rec[4]; }
-    else if (tail_flags & 2) { D.ca[size_t(e) * 8 + 5] = rec[5]; r[3] = make_double2(rec[6], rec[7]); }
+    double *lo = D.ca + size_t(e) * 4, *hi = D.ca_hi + size_t(e) * 4;
+    if (HEAD && (head_flags & 1)) st256(lo, make_double4(rec[0], rec[1], rec[2], rec[3]));
+    if (HEAD && TAIL) st256(hi, make_double4(rec[4], rec[5], rec[6], rec[7]));
+    else if (HEAD) { if (head_flags & 4) hi[0] = rec[4]; }
+    else if (tail_flags & 2) { hi[1] = rec[5]; hi[2] = rec[6]; hi[3] = rec[7]; }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -202,9 +204,10 @@ k_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
     double vn = 0, m = 0, tm = 0, tdot = 0, dvol = 0;
     for (int k = beg; k < end; ++k) {
         const int ent = D.sup_ent[k];
-        const double *r = D.ca + size_t(ent >> 2) * 8;
-        if (MASS) { vn += r[7]; m += r[5]; tm += r[6]; }
-        if (HEAD) { tdot += r[ent & 3]; dvol += r[4]; }
+        if (ent < 0) break;     // padding
+        const double *lo = D.ca + size_t(ent >> 2) * 4, *r = D.ca_hi + size_t(ent >> 2) * 4;
+        if (MASS) { vn += r[3]; m += r[1]; tm += r[2]; }
+        if (HEAD) { tdot += lo[ent & 3]; dvol += r[0]; }
     }
     if (MASS) {
         D.volume_n[n] = vn;
@@ -348,9 +351,19 @@ k_node_b(const __grid_constant__ Dev D)
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= D.nnode) return;
     const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
+    const double vn = D.volume_n[n];
     double acc = 0;
-    for (int k = beg; k < end; ++k) acc += D.etmp[D.sup_ent[k] >> 2];
-    D.ntmp[n] = acc / D.volume_n[n];
+    const int4 *ents = reinterpret_cast<const int4 *>(D.sup_ent);
+    for (int k = beg >> 2; k < (end >> 2); ++k) {
+        const int4 q = ents[k];
+        const int ent[4] = {q.x, q.y, q.z, q.w};
+        double v[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) if (ent[j] >= 0) v[j] = D.etmp[ent[j] >> 2];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) if (ent[j] >= 0) acc += v[j];
+    }
+    D.ntmp[n] = acc / vn;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -421,9 +434,11 @@ k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
     #pragma unroll
     for (int i = 0; i < 4; ++i) st256(out + 4 * i, make_double4(f[i*3], f[i*3 + 1], f[i*3 + 2], 0.0));
 #else
-    double2 *out = reinterpret_cast<double2 *>(D.fc + size_t(e) * 12);
+    // three 256-bit stores (the 96-byte record is 32-byte aligned): half the L1TEX wavefronts
+    // of six 128-bit stores
+    double *out = D.fc + size_t(e) * 12;
     #pragma unroll
-    for (int i = 0; i < 6; ++i) out[i] = make_double2(f[2*i], f[2*i + 1]);
+    for (int i = 0; i < 3; ++i) st256(out + 4 * i, make_double4(f[4*i], f[4*i + 1], f[4*i + 2], f[4*i + 3]));
 #endif
 }
 
@@ -496,6 +511,7 @@ k_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
         const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
         for (int k = beg; k < end; ++k) {
             const int ent = D.sup_ent[k];
+            if (ent < 0) break;     // padding
             const double *tr = D.fc + DES_FC_OFF(ent);
             f[0] -= tr[0]; f[1] -= tr[1]; f[2] -= tr[2];
         }
@@ -639,7 +655,11 @@ __global__ void k_surf_correct_nodes(const __grid_constant__ Dev D)
     if (i >= D.ntop) return;
     const int nt = D.top_nodes[i];
     double acc = 0.;
-    for (int k = D.sup_idx[nt]; k < D.sup_idx[nt + 1]; ++k) acc += D.volume[D.sup_ent[k] >> 2];
+    for (int k = D.sup_idx[nt]; k < D.sup_idx[nt + 1]; ++k) {
+        const int ent = D.sup_ent[k];
+        if (ent < 0) break;     // padding
+        acc += D.volume[ent >> 2];
+    }
     D.volume_n[nt] = acc;
 }
 
@@ -717,11 +737,13 @@ __global__ void k_pack_conn(int n, const int *soa, int4 *out)
     if (e >= n) return;
     out[e] = make_int4(soa[e], soa[size_t(n) + e], soa[size_t(2) * n + e], soa[size_t(3) * n + e]);
 }
-__global__ void k_pack_support(int n, const int *arr, const int *lidx, int *out)
+// one thread per node: its support entries -> packed, into the padded list (out pre-filled with -1)
+__global__ void k_pack_support(int nnode, const int *idx, const int *pidx, const int *arr, const int *lidx, int *out)
 {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    out[k] = (arr[k] << 2) | lidx[k];
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= nnode) return;
+    const int beg = idx[n], end = idx[n + 1], o = pidx[n] - beg;
+    for (int k = beg; k < end; ++k) out[o + k] = (arr[k] << 2) | lidx[k];
 }
 // which: 0 = xyz from soa, 1 = w from soa[n]
 __global__ void k_pack_vec3(int n, const double *soa, double4 *out)

@@ -104,10 +104,11 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
         s[2] = 0; s[2] += v0.z * sz[0]; s[2] += v1.z * sz[1]; s[2] += v2.z * sz[2]; s[2] += v3.z * sz[3];
         rec[4] = trace3(s) * vol;
     }
-    double2 *r = reinterpret_cast<double2 *>(D.ca + size_t(e) * 8);
-    if (head_flags & 1) { r[0] = make_double2(rec[0], rec[1]); r[1] = make_double2(rec[2], rec[3]); }
-    if (TAIL) { r[2] = make_double2(rec[4], rec[5]); r[3] = make_double2(rec[6], rec[7]); }
-    else if (head_flags & 4) D.ca[size_t(e) * 8 + 4] = rec[4];
+    // two 256-bit stores per element, each contiguous across the warp (8 L1TEX wavefronts per
+    // store instead of the 16 per 128-bit store of an interleaved 64-byte record)
+    if (head_flags & 1) st256(D.ca + size_t(e) * 4, make_double4(rec[0], rec[1], rec[2], rec[3]));
+    if (TAIL) st256(D.ca_hi + size_t(e) * 4, make_double4(rec[4], rec[5], rec[6], rec[7]));
+    else if (head_flags & 4) D.ca_hi[size_t(e) * 4] = rec[4];
 }
 
 // ---------------------------------------------------------------------------------------
@@ -293,30 +294,27 @@ k3_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     if (n >= D.nnode) return;
     const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
     double vn = 0, m = 0, tm = 0, tdot = 0, dvol = 0;
-    int k = beg;
-    for (; k + 4 <= end; k += 4) {
-        int ent[4]; double lo[4]; double4 hi[4];
-        #pragma unroll
-        for (int j = 0; j < 4; ++j) ent[j] = D.sup_ent[k + j];
+    // the support list is padded to a multiple of four entries per node (sentinel -1), so a
+    // trip reads its four entries with ONE 128-bit load
+    const int4 *ents = reinterpret_cast<const int4 *>(D.sup_ent);
+    for (int k = beg >> 2; k < (end >> 2); ++k) {
+        const int4 q = ents[k];
+        const int ent[4] = {q.x, q.y, q.z, q.w};
+        double lo[4]; double4 hi[4];
         #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const double *r = D.ca + size_t(ent[j] >> 2) * 8;
-            lo[j] = r[ent[j] & 3];
-            hi[j] = ld256_nc(r + 4);
+            if (ent[j] >= 0) {
+                lo[j] = D.ca[ent[j]];
+                hi[j] = ld256_nc(D.ca_hi + size_t(ent[j] >> 2) * 4);
+            }
         }
         #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            tdot += lo[j]; dvol += hi[j].x;
-            if (MASS) { m += hi[j].y; tm += hi[j].z; vn += hi[j].w; }
+            if (ent[j] >= 0) {
+                tdot += lo[j]; dvol += hi[j].x;
+                if (MASS) { m += hi[j].y; tm += hi[j].z; vn += hi[j].w; }
+            }
         }
-    }
-    for (; k < end; ++k) {
-        const int ent = D.sup_ent[k];
-        const double *r = D.ca + size_t(ent >> 2) * 8;
-        const double lo = r[ent & 3];
-        const double4 hi = ld256_nc(r + 4);
-        tdot += lo; dvol += hi.x;
-        if (MASS) { m += hi.y; tm += hi.z; vn += hi.w; }
     }
     if (MASS) {
         D.volume_n[n] = vn;
@@ -345,39 +343,39 @@ k3_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     const int N = D.nnode;
     const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
     double f[3] = {0, 0, 0};
-    int k = beg;
+    const int4 *ents = reinterpret_cast<const int4 *>(D.sup_ent);
+    for (int k = beg >> 2; k < (end >> 2); ++k) {
+        const int4 q = ents[k];
+        const int ent[4] = {q.x, q.y, q.z, q.w};
 #if DES_FC_STRIDE == 16
-    for (; k + 4 <= end; k += 4) {
-        int ent[4]; double4 t[4];
+        double4 t[4];
         #pragma unroll
-        for (int j = 0; j < 4; ++j) ent[j] = D.sup_ent[k + j];
+        for (int j = 0; j < 4; ++j) if (ent[j] >= 0) t[j] = ld256_nc(D.fc + DES_FC_OFF(ent[j]));
         #pragma unroll
-        for (int j = 0; j < 4; ++j) t[j] = ld256_nc(D.fc + DES_FC_OFF(ent[j]));
-        #pragma unroll
-        for (int j = 0; j < 4; ++j) { f[0] -= t[j].x; f[1] -= t[j].y; f[2] -= t[j].z; }
-    }
-    for (; k < end; ++k) {
-        const double4 t = ld256_nc(D.fc + DES_FC_OFF(D.sup_ent[k]));
-        f[0] -= t.x; f[1] -= t.y; f[2] -= t.z;
-    }
+        for (int j = 0; j < 4; ++j) if (ent[j] >= 0) { f[0] -= t[j].x; f[1] -= t[j].y; f[2] -= t[j].z; }
 #else
-    for (; k + 4 <= end; k += 4) {
-        int ent[4]; double t0[4], t1[4], t2[4];
-        #pragma unroll
-        for (int j = 0; j < 4; ++j) ent[j] = D.sup_ent[k + j];
+        // a 24-byte entry {fx,fy,fz} of the 96-byte element record always lies in exactly two
+        // aligned 16-byte chunks: two 128-bit loads per entry instead of three 64-bit ones
+        double2 A[4], B[4];
         #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const double *tr = D.fc + DES_FC_OFF(ent[j]);
-            t0[j] = tr[0]; t1[j] = tr[1]; t2[j] = tr[2];
+            if (ent[j] >= 0) {
+                const int l = ent[j] & 3;
+                const double2 *c2 = reinterpret_cast<const double2 *>(D.fc + size_t(ent[j] >> 2) * 12) + ((3 * l) >> 1);
+                A[j] = __ldg(c2); B[j] = __ldg(c2 + 1);
+            }
         }
         #pragma unroll
-        for (int j = 0; j < 4; ++j) { f[0] -= t0[j]; f[1] -= t1[j]; f[2] -= t2[j]; }
-    }
-    for (; k < end; ++k) {
-        const double *tr = D.fc + DES_FC_OFF(D.sup_ent[k]);
-        f[0] -= tr[0]; f[1] -= tr[1]; f[2] -= tr[2];
-    }
+        for (int j = 0; j < 4; ++j) {
+            if (ent[j] >= 0) {
+                const bool odd = ent[j] & 1;
+                f[0] -= odd ? A[j].y : A[j].x;
+                f[1] -= odd ? B[j].x : A[j].y;
+                f[2] -= odd ? B[j].y : B[j].x;
+            }
+        }
 #endif
+    }
     const unsigned flag = D.bcflag[n];
     double4 x = ld256(D.xT + n);
     const double4 v4 = ld256(D.vv + n);

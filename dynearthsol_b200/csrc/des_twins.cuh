@@ -14,7 +14,7 @@ __global__ void k_tw_dvol_elem(const __grid_constant__ Dev D)
     if (e >= D.nelem) return;
     const size_t E = D.nelem;
     const double dj = D.strain_rate[e] + D.strain_rate[E + e] + D.strain_rate[2 * E + e];
-    D.ca[size_t(e) * 8 + 4] = dj * D.volume[e];
+    D.ca_hi[size_t(e) * 4] = dj * D.volume[e];
 }
 
 // compute_edvoldt, geometry.cxx:263-272
@@ -68,7 +68,8 @@ __global__ void k_tw_residual(const __grid_constant__ Dev D, double *acc)
     double l2 = 0;
     if (n < D.nnode) {
         const double num = double(D.nnode) * 3;
-        const int end = D.sup_idx[n + 1];
+        int end = D.sup_idx[n + 1];
+        while (end > D.sup_idx[n] && D.sup_ent[end - 1] < 0) --end;     // padding
         if (end > D.sup_idx[n]) {
             const int ent = D.sup_ent[end - 1];
             const double *tr = D.fc + DES_FC_OFF(ent);
