@@ -731,19 +731,53 @@ k_dt(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, DtParti
 // ---------------------------------------------------------------------------------------
 // layout conversion between the reference's host SoA and the device records
 // ---------------------------------------------------------------------------------------
-__global__ void k_pack_conn(int n, const int *soa, int4 *out)
+// Internal element order: elements are stored sorted by their smallest
+// node index, perm[internal] = caller's element id, einv = its inverse (both NULL when the
+// caller's order is kept).  Everything element-indexed crosses the C-ABI in the caller's order.
+__global__ void k_pack_conn(int n, const int *soa, const int *perm, int4 *out)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
-    out[e] = make_int4(soa[e], soa[size_t(n) + e], soa[size_t(2) * n + e], soa[size_t(3) * n + e]);
+    const size_t o = perm ? perm[e] : e;
+    out[e] = make_int4(soa[o], soa[size_t(n) + o], soa[size_t(2) * n + o], soa[size_t(3) * n + o]);
 }
 // one thread per node: its support entries -> packed, into the padded list (out pre-filled with -1)
-__global__ void k_pack_support(int nnode, const int *idx, const int *pidx, const int *arr, const int *lidx, int *out)
+__global__ void k_pack_support(int nnode, const int *idx, const int *pidx, const int *arr, const int *lidx,
+                               const int *einv, int *out)
 {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= nnode) return;
     const int beg = idx[n], end = idx[n + 1], o = pidx[n] - beg;
-    for (int k = beg; k < end; ++k) out[o + k] = (arr[k] << 2) | lidx[k];
+    for (int k = beg; k < end; ++k) {
+        const int e = einv ? einv[arr[k]] : arr[k];
+        out[o + k] = (e << 2) | lidx[k];
+    }
+}
+// rows of an element field, caller's order -> internal order: out[r][i] = in[r][perm[i]]
+template <class T>
+__global__ void k_rows_to_internal(int n, int rows, const T *in, const int *perm, T *out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const size_t o = perm[i];
+    for (int r = 0; r < rows; ++r) out[size_t(r) * n + i] = in[size_t(r) * n + o];
+}
+// internal order -> caller's order: out[r][o] = in[r][einv[o]]
+template <class T>
+__global__ void k_rows_to_caller(int n, int rows, const T *in, const int *einv, T *out)
+{
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= n) return;
+    const size_t i = einv[o];
+    for (int r = 0; r < rows; ++r) out[size_t(r) * n + o] = in[size_t(r) * n + i];
+}
+// marker counts are [E][nmat] (element-major): out[i][m] = in[perm[i]][m]
+__global__ void k_markers_to_internal(int n, int nmat, const int *in, const int *perm, int *out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const size_t o = perm[i];
+    for (int m = 0; m < nmat; ++m) out[size_t(i) * nmat + m] = in[o * nmat + m];
 }
 // which: 0 = xyz from soa, 1 = w from soa[n]
 __global__ void k_pack_vec3(int n, const double *soa, double4 *out)

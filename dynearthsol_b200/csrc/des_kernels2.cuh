@@ -286,6 +286,8 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
 // when DES_FC_STRIDE == 16.  The L1TEX wavefront count per entry -- what bounded the v1
 // gathers (l1tex 94 % busy, DRAM 28 %) -- drops from 5 to 2 (N-A) and from 3 to 1 (N-C).
 // ---------------------------------------------------------------------------------------
+// (min-blocks launch bounds of 5/6 for the node gathers were measured: 48/40 registers with
+// spills, N-A 0.16 -> 0.38 ms at 6 M tets -- dropped)
 template <bool MASS>
 __global__ void __launch_bounds__(256)
 k3_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int head_flags)
