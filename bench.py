@@ -157,7 +157,16 @@ def run_steps(g, n, dt, t, s):
     return g.run(n, dt, t, s)
 
 
-def reference_cpu(steps, warmup, sample="100k"):
+def read_traffic():
+    """DRAM bytes per element and launch of each kernel, from the committed ncu --set full
+    capture (profiles/r01_v5_traffic.json); None if absent."""
+    p = os.path.join(ROOT, "profiles", "r01_v5_traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p))
+    return None
+
+
+def reference_cpu(steps, warmup, sample="100k", target_seconds=None):
     """The unmodified reference on the host cores, same physics, on a box it can initialise.
     Returns (element_steps_per_s, cores, description).  Runs in a subprocess (the reference
     keeps process-wide state)."""
@@ -174,19 +183,24 @@ def reference_cpu(steps, warmup, sample="100k"):
         "from refharness import Ref\n"
         "r = Ref(%r, workdir=%r)\n"
         "r.step(%d)\n"
-        "t = r.step(%d)\n"
-        "print('RESULT', json.dumps({'t': t, 'nelem': r.int('nelem'), 'nnode': r.int('nnode')}))\n"
-    ) % (os.path.join(ROOT, "tests"), os.path.join(wd, "sample.cfg"), wd, warmup, steps)
+        "n = %d\n"
+        "t = r.step(n)\n"
+        "target = %r\n"
+        "if target:\n"
+        "    n = max(n, min(20000, int(target / (t / n))))   # bounded sample: ~target seconds of CPU work\n"
+        "    t = r.step(n)\n"
+        "print('RESULT', json.dumps({'t': t, 'n': n, 'nelem': r.int('nelem'), 'nnode': r.int('nnode')}))\n"
+    ) % (os.path.join(ROOT, "tests"), os.path.join(wd, "sample.cfg"), wd, warmup, steps, target_seconds)
     cores = os.cpu_count() or 1
     env = dict(os.environ, OMP_NUM_THREADS=str(cores))
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
     for line in out.stdout.splitlines():
         if line.startswith("RESULT"):
             r = json.loads(line[7:])
-            rate = r["nelem"] * steps / r["t"]
+            rate = r["nelem"] * r["n"] / r["t"]
             return rate, cores, ("unmodified reference (g++ -O2 -fopenmp), %d-tet box, same physics, "
-                                 "%d steps after %d warm-up, %d OpenMP threads"
-                                 % (r["nelem"], steps, warmup, cores))
+                                 "%d steps (%.1f s) after %d warm-up, %d OpenMP threads"
+                                 % (r["nelem"], r["n"], r["t"], warmup, cores))
     return None, cores, "reference run failed: " + out.stderr[-200:]
 
 
@@ -275,7 +289,7 @@ def main():
             return
         size = a.size or "50M"
         cpu_steps = max(1, min(K, 20))
-        rate, cores, desc = reference_cpu(cpu_steps, min(W, 3), a.cpu_sample)
+        rate, cores, desc = reference_cpu(cpu_steps, min(W, 3), a.cpu_sample, target_seconds=15.0)
         xl, yl, zl, res = SIZES[size]
         line = {"impl": "reference", "metric": metric, "value": rate, "unit": unit, "n_gpus": a.gpus,
                 "steps": K, "warmup": W, "ms_per_step": None, "higher_is_better": True,
@@ -332,8 +346,17 @@ def main():
                                    "achieved_gbs": ab[key] * E / (avg * 1e-3) / 1e9}
     dom = max(per_kernel, key=lambda k: per_kernel[k]["share"])
     step_alg = alg_bytes_step(r)
+    tr = read_traffic()
+    traffic = None
+    if tr:
+        for key, v in tr["dram_bytes_per_elem"].items():
+            if key in per_kernel:
+                per_kernel[key]["dram_bytes_per_elem_ncu"] = v
+        if dom in tr["dram_bytes_per_elem"]:
+            traffic = tr["dram_bytes_per_elem"][dom] * E      # bytes per launch, scaled from the 6M capture
     roofline = {"bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["achieved_gbs"], "peak": peak,
-                "unit": "GB/s", "frac": per_kernel[dom]["achieved_gbs"] / peak, "traffic": None,
+                "unit": "GB/s", "frac": per_kernel[dom]["achieved_gbs"] / peak, "traffic": traffic,
+                "traffic_source": tr["source"] if tr else None,
                 "peak_source": peak_src,
                 "step": {"alg_bytes_per_elem_step": step_alg, "achieved_gbs": value * step_alg / 1e9,
                          "frac": value * step_alg / 1e9 / peak},
@@ -364,7 +387,7 @@ def main():
     # ---- CPU baseline: the unmodified reference on the host cores -----------------------
     cpu = None
     if not a.no_cpu:
-        rate, cores, desc = reference_cpu(10, 2, a.cpu_sample)
+        rate, cores, desc = reference_cpu(10, 2, a.cpu_sample, target_seconds=10.0)
         cpu = {"value": rate, "unit": unit, "cores": cores, "kind": "reference", "sample": desc}
 
     sampler.join(timeout=2)
