@@ -58,6 +58,12 @@ __device__ __forceinline__ double4 ld256_nc(const void *p)      // read-only in 
                  : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
     return r;
 }
+__device__ __forceinline__ double ld64_v(const double *p)       // ordered among the volatile loads
+{
+    double r;
+    asm volatile("ld.global.f64 %0, [%1];" : "=d"(r) : "l"(p));
+    return r;
+}
 // L2 prefetch hint (no register, no scoreboard entry): used for the rows a later block streams
 __device__ __forceinline__ void pf_l2(const void *p)
 {

@@ -27,8 +27,23 @@
 // E-A (v2)
 // ---------------------------------------------------------------------------------------
 #define DES_EA_BLOCK 128      // measured: 128-thread blocks are 7 % faster than 256 here (72 registers)
+// Measured on the 50M box (profiles/experiments/): requesting the velocities only after the
+// shape functions are done (their registers reuse the coordinates') and asking for 6 resident
+// blocks (80 registers, 8 bytes spilled) takes E-A from 1.63 to 1.50 ms; 7 blocks (72
+// registers, 56 bytes spilled) is slower (1.84 ms), and so is the bound without the late loads.
+#ifndef DES_EA_LATE
+#define DES_EA_LATE 1
+#endif
+#ifndef DES_EA_MINB
+#define DES_EA_MINB 6
+#endif
+#if DES_EA_MINB > 0
+#define DES_EA_BOUNDS __launch_bounds__(DES_EA_BLOCK, DES_EA_MINB)
+#else
+#define DES_EA_BOUNDS __launch_bounds__(DES_EA_BLOCK)
+#endif
 template <bool SINGLE, bool TAIL>
-__global__ void __launch_bounds__(DES_EA_BLOCK)
+__global__ void DES_EA_BOUNDS
 k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int tail_flags, int head_flags)
 {
     // tail_flags: 1 volume, 2 mass contributions;  head_flags: 1 T-diffusion, 4 tr(edot)*vol
@@ -47,9 +62,11 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
     if (!(TAIL && (tail_flags & 1))) vol = D.volume[e];
     const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
     double4 v0 = make_double4(0, 0, 0, 0), v1 = v0, v2 = v0, v3 = v0;
+#if !DES_EA_LATE
     if (head_flags & 4) {
         v0 = ld256_nc(D.vv + c.x); v1 = ld256_nc(D.vv + c.y); v2 = ld256_nc(D.vv + c.z); v3 = ld256_nc(D.vv + c.w);
     }
+#endif
 
     if (D.pf) {
         const int ep = e + D.pf;
@@ -68,6 +85,12 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
     double sx[4], sy[4], sz[4];
     shape_fn(a0, a1, a2, a3, vol, sx, sy, sz);
 
+#if DES_EA_LATE
+    // the velocities are requested when the coordinates' registers are free again
+    if (head_flags & 4) {
+        v0 = ld256_nc(D.vv + c.x); v1 = ld256_nc(D.vv + c.y); v2 = ld256_nc(D.vv + c.z); v3 = ld256_nc(D.vv + c.w);
+    }
+#endif
     const double rho = mat_rho(P, nmat, mk, a0.w, a1.w, a2.w, a3.w);
 
     double rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -118,8 +141,22 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
 // The coordinates, velocities and volume the rotation needs (end of step n-1) are the ones
 // the strain rate of step n needs, so one shape-function evaluation serves both.
 // ---------------------------------------------------------------------------------------
+// Measured on the 50M box: stress and strain requested after the strain rate and spin are
+// computed (116 -> 96 registers) and 6 resident blocks (80 registers, 8 bytes spilled): E-B
+// 3.69 -> 3.44 ms; 7 and 8 blocks spill (3.98, 4.78 ms).
+#ifndef DES_EB_LATE
+#define DES_EB_LATE 1
+#endif
+#ifndef DES_EB_MINB
+#define DES_EB_MINB 6
+#endif
+#if DES_EB_MINB > 0
+#define DES_EB_BOUNDS __launch_bounds__(128, DES_EB_MINB)
+#else
+#define DES_EB_BOUNDS __launch_bounds__(128)
+#endif
 template <bool SINGLE, bool ROT, int RHEOL>
-__global__ void __launch_bounds__(128)
+__global__ void DES_EB_BOUNDS
 k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -137,11 +174,13 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     if (RHEOL == DES_RH_EP || RHEOL == DES_RH_EVP) pls = D.plstrain[e];
     if (RHEOL == DES_RH_MAXWELL || RHEOL == DES_RH_EVP) vol_old = D.volume_old[e];
     double s[6], es[6];
+#if !DES_EB_LATE
     #pragma unroll
     for (int i = 0; i < 6; ++i) {
         s[i] = D.stress[size_t(i) * E + e];
         es[i] = D.strain[size_t(i) * E + e];
     }
+#endif
 
     double edot[6], w3 = 0, w4 = 0, w5 = 0;
     double T0, T1, T2, T3;
@@ -199,6 +238,15 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
         for (int i = 0; i < 4; ++i) edot[5] += 0.5 * (vy[i] * sz[i] + vz[i] * sy[i]);
     }
 
+#if DES_EB_LATE
+    // stress and strain are requested only now (volatile: the order is kept), when the 64
+    // registers of the node records are free again; the rows were prefetched into L2
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        s[i] = ld64_v(D.stress + size_t(i) * E + e);
+        es[i] = ld64_v(D.strain + size_t(i) * E + e);
+    }
+#endif
     if (ROT) {
         jaumann3(s, dt_rot, w3, w4, w5);
         jaumann3(es, dt_rot, w3, w4, w5);
