@@ -1,6 +1,7 @@
 // See des_bridge.hpp.  Compiled with the reference's flags (-DTHREED -DSOA) against its headers.
 #include <cstdio>
 #include <cstring>
+#include <iostream>
 #include <string>
 #include <vector>
 
@@ -8,6 +9,7 @@
 #include "parameters.hpp"
 #include "matprops.hpp"
 #include "markerset.hpp"
+#include "output.hpp"
 #include "des_bridge.hpp"
 
 #ifndef THREED
@@ -20,6 +22,7 @@ struct DesBridge {
     std::string err;
     std::vector<int> flat_markers;
     std::vector<std::vector<int> > flat_facets;
+    double avg_time0 = 0;       // Output::time0 of the running averaging interval
 };
 
 namespace {
@@ -252,6 +255,73 @@ int des_bridge_markers_changed(DesBridge *b, const Param &param, const Variables
     flatten_markers(b, param, var);
     int rc = des_gpu_upload_elemmarkers(b->h, b->flat_markers.data());
     if (rc) return fail(b, rc, "upload_elemmarkers");
+    return 0;
+}
+
+int des_bridge_bad_mesh_quality(DesBridge *b, const Param &param, const Variables &var,
+                                int &index, double &min_quality)
+{
+    DesQualityParam qp;
+    qp.smallest_size = param.mesh.smallest_size;
+    qp.resolution = param.mesh.resolution;
+    qp.max_boundary_distortion = param.mesh.max_boundary_distortion;
+    qp.min_quality = param.mesh.min_quality;
+    qp.xlength = param.mesh.xlength; qp.ylength = param.mesh.ylength; qp.zlength = param.mesh.zlength;
+    qp.remeshing_option = param.mesh.remeshing_option;
+    DesQuality q;
+    int rc = des_gpu_mesh_quality(b->h, &qp, &q);
+    if (rc) { fail(b, rc, "mesh_quality"); return -1; }
+    const int code = des_quality_verdict(&qp, &q, &index, &min_quality);
+    // the reference's diagnostics (remeshing.cxx:2769, 2789, 2804-2826, 2850-2855)
+    if (code == 3)
+        std::cout << "    The size of element #" << index << " is too small.\n";
+    else if (code == 2 && q.first_bottom_node >= 0)
+        std::cout << "    Node #" << index << " is too far from the bottm: z = " << q.bottom_value << "\n";
+    else if (code == 2) {
+        const uint flag = (*var.bcflag)[index];
+        const char *side = (flag & BOUNDX0) ? "x0 side: x = " : (flag & BOUNDX1) ? "x1 side: x = " :
+                           (flag & BOUNDY0) ? "y0 side: y = " : "y1 side: y = ";
+        std::cout << "    Node #" << index << " is too far from the " << side << q.side_value << "\n";
+    }
+    else if (code == 1) {
+        std::cout << "    Element #" << index << " has mesh quality = " << min_quality << " (bcflag: ";
+        for (int i = 0; i < NODES_PER_ELEM; i++) {
+            std::cout << (*var.bcflag)[(*var.connectivity)[index][i]];
+            std::cout << (i < NODES_PER_ELEM - 1 ? ", " : ").\n");
+        }
+    }
+    return code;
+}
+
+int des_bridge_average_fields(DesBridge *b, const Param &param, const Variables &var)
+{
+    const int interval = param.mesh.quality_check_step_interval;    // Output::average_interval
+    const int first = (var.steps % interval == 1);
+    if (first) b->avg_time0 = var.time;
+    int rc = des_gpu_average_fields(b->h, first);
+    if (rc) return fail(b, rc, "average_fields");
+    return 0;
+}
+
+int des_bridge_flush_averages(DesBridge *b, const Param &param, Variables &var)
+{
+    // Output keeps time0 / coord0 / strain0 / stress_avg / delta_plstrain_avg private.  Its own
+    // first-step branch (output.cxx:317-339) copies exactly those five from `var`, so it is
+    // shown a `var` whose time, coord, strain, stress and delta_plstrain ARE the accumulators.
+    array_t coord0(var.nnode);
+    tensor_t strain0(var.nelem), stress_avg(var.nelem);
+    double_vec dpl(var.nelem);
+    int rc = des_gpu_download_averages(b->h, coord0.data(), strain0.data(), stress_avg.data(), dpl.data());
+    if (rc) return fail(b, rc, "download_averages");
+    array_t *coord = var.coord; tensor_t *strain = var.strain, *stress = var.stress;
+    double_vec *delta_plstrain = var.delta_plstrain;
+    const double time = var.time; const int steps = var.steps;
+    var.coord = &coord0; var.strain = &strain0; var.stress = &stress_avg; var.delta_plstrain = &dpl;
+    var.time = b->avg_time0;
+    var.steps = param.mesh.quality_check_step_interval + 1;     // steps % average_interval == 1
+    var.output->average_fields(var);
+    var.coord = coord; var.strain = strain; var.stress = stress; var.delta_plstrain = delta_plstrain;
+    var.time = time; var.steps = steps;
     return 0;
 }
 

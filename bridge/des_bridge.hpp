@@ -35,6 +35,16 @@ double des_bridge_compute_dt(DesBridge *b, const Param &param, Variables &var);
 int des_bridge_download(DesBridge *b, Variables &var, int what);
 // elemmarkers changed on the host (phase_changes, surface markers): dynearthsol.cxx:887
 int des_bridge_markers_changed(DesBridge *b, const Param &param, const Variables &var);
+// bad_mesh_quality (dynearthsol.cxx:942; remeshing.cxx:2752-2866) from device reductions: same
+// return code, index, min_quality and diagnostic line as the reference, no field download
+int des_bridge_bad_mesh_quality(DesBridge *b, const Param &param, const Variables &var,
+                                int &index, double &min_quality);
+// Output::average_fields (dynearthsol.cxx:903; output.cxx:312-352) with the accumulators kept
+// on the device: replaces the per-step download of stress and delta_plstrain
+int des_bridge_average_fields(DesBridge *b, const Param &param, const Variables &var);
+// before Output::write on a frame step: hands the device accumulators to the Output object
+// (through its own average_fields, so output.cxx stays untouched)
+int des_bridge_flush_averages(DesBridge *b, const Param &param, Variables &var);
 const char *des_bridge_last_error(const DesBridge *b);
 void des_bridge_destroy(DesBridge *b);
 

@@ -96,9 +96,9 @@ int main(int argc, const char* argv[])
         }
 
         if (param.sim.is_outputting_averaged_fields) {
-            // [B200] average_fields reads stress and delta_plstrain every step (output.cxx:312)
-            des_bridge_download(gpu, var, DES_DL_OUTPUT);
-            var.output->average_fields(var);
+            // [B200] var.output->average_fields(var);   (dynearthsol.cxx:903) -- the running sums of
+            // stress and delta_plstrain stay on the device, nothing crosses PCIe here
+            if (des_bridge_average_fields(gpu, param, var)) return 1;
         }
 
         if (( (param.sim.output_step_interval != std::numeric_limits<int>::max() &&
@@ -114,6 +114,8 @@ int main(int argc, const char* argv[])
             ) {
                 // [B200] bring the output fields back into Variables before Output::write
                 des_bridge_download(gpu, var, DES_DL_ALL);
+                if (param.sim.is_outputting_averaged_fields)
+                    if (des_bridge_flush_averages(gpu, param, var)) return 1;
                 if (next_regular_frame % param.sim.checkpoint_frame_interval == 0)
                     var.output->write_checkpoint(param, var);
                 var.output->write(var);
@@ -125,10 +127,11 @@ int main(int argc, const char* argv[])
         if (var.steps % param.mesh.quality_check_step_interval == 0) {
             double min_quality = 1.0;
             if (param.control.has_moving_mesh) {
-                // [B200] bad_mesh_quality reads coord and volume on the host
-                des_bridge_download(gpu, var, DES_DL_GEOMETRY);
+                // [B200] quality_is_bad = bad_mesh_quality(param, var, bad_quality_index, min_quality);
+                // (dynearthsol.cxx:942) -- its loops over volume, coord and bcflag run on the device
                 int quality_is_bad, bad_quality_index;
-                quality_is_bad = bad_mesh_quality(param, var, bad_quality_index, min_quality);
+                quality_is_bad = des_bridge_bad_mesh_quality(gpu, param, var, bad_quality_index, min_quality);
+                if (quality_is_bad < 0) return 1;
                 if (quality_is_bad) {
                     // [B200] full state to the host, host remesh, full re-upload (cost reported)
                     int64_t t0 = get_nanoseconds();

@@ -99,6 +99,21 @@ class DesDtReductions(C.Structure):
                 ("max_surf_vel", C.c_double)]
 
 
+class DesQualityParam(C.Structure):
+    """Param.mesh members bad_mesh_quality reads (remeshing.cxx:2752-2866)."""
+    _fields_ = [("smallest_size", C.c_double), ("resolution", C.c_double),
+                ("max_boundary_distortion", C.c_double), ("min_quality", C.c_double),
+                ("xlength", C.c_double), ("ylength", C.c_double), ("zlength", C.c_double),
+                ("remeshing_option", C.c_int)]
+
+
+class DesQuality(C.Structure):
+    _fields_ = [("first_small_elem", C.c_int), ("first_bottom_node", C.c_int),
+                ("first_side_node", C.c_int), ("worst_elem", C.c_int),
+                ("worst_quality", C.c_double), ("bottom_value", C.c_double),
+                ("side_value", C.c_double)]
+
+
 # every symbol include/des_gpu.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
     "des_gpu_create", "des_gpu_destroy", "des_gpu_last_error", "des_gpu_upload_mesh",
@@ -115,6 +130,8 @@ ABI_SYMBOLS = [
     "des_gpu_event_record", "des_gpu_event_elapsed_ms",
     "des_gpu_step_segment", "des_gpu_set_stream", "des_gpu_set_halo", "des_gpu_halo_buffers",
     "des_gpu_halo_width", "des_gpu_halo_pack", "des_gpu_halo_unpack",
+    "des_gpu_mesh_quality", "des_quality_verdict", "des_gpu_average_fields",
+    "des_gpu_download_averages",
 ]
 
 _lib = None
@@ -168,7 +185,12 @@ def load_library():
     L.des_gpu_halo_unpack.argtypes = [H, C.c_int]
     L.des_host_build_support.argtypes = [C.c_int, C.c_int, _IP, _IP, _IP, _IP]
     L.des_abi_sizeof.argtypes = [C.c_int]
-    for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions)):
+    L.des_gpu_mesh_quality.argtypes = [H, C.POINTER(DesQualityParam), C.POINTER(DesQuality)]
+    L.des_quality_verdict.argtypes = [C.POINTER(DesQualityParam), C.POINTER(DesQuality),
+                                      C.POINTER(C.c_int), _DP]
+    L.des_gpu_average_fields.argtypes = [H, C.c_int]
+    L.des_gpu_download_averages.argtypes = [H, _DP, _DP, _DP, _DP]
+    for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions, DesQualityParam, DesQuality)):
         if L.des_abi_sizeof(i) != C.sizeof(st):
             raise ImportError("ABI mismatch: %s is %d bytes in the library, %d in core.py"
                               % (st.__name__, L.des_abi_sizeof(i), C.sizeof(st)))
@@ -405,6 +427,30 @@ class DesGpu:
         if not dt > 0:
             raise DesError(11, "dt <= 0")
         return dt, vmag.value, r
+
+    def mesh_quality(self, **mesh_param):
+        """bad_mesh_quality (remeshing.cxx:2752) on the device: returns (code, index, min_quality,
+        DesQuality); min_quality is None when the reference would not have written it."""
+        qp = DesQualityParam(**mesh_param)
+        q = DesQuality()
+        self._ck(self.lib.des_gpu_mesh_quality(self.h, C.byref(qp), C.byref(q)))
+        idx = C.c_int(-12345)
+        mq = C.c_double(float("nan"))
+        code = self.lib.des_quality_verdict(C.byref(qp), C.byref(q), C.byref(idx), C.byref(mq))
+        mqv = None if mq.value != mq.value else mq.value
+        return code, (None if idx.value == -12345 else idx.value), mqv, q
+
+    def average_fields(self, first):
+        """Output::average_fields (output.cxx:312) with device-resident accumulators."""
+        self._ck(self.lib.des_gpu_average_fields(self.h, 1 if first else 0))
+
+    def download_averages(self):
+        """(coord0 [3N], strain0 [6E], stress_avg [6E], delta_plstrain_avg [E]) as the reference lays
+        them out."""
+        N, E = self.nnode, self.nelem
+        out = [np.empty(3 * N), np.empty(6 * E), np.empty(6 * E), np.empty(E)]
+        self._ck(self.lib.des_gpu_download_averages(self.h, *[_ptr(a, C.c_double) for a in out]))
+        return out
 
     def sync(self):
         self._ck(self.lib.des_gpu_sync(self.h))

@@ -6,6 +6,7 @@
 #include <cstring>
 #include <cmath>
 #include <cfloat>
+#include <climits>
 #include <map>
 #include <string>
 #include <unordered_map>
@@ -14,6 +15,7 @@
 #include <limits>
 
 #include "des_kernels2.cuh"
+#include "des_aux.cuh"
 
 namespace {
 
@@ -61,6 +63,10 @@ struct DesGpu {
     // staging
     void *stage = nullptr; size_t stage_bytes = 0;
     DtPartial *dt_partials = nullptr; int dt_blocks = 0;
+    QPartial *q_partials = nullptr; int *q_nodes = nullptr;     // des_gpu_mesh_quality
+    // Output::average_fields accumulators (mesh-lifetime allocations, internal element order)
+    double *avg_coord0 = nullptr, *avg_strain0 = nullptr, *avg_stress = nullptr, *avg_dpl = nullptr;
+    bool avg_valid = false;
     // timing
     bool timing = false;
     std::vector<EvPair> ev_pool; size_t ev_used = 0;
@@ -173,6 +179,8 @@ void free_mesh(DesGpu *h)
     h->nsend = h->nrecv = 0;
     h->send_idx = h->recv_idx = h->top_of_node = nullptr;
     h->send_buf = h->recv_buf = nullptr;
+    h->avg_coord0 = h->avg_strain0 = h->avg_stress = h->avg_dpl = nullptr;
+    h->avg_valid = false;
     h->eperm = h->einv = nullptr;
     h->h_einv.clear();
     memset(&h->D, 0, sizeof(h->D));
@@ -404,6 +412,8 @@ int des_gpu_destroy(DesGpu *h)
     free_mesh(h);
     if (h->stage) cudaFree(h->stage);
     if (h->dt_partials) cudaFree(h->dt_partials);
+    if (h->q_partials) cudaFree(h->q_partials);
+    if (h->q_nodes) cudaFree(h->q_nodes);
     for (auto &p : h->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto &e : h->user_ev) if (e) cudaEventDestroy(e);
     if (h->stream && h->own_stream) cudaStreamDestroy(h->stream);
@@ -903,6 +913,134 @@ double des_dt_from_reductions(const DesParam *p, const DesDtReductions *r, doubl
     return dt;
 }
 
+// ---- bad_mesh_quality / average_fields on the device ----------
+
+int des_gpu_mesh_quality(DesGpu *h, const DesQualityParam *qp, DesQuality *out)
+{
+    if (!h || !qp || !out) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    CK(cudaSetDevice(h->device));
+    int rc = flush_tail(h);     // bad_mesh_quality reads the volume compute_volume stored
+    if (rc) return rc;
+    const int nb = h->dt_blocks;
+    if (!h->q_partials) CK(cudaMalloc(&h->q_partials, sizeof(QPartial) * nb));
+    if (!h->q_nodes) CK(cudaMalloc(&h->q_nodes, sizeof(int) * 2));
+    // remeshing.cxx:2764 (sizefactor = 0.118 in 3D, mesh.cxx:63) and geometry.cxx:1893
+    const double smallest_vol = qp->smallest_size * 0.118 * std::pow(qp->resolution, 3);
+    const double normf = 216 * std::sqrt(3);
+    const int ro = qp->remeshing_option;
+    const int check_bottom = (ro == 1 || ro == 2 || ro == 11 || ro == 13);
+    const int check_sides = (ro == 13);
+    const double dist = qp->max_boundary_distortion * qp->resolution;
+    CK(cudaMemsetAsync(h->q_nodes, 0x7f, sizeof(int) * 2, h->stream));      // 0x7f7f7f7f > any id
+    LAUNCH_G(KC_DT, k_quality_elems, nb, 256, 0, h->D, h->eperm, smallest_vol, normf, h->q_partials);
+    if (check_bottom || check_sides)
+        LAUNCH(KC_DT, k_quality_nodes, h->D.nnode, 256, h->D, -qp->zlength, dist, qp->xlength, qp->ylength,
+               check_bottom, check_sides, h->q_nodes);
+    std::vector<QPartial> part(nb);
+    int nodes[2];
+    CK(cudaMemcpyAsync(part.data(), h->q_partials, sizeof(QPartial) * nb, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(nodes, h->q_nodes, sizeof(nodes), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    QPartial r = part[0];
+    for (int i = 1; i < nb; ++i) {
+        if (part[i].q < r.q || (part[i].q == r.q && part[i].worst < r.worst)) { r.q = part[i].q; r.worst = part[i].worst; }
+        r.small = std::min(r.small, part[i].small);
+    }
+    out->first_small_elem = (r.small == INT_MAX) ? -1 : r.small;
+    out->worst_elem = r.worst;
+    out->worst_quality = r.q;
+    out->first_bottom_node = (nodes[0] >= h->D.nnode) ? -1 : nodes[0];
+    out->first_side_node = (nodes[1] >= h->D.nnode) ? -1 : nodes[1];
+    out->bottom_value = out->side_value = 0;
+    double4 x;
+    if (out->first_bottom_node >= 0) {
+        CK(cudaMemcpy(&x, h->D.xT + out->first_bottom_node, sizeof(x), cudaMemcpyDeviceToHost));
+        out->bottom_value = x.z;
+    }
+    if (out->first_side_node >= 0) {
+        unsigned flag;
+        CK(cudaMemcpy(&x, h->D.xT + out->first_side_node, sizeof(x), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&flag, h->D.bcflag + out->first_side_node, sizeof(flag), cudaMemcpyDeviceToHost));
+        out->side_value = (flag & (BOUNDX0 | BOUNDX1)) ? x.x : x.y;
+    }
+    return DES_OK;
+}
+
+// remeshing.cxx:2766-2866: tiny element (3), bottom / side node (2), distortion (1), else 0
+int des_quality_verdict(const DesQualityParam *qp, const DesQuality *q, int *index, double *min_quality)
+{
+    if (q->first_small_elem >= 0) { if (index) *index = q->first_small_elem; return 3; }
+    if (q->first_bottom_node >= 0) { if (index) *index = q->first_bottom_node; return 2; }
+    if (qp->remeshing_option == 13) {
+        if (index) *index = q->first_side_node;     // the reference leaves -1 here when none is bad
+        if (q->first_side_node >= 0) return 2;
+    }
+    const double qq = std::pow(q->worst_quality, 1.0 / 3);
+    if (min_quality) *min_quality = qq;
+    if (qq < qp->min_quality) { if (index) *index = q->worst_elem; return 1; }
+    return 0;
+}
+
+int des_gpu_average_fields(DesGpu *h, int first)
+{
+    if (!h) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    CK(cudaSetDevice(h->device));
+    int rc = flush_tail(h);     // average_fields sees the stress AFTER rotate_stress
+    if (rc) return rc;
+    Dev &D = h->D;
+    const size_t N = D.nnode, E = D.nelem;
+    if (!h->avg_coord0) {
+        if ((rc = dalloc(h, &h->avg_coord0, N * 3, "avg_coord0"))) return rc;
+        if ((rc = dalloc(h, &h->avg_strain0, E * 6, "avg_strain0"))) return rc;
+        if ((rc = dalloc(h, &h->avg_stress, E * 6, "avg_stress"))) return rc;
+        if ((rc = dalloc(h, &h->avg_dpl, E, "avg_dpl"))) return rc;
+    }
+    if (first) {
+        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, h->avg_coord0);
+        CK(cudaMemcpyAsync(h->avg_strain0, D.strain, E * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->avg_stress, D.stress, E * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->avg_dpl, D.delta_plstrain, E * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        h->avg_valid = true;
+    } else {
+        if (!h->avg_valid) return fail(h, DES_E_STATE, "average_fields: no snapshot in this interval");
+        const size_t n6 = E * 6;
+        { LaunchScope ls(h, KC_PACK);
+          k_avg_accumulate<<<unsigned((n6 + 255) / 256), 256, 0, h->stream>>>(n6, D.stress, h->avg_stress); }
+        { LaunchScope ls(h, KC_PACK);
+          k_avg_accumulate<<<unsigned((E + 255) / 256), 256, 0, h->stream>>>(E, D.delta_plstrain, h->avg_dpl); }
+    }
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
+int des_gpu_download_averages(DesGpu *h, double *coord0, double *strain0, double *stress_avg, double *dpl_avg)
+{
+    if (!h) return DES_E_ARG;
+    if (!h->have_mesh || !h->avg_valid) return fail(h, DES_E_STATE, "no averaged fields on the device");
+    CK(cudaSetDevice(h->device));
+    const size_t N = h->D.nnode, E = h->D.nelem;
+    int rc;
+    if ((rc = ensure_stage(h, (h->eperm ? E * 6 : size_t(1)) * sizeof(double)))) return rc;
+    double *st = static_cast<double *>(h->stage);
+    if (coord0) CK(cudaMemcpyAsync(coord0, h->avg_coord0, N * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    struct { double *dst; const double *src; int rows; } f[3] = {
+        {strain0, h->avg_strain0, 6}, {stress_avg, h->avg_stress, 6}, {dpl_avg, h->avg_dpl, 1}};
+    for (auto &x : f) {
+        if (!x.dst) continue;
+        const double *src = x.src;
+        if (h->eperm) {
+            LAUNCH(KC_PACK, k_rows_to_caller<double>, int(E), 256, int(E), x.rows, x.src, h->einv, st);
+            src = st;
+        }
+        CK(cudaMemcpyAsync(x.dst, src, E * x.rows * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        if (h->eperm) CK(cudaStreamSynchronize(h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    return DES_OK;
+}
+
 // ---- multi-GPU ghost exchange -------------------------------------------------------------
 int des_gpu_set_stream(DesGpu *h, void *stream, int own)
 {
@@ -1006,6 +1144,8 @@ int des_abi_sizeof(int which)
     case 1: return int(sizeof(DesMesh));
     case 2: return int(sizeof(DesState));
     case 3: return int(sizeof(DesDtReductions));
+    case 4: return int(sizeof(DesQualityParam));
+    case 5: return int(sizeof(DesQuality));
     default: return -1;
     }
 }

@@ -196,6 +196,41 @@ double des_dt_from_reductions(const DesParam *param, const DesDtReductions *r,
                               double *max_global_vel_mag);
 int des_gpu_sync(DesGpu *h);
 
+/* ---- host touch points of the step loop kept on the device -- */
+/* bad_mesh_quality (dynearthsol.cxx:942; remeshing.cxx:2752-2866): the members of Param.mesh
+ * it reads ... */
+typedef struct DesQualityParam {
+    double smallest_size, resolution, max_boundary_distortion, min_quality;
+    double xlength, ylength, zlength;
+    int remeshing_option;
+} DesQualityParam;
+/* ... and what its loops find.  Ids are the caller's; -1 = none.  `value` members are the
+ * coordinate the reference prints for the offending node. */
+typedef struct DesQuality {
+    int first_small_elem;       /* lowest e with volume[e] < smallest_vol (return 3) */
+    int first_bottom_node;      /* lowest bottom node too far from -zlength (return 2) */
+    int first_side_node;        /* remeshing_option 13: lowest side node off its plane (return 2) */
+    int worst_elem;             /* worst_elem_quality's argmin (first minimum), geometry.cxx:1914 */
+    double worst_quality;       /* its elem_quality, BEFORE the cube root of remeshing.cxx:2845 */
+    double bottom_value, side_value;
+} DesQuality;
+/* device reductions only; no field leaves the GPU */
+int des_gpu_mesh_quality(DesGpu *h, const DesQualityParam *qp, DesQuality *out);
+/* the decision ladder of bad_mesh_quality on those reductions (host libm for the cube root):
+ * returns 0..3 like the reference, sets index and min_quality the same way (min_quality is
+ * only written when the ladder reaches the distortion check) */
+int des_quality_verdict(const DesQualityParam *qp, const DesQuality *q, int *index, double *min_quality);
+
+/* Output::average_fields (dynearthsol.cxx:903; output.cxx:312-352) with device-resident
+ * accumulators.  first != 0 (steps % average_interval == 1): snapshot coord, strain, stress,
+ * delta_plstrain; otherwise stress_avg += stress, delta_plstrain_avg += delta_plstrain. */
+int des_gpu_average_fields(DesGpu *h, int first);
+/* D->H of the accumulators in the reference's layouts ([3*nnode], [6*nelem], [6*nelem],
+ * [nelem]); NULL members are skipped.  DES_E_STATE if no snapshot was taken since the mesh
+ * was uploaded. */
+int des_gpu_download_averages(DesGpu *h, double *coord0, double *strain0, double *stress_avg,
+                              double *delta_plstrain_avg);
+
 /* ---- fine-grained twins of the reference calls (PT loop dynearthsol.cxx:803-864,
  * isostasy_adjustment :506-539, remeshing.cxx:3133-3168; also the per-function parity
  * tests).  Same device state; each is the un-fused reference loop nest. --------------- */
@@ -245,7 +280,7 @@ int des_gpu_halo_unpack(DesGpu *h, int phase);
 int des_host_build_support(int nnode, int nelem, const int *connectivity,
                            int *idx, int *arr, int *lidx);
 /* sizeof() of the ABI structs as compiled, so a foreign-language binding can verify its
- * own layout: which = 0 DesParam, 1 DesMesh, 2 DesState, 3 DesDtReductions */
+ * own layout: which = 0 DesParam, 1 DesMesh, 2 DesState, 3 DesDtReductions, 4 DesQualityParam, 5 DesQuality */
 int des_abi_sizeof(int which);
 
 /* ---- instrumentation ----------------------------------------------------------------- */

@@ -29,6 +29,7 @@
 #include "matprops.hpp"
 #include "mesh.hpp"
 #include "output.hpp"
+#include "remeshing.hpp"
 #include "rheology.hpp"
 #include "phasechanges.hpp"
 #include "utils.hpp"
@@ -374,6 +375,38 @@ int desref_call(const char *fn)
     else if (f == "rho_all") {   // into etmp
         for (int e = 0; e < var.nelem; ++e) (*var.etmp)[e] = var.mat->rho(e);
     }
+    else return -1;
+    return 0;
+}
+
+// bad_mesh_quality (remeshing.cxx:2752) on the current state, with the four Param.mesh knobs
+// it reads overridden for this call.  index / min_quality keep the caller's sentinel when the
+// reference does not write them.  The reference prints its diagnosis to stdout.
+int desref_bad_mesh_quality(double smallest_size, double max_boundary_distortion, double min_quality,
+                            int remeshing_option, int *index, double *minq)
+{
+    Param &p = *g_param;
+    const Mesh saved = p.mesh;
+    p.mesh.smallest_size = smallest_size;
+    p.mesh.max_boundary_distortion = max_boundary_distortion;
+    p.mesh.min_quality = min_quality;
+    p.mesh.remeshing_option = remeshing_option;
+    int rc = bad_mesh_quality(p, *g_var, *index, *minq);
+    p.mesh = saved;
+    return rc;
+}
+
+int desref_get_mesh_param(const char *name, double *out)
+{
+    const Mesh &m = g_param->mesh; std::string n(name);
+    if (n == "smallest_size") *out = m.smallest_size;
+    else if (n == "resolution") *out = m.resolution;
+    else if (n == "max_boundary_distortion") *out = m.max_boundary_distortion;
+    else if (n == "min_quality") *out = m.min_quality;
+    else if (n == "xlength") *out = m.xlength;
+    else if (n == "ylength") *out = m.ylength;
+    else if (n == "zlength") *out = m.zlength;
+    else if (n == "remeshing_option") *out = m.remeshing_option;
     else return -1;
     return 0;
 }

@@ -55,6 +55,43 @@ STEP_CALLS = [
 ]
 
 
+MESH_PARAMS = ["smallest_size", "resolution", "max_boundary_distortion", "min_quality", "xlength",
+               "ylength", "zlength", "remeshing_option"]
+# (smallest_size, max_boundary_distortion, min_quality, remeshing_option) overrides for
+# bad_mesh_quality at the last dumped state; None = the cfg's own value.  Chosen to reach every
+# return of remeshing.cxx:2752-2866: 0, 1 (distortion), 2 (bottom; sides with option 13), 3 (tiny).
+QUALITY_CASES = [(None, None, None, None), (None, None, 0.999, None), (None, 1e-12, None, 1),
+                 (None, 1e-12, None, 13), (None, 1e9, None, 13), (None, 1e-12, None, 0),
+                 (1e3, None, None, None), (None, None, 1e-9, 11)]
+
+
+def quality_cases(r, out):
+    base = [r.mesh_param(k) for k in ("smallest_size", "max_boundary_distortion", "min_quality",
+                                      "remeshing_option")]
+    rows, res = [], []
+    for case in QUALITY_CASES:
+        a = [b if c is None else c for b, c in zip(base, case)]
+        code, idx, mq = r.bad_mesh_quality(a[0], a[1], a[2], int(a[3]))
+        rows.append(a)
+        res.append((code, idx, mq))
+    out["q_params"] = np.asarray(rows, dtype=np.float64)
+    out["q_code"] = np.asarray([x[0] for x in res], dtype=np.int32)
+    out["q_index"] = np.asarray([x[1] for x in res], dtype=np.int32)
+    out["q_minq"] = np.asarray([x[2] for x in res], dtype=np.float64)
+    # the side-node branch alone (remeshing_option 13, :2795-2838): same state with the bottom
+    # nodes put back on z = -zlength, so the bottom check passes and the else-if chain decides
+    coord = r.get("coord")
+    n = r.int("nnode")
+    c2 = coord.copy()
+    bottom = (r.get("bcflag") & 16) != 0
+    c2[2 * n:][bottom] = -r.mesh_param("zlength")
+    r.set("coord", c2)
+    code, idx, mq = r.bad_mesh_quality(base[0], 1e-12, base[2], 13)
+    r.set("coord", coord)
+    out["q2_coord"] = c2
+    out["q2_result"] = np.asarray([code, idx], dtype=np.int32)
+
+
 def snapshot(r, out, prefix):
     for a in STATE_ARRAYS:
         out[prefix + a] = r.get(a)
@@ -105,6 +142,9 @@ def dump(cfg, out_path, steps=(1,), sets=(), by_function=True):
             r.step(k - done)
             done = k
             snapshot(r, out, "s%d_" % k)
+        for s in MESH_PARAMS:
+            out["m_" + s] = np.float64(r.mesh_param(s))
+        quality_cases(r, out)
         out["steps"] = np.asarray(sorted(steps), dtype=np.int32)
         np.savez_compressed(out_path, **out)
 

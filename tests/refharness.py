@@ -29,6 +29,9 @@ class Ref:
         L.desref_call.argtypes = [C.c_char_p]
         L.desref_step.argtypes = [C.c_int]; L.desref_step.restype = C.c_double
         L.desref_l2_residual.restype = C.c_double
+        L.desref_bad_mesh_quality.argtypes = [C.c_double, C.c_double, C.c_double, C.c_int,
+                                              C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.desref_get_mesh_param.argtypes = [C.c_char_p, C.POINTER(C.c_double)]
         cwd = os.getcwd()
         if workdir:
             os.chdir(workdir)
@@ -85,3 +88,17 @@ class Ref:
 
     def step(self, n=1):
         return self.lib.desref_step(n)
+
+    def mesh_param(self, name):
+        v = C.c_double()
+        assert self.lib.desref_get_mesh_param(name.encode(), C.byref(v)) == 0, name
+        return v.value
+
+    def bad_mesh_quality(self, smallest_size, max_boundary_distortion, min_quality, remeshing_option):
+        """bad_mesh_quality (remeshing.cxx:2752) with those Param.mesh knobs: (code, index, min_quality);
+        index is -12345 and min_quality NaN where the reference leaves them unwritten."""
+        idx = C.c_int(-12345)
+        mq = C.c_double(float("nan"))
+        code = self.lib.desref_bad_mesh_quality(smallest_size, max_boundary_distortion, min_quality,
+                                                remeshing_option, C.byref(idx), C.byref(mq))
+        return code, idx.value, mq.value

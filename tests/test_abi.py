@@ -35,7 +35,8 @@ def test_header_symbols_exported():
 
 def test_struct_sizes_match():
     L = core.load_library()
-    for i, st in enumerate((core.DesParam, core.DesMesh, core.DesState, core.DesDtReductions)):
+    for i, st in enumerate((core.DesParam, core.DesMesh, core.DesState, core.DesDtReductions,
+                            core.DesQualityParam, core.DesQuality)):
         assert L.des_abi_sizeof(i) == C.sizeof(st)
     assert L.des_abi_sizeof(99) == -1
 
@@ -147,4 +148,56 @@ def test_golden_fixture_is_the_reference():
         if k == "mesh_connectivity_surface":
             # conn_t has 4 columns, the reference fills 3 (mesh.cxx:3249-3262)
             a, b = a.reshape(4, -1)[:3], b.reshape(4, -1)[:3]
-        assert np.array_equal(a, b), "golden fixture differs from the live reference: " + k
+        # q_minq holds NaN where bad_mesh_quality leaves min_quality unwritten
+        same = np.array_equal(a, b, equal_nan=(a.dtype.kind == "f"))
+        assert same, "golden fixture differs from the live reference: " + k
+
+
+def test_quality_verdict_ladder():
+    """des_quality_verdict is the decision ladder of bad_mesh_quality (remeshing.cxx:2766-2866):
+    fed the reductions that the reference's loops would find, it returns the reference's code,
+    index and min_quality for every case recorded in the golden fixture."""
+    d = np.load(GOLDEN)
+    L = core.load_library()
+    N, E = int(d["p_nnode"]), int(d["p_nelem"])
+    x = d["s10_coord"].reshape(3, N)
+    vol = d["s10_volume"]
+    conn = d["mesh_connectivity"].reshape(4, E)
+    flag = d["mesh_bcflag"]
+    p = [x[:, conn[i]] for i in range(4)]
+
+    def area(a, b, c):
+        ab, ac = b - a, c - a
+        d0 = ab[1] * ac[2] - ab[2] * ac[1]
+        d1 = ab[2] * ac[0] - ab[0] * ac[2]
+        d2 = ab[0] * ac[1] - ab[1] * ac[0]
+        return np.sqrt(d0 * d0 + d1 * d1 + d2 * d2) / 2
+
+    asum = area(p[0], p[1], p[2]) + area(p[0], p[1], p[3]) + area(p[2], p[3], p[0]) + area(p[2], p[3], p[1])
+    quality = 216 * np.sqrt(3.0) * vol * vol / (asum * asum * asum)
+    res = float(d["m_resolution"])
+    for row, code, index, minq in zip(d["q_params"], d["q_code"], d["q_index"], d["q_minq"]):
+        qp = core.DesQualityParam(smallest_size=row[0], resolution=res, max_boundary_distortion=row[1],
+                                  min_quality=row[2], xlength=float(d["m_xlength"]),
+                                  ylength=float(d["m_ylength"]), zlength=float(d["m_zlength"]),
+                                  remeshing_option=int(row[3]))
+        q = core.DesQuality()
+        small = np.nonzero(vol < row[0] * 0.118 * res ** 3)[0]
+        q.first_small_elem = int(small[0]) if len(small) else -1
+        dist = row[1] * res
+        ro = int(row[3])
+        q.first_bottom_node = q.first_side_node = -1
+        if ro in (1, 2, 11, 13):
+            bad = np.nonzero(((flag & 16) != 0) & (np.abs(x[2] + float(d["m_zlength"])) > dist))[0]
+            q.first_bottom_node = int(bad[0]) if len(bad) else -1
+        if ro == 13:
+            off = np.where(flag & 1, np.abs(x[0]), np.where(flag & 2, np.abs(x[0] - float(d["m_xlength"])),
+                  np.where(flag & 4, np.abs(x[1]), np.where(flag & 8, np.abs(x[1] - float(d["m_ylength"])), 0.0))))
+            bad = np.nonzero(off > dist)[0]
+            q.first_side_node = int(bad[0]) if len(bad) else -1
+        w = int(np.argmin(quality)) if quality.min() < 1 else 0
+        q.worst_elem, q.worst_quality = w, float(min(quality[w], 1.0))
+        idx, mq = C.c_int(-12345), C.c_double(float("nan"))
+        got = L.des_quality_verdict(C.byref(qp), C.byref(q), C.byref(idx), C.byref(mq))
+        assert (got, idx.value) == (int(code), int(index)), (row, got, idx.value, code, index)
+        assert (np.isnan(minq) and np.isnan(mq.value)) or mq.value == float(minq), (row, mq.value, minq)

@@ -130,3 +130,82 @@ def test_determinism():
         g.close()
     for k in FIELDS:
         assert np.array_equal(outs[0][k], outs[1][k]), k
+
+
+def _quality_kwargs(d, row):
+    return dict(smallest_size=float(row[0]), resolution=float(d["m_resolution"]),
+                max_boundary_distortion=float(row[1]), min_quality=float(row[2]),
+                xlength=float(d["m_xlength"]), ylength=float(d["m_ylength"]),
+                zlength=float(d["m_zlength"]), remeshing_option=int(row[3]))
+
+
+@pytest.mark.parametrize("case", ["box-ep-tiny", "box-ep"])
+def test_mesh_quality(case):
+    """bad_mesh_quality (remeshing.cxx:2752-2866) with its loops on the device: for every knob
+    combination refdump.QUALITY_CASES records -- each return code 0..3 -- the code, the index
+    (integer: exact) and min_quality (bit-exact: same arithmetic, host cube root) are the
+    reference's, from the state 20 steps in.  The state is uploaded, and in a second pass
+    reached by stepping on the device (so the deferred compute_volume is exercised)."""
+    d = ref_dump(case, [1, 20])
+    for mode in ("uploaded", "stepped"):
+        if mode == "uploaded":
+            g = refmodel.model_from_dump(d, prefix="s20_")
+        else:
+            g = refmodel.model_from_dump(d)
+            g.run(20, float(d["s0_dt"]))
+        for row, code, index, minq in zip(d["q_params"], d["q_code"], d["q_index"], d["q_minq"]):
+            got, idx, mq, q = g.mesh_quality(**_quality_kwargs(d, row))
+            assert got == int(code), (mode, row, got, code)
+            assert (idx if idx is not None else -12345) == int(index), (mode, row, idx, index)
+            if np.isnan(minq):
+                assert mq is None, (mode, row, mq)
+            elif mode == "uploaded":
+                assert mq == float(minq), (mode, row, mq, minq)
+            else:
+                assert abs(mq - float(minq)) <= 1e-10 * float(minq), (mode, row, mq, minq)
+        if mode == "uploaded":
+            # the side-node branch alone: bottom nodes back on z = -zlength
+            g.upload_state(coord=d["q2_coord"])
+            row = d["q_params"][0].copy(); row[1] = 1e-12; row[3] = 13
+            got, idx, mq, q = g.mesh_quality(**_quality_kwargs(d, row))
+            assert (got, idx) == (int(d["q2_result"][0]), int(d["q2_result"][1])), (got, idx, d["q2_result"])
+            assert q.first_bottom_node == -1 and q.first_side_node == idx
+        g.close()
+
+
+def test_average_fields():
+    """Output::average_fields (output.cxx:312-352) with device accumulators: snapshot at the first
+    step of the interval, running sums afterwards.  The host loop `s_avg[i] += s[i]` is restated
+    here on the per-step downloads; the device accumulators must match it bit for bit (and
+    tests/test_bridge_gpu.py compares the frames Output::write makes from them with the
+    reference binary's)."""
+    d = ref_dump("box-ep", [1, 20])
+    g = refmodel.model_from_dump(d)
+    dt = float(d["s0_dt"])
+    t = 0.0
+    want = None
+    for i in range(6):
+        t += dt
+        g.step(dt, t, i + 1)
+        s = g.download_state("coord", "strain", "stress", "delta_plstrain")
+        g.average_fields(first=(i == 0))
+        if i == 0:
+            want = {k: v.copy() for k, v in s.items()}
+        else:
+            want["stress"] += s["stress"]
+            want["delta_plstrain"] += s["delta_plstrain"]
+    coord0, strain0, stress_avg, dpl_avg = g.download_averages()
+    assert np.array_equal(coord0, want["coord"])
+    assert np.array_equal(strain0, want["strain"])
+    assert np.array_equal(stress_avg, want["stress"])
+    assert np.array_equal(dpl_avg, want["delta_plstrain"])
+    # and without the per-step downloads (the deferred tail is flushed by average_fields itself)
+    h = refmodel.model_from_dump(d)
+    t = 0.0
+    for i in range(6):
+        t += dt
+        h.step(dt, t, i + 1)
+        h.average_fields(first=(i == 0))
+    for a, b in zip(h.download_averages(), (coord0, strain0, stress_avg, dpl_avg)):
+        assert np.array_equal(a, b)
+    g.close(); h.close()
