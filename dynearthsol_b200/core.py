@@ -132,6 +132,8 @@ ABI_SYMBOLS = [
     "des_gpu_halo_width", "des_gpu_halo_pack", "des_gpu_halo_unpack",
     "des_gpu_mesh_quality", "des_quality_verdict", "des_gpu_average_fields",
     "des_gpu_download_averages",
+    "des_gpu_build_support", "des_gpu_find_boundary_facets", "des_host_boundary_flags",
+    "des_host_boundary_nodes", "des_host_bucket_facets", "des_host_surface_topology",
 ]
 
 _lib = None
@@ -188,6 +190,17 @@ def load_library():
     L.des_gpu_mesh_quality.argtypes = [H, C.POINTER(DesQualityParam), C.POINTER(DesQuality)]
     L.des_quality_verdict.argtypes = [C.POINTER(DesQualityParam), C.POINTER(DesQuality),
                                       C.POINTER(C.c_int), _DP]
+    _UP = C.POINTER(C.c_uint)
+    L.des_gpu_build_support.argtypes = [C.c_int, C.c_int, C.c_int, _IP, _IP, _IP, _IP]
+    L.des_gpu_find_boundary_facets.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _IP, _IP, _IP, _UP,
+                                               _IP, _IP, _IP, _IP]
+    L.des_host_boundary_flags.argtypes = [C.c_int, C.c_int, _IP, _IP, _UP]
+    L.des_host_boundary_nodes.argtypes = [C.c_int, _UP, C.POINTER(C.c_int * DES_NBDRY),
+                                          C.POINTER(_IP * DES_NBDRY)]
+    L.des_host_bucket_facets.argtypes = [C.c_int, C.c_int, _IP, _IP, _IP, _IP, C.POINTER(C.c_int * DES_NBDRY),
+                                         C.POINTER(C.c_int * (DES_NBDRY + 1)), _IP, _IP]
+    L.des_host_surface_topology.argtypes = [C.c_int, C.c_int, _IP, _DP, _IP, _IP, C.c_int, _IP, _IP,
+                                            C.c_int, _IP, _IP, _IP, _IP, _IP]
     L.des_gpu_average_fields.argtypes = [H, C.c_int]
     L.des_gpu_download_averages.argtypes = [H, _DP, _DP, _DP, _DP]
     for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions, DesQualityParam, DesQuality)):
@@ -212,6 +225,100 @@ def host_build_support(nnode, conn):
     if rc:
         raise DesError(rc, "des_host_build_support")
     return idx, arr, lidx
+
+
+def _ck_plain(rc, what):
+    if rc:
+        raise DesError(rc, what)
+
+
+def host_boundary_flags(nnode, segment, segflag):
+    """create_boundary_flags (mesh.cxx:2824-2851): segment is segment_t SoA [3*nseg]."""
+    L = load_library()
+    segment = np.ascontiguousarray(segment, dtype=np.int32).reshape(-1)
+    segflag = np.ascontiguousarray(segflag, dtype=np.int32).reshape(-1)
+    bc = np.zeros(nnode, dtype=np.uint32)
+    _ck_plain(L.des_host_boundary_flags(nnode, segflag.size, _ptr(segment, C.c_int), _ptr(segflag, C.c_int),
+                                        _ptr(bc, C.c_uint)), "des_host_boundary_flags")
+    return bc
+
+
+def host_boundary_nodes(bcflag):
+    """create_boundary_nodes (mesh.cxx:2854-2880): list of ten int32 arrays."""
+    L = load_library()
+    bcflag = np.ascontiguousarray(bcflag, dtype=np.uint32)
+    cnt = (C.c_int * DES_NBDRY)()
+    _ck_plain(L.des_host_boundary_nodes(bcflag.size, _ptr(bcflag, C.c_uint), C.byref(cnt), None),
+              "des_host_boundary_nodes")
+    out = [np.empty(cnt[j], dtype=np.int32) for j in range(DES_NBDRY)]
+    ptrs = (_IP * DES_NBDRY)(*[_ptr(a, C.c_int) for a in out])
+    _ck_plain(L.des_host_boundary_nodes(bcflag.size, _ptr(bcflag, C.c_uint), C.byref(cnt), C.byref(ptrs)),
+              "des_host_boundary_nodes")
+    return out
+
+
+def host_surface_topology(nnode, bnodes_z1, coord_x, support_idx, support_arr, conn_surface):
+    """create_top_elems + create_surface_info integer tables (mesh.cxx:2882-3098)."""
+    L = load_library()
+    bz = np.ascontiguousarray(bnodes_z1, dtype=np.int32)
+    cx = np.ascontiguousarray(coord_x, dtype=np.float64)
+    cs = np.ascontiguousarray(conn_surface, dtype=np.int32).reshape(-1)
+    etop = cs.size // 4
+    ntop = bz.size
+    top_nodes = np.empty(ntop, dtype=np.int32)
+    cap = int(support_arr.size // 4)
+    top_elems = np.empty(cap, dtype=np.int32)
+    n_te = C.c_int()
+    ean = np.empty(3 * etop, dtype=np.int32)
+    sidx = np.empty(ntop + 1, dtype=np.int32)
+    sarr = np.empty(3 * etop, dtype=np.int32)
+    _ck_plain(L.des_host_surface_topology(nnode, ntop, _ptr(bz, C.c_int), _ptr(cx, C.c_double),
+                                          _ptr(support_idx, C.c_int), _ptr(support_arr, C.c_int),
+                                          etop, _ptr(cs, C.c_int), _ptr(top_nodes, C.c_int), cap,
+                                          C.byref(n_te), _ptr(top_elems, C.c_int), _ptr(ean, C.c_int),
+                                          _ptr(sidx, C.c_int), _ptr(sarr, C.c_int)), "des_host_surface_topology")
+    return dict(top_nodes=top_nodes, top_elems=top_elems[:n_te.value].copy(), elem_and_nodes=ean,
+                support_surf_idx=sidx, support_surf_arr=sarr)
+
+
+def build_topology(coord, conn, segment, segflag, device=0):
+    """All integer tables of DesMesh from connectivity + boundary segments (the reference's
+    create_boundary_flags/nodes/facets, create_support, create_top_elems, create_surface_info:
+    mesh.cxx:2824-3329), bit-identical to the reference's.  The two O(nelem) builders run on
+    the GPU.  coord [3, N], conn [4, E], segment [3, nseg] (all SoA), segflag [nseg]."""
+    L = load_library()
+    coord = np.ascontiguousarray(coord, dtype=np.float64)
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    segment = np.ascontiguousarray(segment, dtype=np.int32)
+    segflag = np.ascontiguousarray(segflag, dtype=np.int32).reshape(-1)
+    N, E, S = coord.shape[1], conn.shape[1], segflag.size
+    m = {"nnode": N, "nelem": E, "connectivity": conn}
+    m["bcflag"] = host_boundary_flags(N, segment, segflag)
+    idx = np.empty(N + 1, dtype=np.int32); arr = np.empty(4 * E, dtype=np.int32); lidx = np.empty(4 * E, dtype=np.int32)
+    _ck_plain(L.des_gpu_build_support(device, N, E, _ptr(conn, C.c_int), _ptr(idx, C.c_int), _ptr(arr, C.c_int),
+                                      _ptr(lidx, C.c_int)), "des_gpu_build_support")
+    m["support_idx"], m["support_arr"], m["support_lidx"] = idx, arr, lidx
+    se = np.empty(S, dtype=np.int32); sf = np.empty(S, dtype=np.int32)
+    _ck_plain(L.des_gpu_find_boundary_facets(device, N, E, S, _ptr(conn, C.c_int), _ptr(segment, C.c_int),
+                                             _ptr(segflag, C.c_int), _ptr(m["bcflag"], C.c_uint),
+                                             _ptr(idx, C.c_int), _ptr(arr, C.c_int), _ptr(se, C.c_int),
+                                             _ptr(sf, C.c_int)), "des_gpu_find_boundary_facets")
+    nb = (C.c_int * DES_NBDRY)(); off = (C.c_int * (DES_NBDRY + 1))()
+    pairs = np.empty(2 * max(S, 1), dtype=np.int32)
+    etop_max = int((segflag == 32).sum())
+    cs = np.zeros(4 * etop_max, dtype=np.int32)
+    _ck_plain(L.des_host_bucket_facets(E, S, _ptr(segflag, C.c_int), _ptr(se, C.c_int), _ptr(sf, C.c_int),
+                                       _ptr(conn, C.c_int), C.byref(nb), C.byref(off), _ptr(pairs, C.c_int),
+                                       _ptr(cs, C.c_int)), "des_host_bucket_facets")
+    for k in range(DES_NBDRY):
+        m["bfacets%d" % k] = pairs[2 * off[k]:2 * off[k + 1]].copy()
+    m["connectivity_surface"] = cs.reshape(4, -1)
+    bn = host_boundary_nodes(m["bcflag"])
+    for k in range(DES_NBDRY):
+        m["bnodes%d" % k] = bn[k]
+    m.update(host_surface_topology(N, bn[5], coord[0], idx, arr, cs))
+    m["seg_elem"], m["seg_facet"] = se, sf
+    return m
 
 
 def make_param(**kw):

@@ -1206,3 +1206,4 @@ void *des_gpu_device_ptr(DesGpu *h, const char *name)
 } // extern "C"
 
 #include "des_twins.cuh"
+#include "des_topology_api.cuh"

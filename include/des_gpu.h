@@ -279,6 +279,38 @@ int des_gpu_halo_unpack(DesGpu *h, int phase);
  * [4*nelem] are caller-allocated.  Bit-identical to the reference's arrays. */
 int des_host_build_support(int nnode, int nelem, const int *connectivity,
                            int *idx, int *arr, int *lidx);
+/* ---- topology builders: the integer tables of DesMesh from
+ * connectivity + boundary segments, bit-identical to mesh.cxx:2824-3329, without the
+ * reference's O(nseg*nelem) facet search.  Arrays are the reference's layouts (conn_t /
+ * segment_t SoA); outputs are caller-allocated.  The two O(nelem) builders run on the GPU,
+ * the O(nnode) / O(surface) ones on the host with the reference's own std::sort calls. ---- */
+/* create_support (mesh.cxx:3287-3329) on device `device`; outputs as des_host_build_support */
+int des_gpu_build_support(int device, int nnode, int nelem, const int *connectivity,
+                          int *idx, int *arr, int *lidx);
+/* the search loop of create_boundary_facets (mesh.cxx:3176-3225), through the support of each
+ * segment's smallest node: seg_elem[i] = element (-1: not a boundary segment, -2: on no
+ * element), seg_facet[i] = its facet 0..3 */
+int des_gpu_find_boundary_facets(int device, int nnode, int nelem, int nseg, const int *connectivity,
+                                 const int *segment, const int *segflag, const unsigned *bcflag,
+                                 const int *support_idx, const int *support_arr,
+                                 int *seg_elem, int *seg_facet);
+/* create_boundary_flags2 (mesh.cxx:2824-2835); bcflag zeroed by the caller */
+int des_host_boundary_flags(int nnode, int nseg, const int *segment, const int *segflag, unsigned *bcflag);
+/* create_boundary_nodes (mesh.cxx:2854-2880); bnodes == NULL: counts only */
+int des_host_boundary_nodes(int nnode, const unsigned *bcflag, int nbnodes[DES_NBDRY],
+                            int *const bnodes[DES_NBDRY]);
+/* bucketing + per-boundary sort + connectivity_surface of create_boundary_facets
+ * (mesh.cxx:3205-3262): pairs [2*nseg], bucket k at pairs + 2*offset[k] */
+int des_host_bucket_facets(int nelem, int nseg, const int *segflag, const int *seg_elem, const int *seg_facet,
+                           const int *connectivity, int nbfacets[DES_NBDRY], int offset[DES_NBDRY + 1],
+                           int *pairs, int *conn_surface);
+/* create_top_elems (mesh.cxx:2882-2931), create_surface_info / create_support_surf integer
+ * tables (mesh.cxx:3031-3098, 2937-2964) */
+int des_host_surface_topology(int nnode, int ntop, const int *bnodes_z1, const double *coord_x,
+                              const int *support_idx, const int *support_arr,
+                              int etop, const int *conn_surface,
+                              int *top_nodes, int max_top_elems, int *ntop_elems, int *top_elems,
+                              int *elem_and_nodes, int *ssup_idx, int *ssup_arr);
 /* sizeof() of the ABI structs as compiled, so a foreign-language binding can verify its
  * own layout: which = 0 DesParam, 1 DesMesh, 2 DesState, 3 DesDtReductions, 4 DesQualityParam, 5 DesQuality */
 int des_abi_sizeof(int which);

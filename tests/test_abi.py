@@ -201,3 +201,19 @@ def test_quality_verdict_ladder():
         got = L.des_quality_verdict(C.byref(qp), C.byref(q), C.byref(idx), C.byref(mq))
         assert (got, idx.value) == (int(code), int(index)), (row, got, idx.value, code, index)
         assert (np.isnan(minq) and np.isnan(mq.value)) or mq.value == float(minq), (row, mq.value, minq)
+
+
+def test_host_topology_builders_match_reference():
+    """create_boundary_flags / create_boundary_nodes / create_top_elems / create_surface_info
+    (mesh.cxx:2824-3098) through the library's host builders: bit-identical integer tables."""
+    d = np.load(GOLDEN)
+    N, E = int(d["p_nnode"]), int(d["p_nelem"])
+    bc = core.host_boundary_flags(N, d["mesh_segment"], d["mesh_segflag"])
+    assert np.array_equal(bc, d["mesh_bcflag"])
+    bn = core.host_boundary_nodes(bc)
+    for k in range(10):
+        assert np.array_equal(bn[k], d["mesh_bnodes%d" % k]), k
+    s = core.host_surface_topology(N, bn[5], d["s0_coord"][:N], d["mesh_support_idx"], d["mesh_support_arr"],
+                                   d["mesh_connectivity_surface"])
+    for k in ("top_nodes", "top_elems", "elem_and_nodes", "support_surf_idx", "support_surf_arr"):
+        assert np.array_equal(s[k], d["mesh_" + k]), k
