@@ -65,8 +65,9 @@ struct DesGpu {
     DtPartial *dt_partials = nullptr; int dt_blocks = 0;
     QPartial *q_partials = nullptr; int *q_nodes = nullptr;     // des_gpu_mesh_quality
     // Output::average_fields accumulators (mesh-lifetime allocations, internal element order)
-    double *avg_coord0 = nullptr, *avg_strain0 = nullptr, *avg_stress = nullptr, *avg_dpl = nullptr;
+    double *avg_coord0 = nullptr;   // the element accumulators live in Dev (avg_stress, avg_strain0, avg_dpl)
     bool avg_valid = false;
+    int avg_pending = 0;        // 1 accumulate / 2 snapshot: deferred into the next E-B (with the rotation)
     // timing
     bool timing = false;
     std::vector<EvPair> ev_pool; size_t ev_used = 0;
@@ -179,8 +180,9 @@ void free_mesh(DesGpu *h)
     h->nsend = h->nrecv = 0;
     h->send_idx = h->recv_idx = h->top_of_node = nullptr;
     h->send_buf = h->recv_buf = nullptr;
-    h->avg_coord0 = h->avg_strain0 = h->avg_stress = h->avg_dpl = nullptr;
+    h->avg_coord0 = nullptr;
     h->avg_valid = false;
+    h->avg_pending = 0;
     h->eperm = h->einv = nullptr;
     h->h_einv.clear();
     memset(&h->D, 0, sizeof(h->D));
@@ -348,15 +350,37 @@ int tail_flags(const DesGpu *h)
 int head_flags(const DesGpu *h) { return (h->hp.has_thermal_diffusion ? 1 : 0) | 2 | 4; }
 
 // Completes the deferred end-of-step element work (volume, mass, rotation) on its own.
+// Output::average_fields on the current device state (output.cxx:317-350), as its own kernels
+int average_now(DesGpu *h)
+{
+    if (!h->avg_pending) return DES_OK;
+    Dev &D = h->D;
+    const size_t E = D.nelem;
+    if (h->avg_pending == 2) {
+        CK(cudaMemcpyAsync(D.avg_strain0, D.strain, E * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        CK(cudaMemcpyAsync(D.avg_stress, D.stress, E * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        CK(cudaMemcpyAsync(D.avg_dpl, D.delta_plstrain, E * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    } else {
+        const size_t n6 = E * 6;
+        { LaunchScope ls(h, KC_PACK);
+          k_avg_accumulate<<<unsigned((n6 + 255) / 256), 256, 0, h->stream>>>(n6, D.stress, D.avg_stress); }
+        { LaunchScope ls(h, KC_PACK);
+          k_avg_accumulate<<<unsigned((E + 255) / 256), 256, 0, h->stream>>>(E, D.delta_plstrain, D.avg_dpl); }
+    }
+    h->avg_pending = 0;
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
 int flush_tail(DesGpu *h)
 {
-    if (!h->tail_pending) return DES_OK;
+    if (!h->tail_pending) return average_now(h);
     const int mm = h->hp.has_moving_mesh;
     LAUNCH(KC_ELEM_A, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, h->dt_prev, tail_flags(h), 0);
     if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, false>), h->D.nnode, 256, h->P, h->D, 0.0, 0);
     h->tail_pending = false;
     CK(cudaGetLastError());
-    return DES_OK;
+    return average_now(h);      // a deferred average_fields wanted exactly this (rotated) state
 }
 
 int run_surface(DesGpu *h, double dt, bool with_volume_n)
@@ -756,17 +780,24 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
     // E-B / N-B
     {
         const double dtr = rot ? h->dt_prev : 0.0;
-#define EB_CASE(S, R) switch (h->hp.rheol_type) { \
-        case DES_RH_ELASTIC: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_ELASTIC>), E, 128, h->P, D, dt, dtr); break; \
-        case DES_RH_MAXWELL: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_MAXWELL>), E, 128, h->P, D, dt, dtr); break; \
-        case DES_RH_EP:      LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EP>), E, 128, h->P, D, dt, dtr); break; \
-        default:             LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EVP>), E, 128, h->P, D, dt, dtr); break; }
+#define EB_CASE(S, R, A) switch (h->hp.rheol_type) { \
+        case DES_RH_ELASTIC: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_ELASTIC, A>), E, 128, h->P, D, dt, dtr, afirst); break; \
+        case DES_RH_MAXWELL: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_MAXWELL, A>), E, 128, h->P, D, dt, dtr, afirst); break; \
+        case DES_RH_EP:      LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EP, A>), E, 128, h->P, D, dt, dtr, afirst); break; \
+        default:             LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EVP, A>), E, 128, h->P, D, dt, dtr, afirst); break; }
         const bool single = h->hp.nmat == 1;
-        if (single && rot) EB_CASE(true, true)
-        else if (single) EB_CASE(true, false)
-        else if (rot) EB_CASE(false, true)
-        else EB_CASE(false, false)
+        // a deferred Output::average_fields rides on the rotation (des_gpu_average_fields)
+        const bool avg = rot && h->avg_pending != 0;
+        const int afirst = (h->avg_pending == 2) ? 1 : 0;
+        if (!rot && h->avg_pending) { int rc = average_now(h); if (rc) return rc; }
+        if (single && avg) EB_CASE(true, true, true)
+        else if (avg) EB_CASE(false, true, true)
+        else if (single && rot) EB_CASE(true, true, false)
+        else if (single) EB_CASE(true, false, false)
+        else if (rot) EB_CASE(false, true, false)
+        else EB_CASE(false, false, false)
 #undef EB_CASE
+        if (avg) h->avg_pending = 0;
     }
     if (h->hp.is_using_mixed_stress) {
         LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
@@ -987,30 +1018,26 @@ int des_gpu_average_fields(DesGpu *h, int first)
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     CK(cudaSetDevice(h->device));
-    int rc = flush_tail(h);     // average_fields sees the stress AFTER rotate_stress
-    if (rc) return rc;
+    int rc;
     Dev &D = h->D;
     const size_t N = D.nnode, E = D.nelem;
+    if (h->avg_pending && (rc = flush_tail(h))) return rc;     // two calls without a step in between
     if (!h->avg_coord0) {
         if ((rc = dalloc(h, &h->avg_coord0, N * 3, "avg_coord0"))) return rc;
-        if ((rc = dalloc(h, &h->avg_strain0, E * 6, "avg_strain0"))) return rc;
-        if ((rc = dalloc(h, &h->avg_stress, E * 6, "avg_stress"))) return rc;
-        if ((rc = dalloc(h, &h->avg_dpl, E, "avg_dpl"))) return rc;
+        if ((rc = dalloc(h, &D.avg_strain0, E * 6, "avg_strain0"))) return rc;
+        if ((rc = dalloc(h, &D.avg_stress, E * 6, "avg_stress"))) return rc;
+        if ((rc = dalloc(h, &D.avg_dpl, E, "avg_dpl"))) return rc;
     }
-    if (first) {
-        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, h->avg_coord0);
-        CK(cudaMemcpyAsync(h->avg_strain0, D.strain, E * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
-        CK(cudaMemcpyAsync(h->avg_stress, D.stress, E * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
-        CK(cudaMemcpyAsync(h->avg_dpl, D.delta_plstrain, E * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
-        h->avg_valid = true;
-    } else {
-        if (!h->avg_valid) return fail(h, DES_E_STATE, "average_fields: no snapshot in this interval");
-        const size_t n6 = E * 6;
-        { LaunchScope ls(h, KC_PACK);
-          k_avg_accumulate<<<unsigned((n6 + 255) / 256), 256, 0, h->stream>>>(n6, D.stress, h->avg_stress); }
-        { LaunchScope ls(h, KC_PACK);
-          k_avg_accumulate<<<unsigned((E + 255) / 256), 256, 0, h->stream>>>(E, D.delta_plstrain, h->avg_dpl); }
-    }
+    if (!first && !h->avg_valid) return fail(h, DES_E_STATE, "average_fields: no snapshot in this interval");
+    // coordinates are final for the step (nothing moves them before the next N-C)
+    if (first) LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, h->avg_coord0);
+    h->avg_valid = true;
+    // average_fields must see the stress AFTER rotate_stress.  With the end-of-step work still
+    // deferred, the rotation happens inside the next step's E-B, and the sums ride on it there
+    // (k2_elem_b<.., AVG>): no flush, +112 B/element in that launch.  Otherwise: now.
+    h->avg_pending = first ? 2 : 1;
+    const bool rides = h->tail_pending && h->schedule != 1 && (h->hp.rheol_type & DES_RH_ELASTIC);
+    if (!rides && (rc = flush_tail(h))) return rc;
     CK(cudaGetLastError());
     return DES_OK;
 }
@@ -1022,11 +1049,12 @@ int des_gpu_download_averages(DesGpu *h, double *coord0, double *strain0, double
     CK(cudaSetDevice(h->device));
     const size_t N = h->D.nnode, E = h->D.nelem;
     int rc;
+    if (h->avg_pending && (rc = flush_tail(h))) return rc;
     if ((rc = ensure_stage(h, (h->eperm ? E * 6 : size_t(1)) * sizeof(double)))) return rc;
     double *st = static_cast<double *>(h->stage);
     if (coord0) CK(cudaMemcpyAsync(coord0, h->avg_coord0, N * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     struct { double *dst; const double *src; int rows; } f[3] = {
-        {strain0, h->avg_strain0, 6}, {stress_avg, h->avg_stress, 6}, {dpl_avg, h->avg_dpl, 1}};
+        {strain0, h->D.avg_strain0, 6}, {stress_avg, h->D.avg_stress, 6}, {dpl_avg, h->D.avg_dpl, 1}};
     for (auto &x : f) {
         if (!x.dst) continue;
         const double *src = x.src;

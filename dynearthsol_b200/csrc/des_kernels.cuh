@@ -60,6 +60,8 @@ struct Dev {
     unsigned long long *maxdh_bits;
     // multi-GPU: 1 for ghost nodes (values received from the owner), NULL on a single GPU
     const unsigned char *ghost;
+    // Output::average_fields accumulators (des_aux.cuh), NULL until des_gpu_average_fields is used
+    double *avg_stress, *avg_strain0, *avg_dpl;     // [6E], [6E], [E]
     // L2 prefetch distance of the element kernels, in elements (0 = off): thread e asks L2 for
     // the streamed rows of element e + pf, so that block finds them in L2 instead of HBM
     int pf;

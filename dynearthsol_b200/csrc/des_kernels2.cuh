@@ -155,9 +155,13 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
 #else
 #define DES_EB_BOUNDS __launch_bounds__(128)
 #endif
-template <bool SINGLE, bool ROT, int RHEOL>
+// AVG (only with ROT): Output::average_fields (output.cxx:312-352) of the step that just ended,
+// whose call the host deferred to this launch -- the rotated stress it must see is in
+// registers here.  avg_first: the interval's first step (snapshot) instead of a running sum.
+template <bool SINGLE, bool ROT, int RHEOL, bool AVG = false>
 __global__ void DES_EB_BOUNDS
-k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot)
+k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot,
+          int avg_first = 0)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= D.nelem) return;
@@ -250,6 +254,27 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     if (ROT) {
         jaumann3(s, dt_rot, w3, w4, w5);
         jaumann3(es, dt_rot, w3, w4, w5);
+    }
+    if (AVG) {
+        // s, es: stress and strain as the previous step left them (after rotate_stress);
+        // delta_plstrain[e] still holds that step's value (it is rewritten below)
+        const double dpl_prev = D.delta_plstrain[e];
+        if (avg_first) {
+            #pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                D.avg_stress[size_t(i) * E + e] = s[i];
+                D.avg_strain0[size_t(i) * E + e] = es[i];
+            }
+            D.avg_dpl[e] = dpl_prev;
+        } else {
+            double a[6];
+            #pragma unroll
+            for (int i = 0; i < 6; ++i) a[i] = D.avg_stress[size_t(i) * E + e];
+            const double ad = D.avg_dpl[e];
+            #pragma unroll
+            for (int i = 0; i < 6; ++i) D.avg_stress[size_t(i) * E + e] = a[i] + s[i];
+            D.avg_dpl[e] = ad + dpl_prev;
+        }
     }
     const double old_s = trace3(s);
 
