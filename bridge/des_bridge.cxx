@@ -258,6 +258,28 @@ int des_bridge_markers_changed(DesBridge *b, const Param &param, const Variables
     return 0;
 }
 
+int des_bridge_isostasy_adjustment(DesBridge *b, const Param &param, Variables &var)
+{
+    std::cout << "Adjusting isostasy for " << param.ic.isostasy_adjustment_time_in_yr << " yrs...\n";
+    var.dt = des_bridge_compute_dt(b, param, var);
+    if (!(var.dt > 0)) return fail(b, DES_E_NAN, "isostasy: dt <= 0");
+    int iso_steps = param.ic.isostasy_adjustment_time_in_yr*YEAR2SEC / var.dt;
+    for (int n = 0; n < iso_steps; n++) {
+        int rc;
+        // update_strain_rate ... update_mesh, dynearthsol.cxx:507-536 (no vbcs: free boundary)
+        if ((rc = des_gpu_update_strain_rate(b->h))) return fail(b, rc, "update_strain_rate");
+        if ((rc = des_gpu_compute_dvoldt(b->h))) return fail(b, rc, "compute_dvoldt");
+        if ((rc = des_gpu_compute_edvoldt(b->h))) return fail(b, rc, "compute_edvoldt");
+        if ((rc = des_gpu_update_stress(b->h, var.dt))) return fail(b, rc, "update_stress");
+        if ((rc = des_gpu_update_force(b->h))) return fail(b, rc, "update_force");
+        if ((rc = des_gpu_update_velocity(b->h, var.dt))) return fail(b, rc, "update_velocity");
+        if ((rc = des_gpu_isostasy_constrain_velocity(b->h))) return fail(b, rc, "isostasy_constrain_velocity");
+        if ((rc = des_gpu_update_mesh(b->h, var.dt))) return fail(b, rc, "update_mesh");
+    }
+    std::cout << "Adjusted isostasy for " << iso_steps << " steps.\n";
+    return 0;
+}
+
 int des_bridge_bad_mesh_quality(DesBridge *b, const Param &param, const Variables &var,
                                 int &index, double &min_quality)
 {

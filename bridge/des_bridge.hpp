@@ -35,6 +35,9 @@ double des_bridge_compute_dt(DesBridge *b, const Param &param, Variables &var);
 int des_bridge_download(DesBridge *b, Variables &var, int what);
 // elemmarkers changed on the host (phase_changes, surface markers): dynearthsol.cxx:887
 int des_bridge_markers_changed(DesBridge *b, const Param &param, const Variables &var);
+// isostasy_adjustment (dynearthsol.cxx:496-539), between init() and the first compute_dt: the
+// same call sequence through the fine-grained twins; sets var.dt like the reference
+int des_bridge_isostasy_adjustment(DesBridge *b, const Param &param, Variables &var);
 // bad_mesh_quality (dynearthsol.cxx:942; remeshing.cxx:2752-2866) from device reductions: same
 // return code, index, min_quality and diagnostic line as the reference, no field download
 int des_bridge_bad_mesh_quality(DesBridge *b, const Param &param, const Variables &var,

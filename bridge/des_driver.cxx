@@ -3,8 +3,8 @@
 // (oracle/_ref/obj/*.o, dynearthsol.cxx compiled with -Dmain=desref_unused_main): input
 // parsing, init(), mesh generation, markers, phase changes, remeshing, output.
 //
-// main() below follows dynearthsol.cxx:593-1030 for the configurations in scope (no restart,
-// GoSPL, PT loop, hydraulics, rate-and-state/ATS, monitor): the statements that remain are
+// main() below follows dynearthsol.cxx:593-1030 for the configurations in scope (isostasy
+// spin-up included; no restart, GoSPL, PT loop, hydraulics, rate-and-state/ATS, monitor): the statements that remain are
 // the reference's own calls; the lines marked [B200] are the swaps INTEGRATION.md lists.
 #include <cstdio>
 #include <iostream>
@@ -46,7 +46,6 @@ int main(int argc, const char* argv[])
     if (param.control.has_PT) return unsupported("control.has_PT");
     if (param.control.has_hydraulic_diffusion) return unsupported("control.has_hydraulic_diffusion");
     if (param.control.use_global_velocity_scaling) return unsupported("control.use_global_velocity_scaling");
-    if (param.ic.isostasy_adjustment_time_in_yr > 0) return unsupported("ic.isostasy_adjustment_time_in_yr");
     if (param.ic.has_body_force_adjustment) return unsupported("ic.has_body_force_adjustment");
 
     static Variables var;
@@ -58,6 +57,12 @@ int main(int argc, const char* argv[])
     // [B200] device model: after init() (dynearthsol.cxx:634), replaces init_offload_device()
     DesBridge *gpu = des_bridge_create(param, var, 0);
     if (!gpu) return 1;
+    if (param.ic.isostasy_adjustment_time_in_yr > 0) {
+        // [B200] isostasy_adjustment(param, var);   (dynearthsol.cxx:638-641) through the twins,
+        // then the adjusted state back into Variables for the first frame
+        if (des_bridge_isostasy_adjustment(gpu, param, var)) return 1;
+        if (des_bridge_download(gpu, var, DES_DL_ALL)) return 1;
+    }
     // [B200] var.dt = compute_dt(param, var);   (dynearthsol.cxx:643)
     var.dt = des_bridge_compute_dt(gpu, param, var);
     if (!(var.dt > 0)) { std::cerr << "dt <= 0\n"; return 11; }

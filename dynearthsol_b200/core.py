@@ -124,7 +124,7 @@ ABI_SYMBOLS = [
     "des_gpu_compute_edvoldt", "des_gpu_update_stress", "des_gpu_nmd_stress",
     "des_gpu_update_force", "des_gpu_update_velocity", "des_gpu_apply_vbcs",
     "des_gpu_update_mesh", "des_gpu_compute_volume", "des_gpu_compute_mass",
-    "des_gpu_rotate_stress", "des_gpu_residual_force",
+    "des_gpu_rotate_stress", "des_gpu_residual_force", "des_gpu_isostasy_constrain_velocity",
     "des_gpu_launch_count", "des_gpu_enable_kernel_timing", "des_gpu_kernel_time",
     "des_gpu_device_ptr", "des_host_build_support", "des_abi_sizeof",
     "des_gpu_event_record", "des_gpu_event_elapsed_ms",
@@ -167,7 +167,7 @@ def load_library():
               "rotate_stress"]:
         getattr(L, "des_gpu_" + f).argtypes = [H, C.c_double]
     for f in ["update_strain_rate", "compute_dvoldt", "compute_edvoldt", "nmd_stress", "update_force",
-              "compute_volume", "compute_mass"]:
+              "compute_volume", "compute_mass", "isostasy_constrain_velocity"]:
         getattr(L, "des_gpu_" + f).argtypes = [H]
     L.des_gpu_residual_force.argtypes = [H, _DP]
     L.des_gpu_launch_count.argtypes = [H]

@@ -600,7 +600,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
 
     if ((rc = build_stress_bcs(h, m))) return rc;
 
-    h->dt_blocks = 148 * 4;
+    h->dt_blocks = 148 * 32;     // ~40 elements per thread at 51 M tets: enough warps in flight for the gathers (592 blocks: 2.05 ms, measured)
     if (!h->dt_partials) CK(cudaMalloc(&h->dt_partials, sizeof(DtPartial) * h->dt_blocks));
     CK(cudaStreamSynchronize(h->stream));
     h->have_mesh = true;

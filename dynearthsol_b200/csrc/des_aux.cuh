@@ -88,3 +88,17 @@ __global__ void k_avg_accumulate(size_t n, const double *__restrict__ src, doubl
     const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) acc[i] += src[i];
 }
+
+// ---------------------------------------------------------------------------------------
+// isostasy_adjustment's velocity constraint, dynearthsol.cxx:522-533: displacement is vertical
+// only; without a Winkler foundation the bottom is held
+// ---------------------------------------------------------------------------------------
+__global__ void k_isostasy_velocity(const __grid_constant__ Dev D, int hold_bottom)
+{
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= D.nnode) return;
+    double4 v = D.vv[n];
+    v.x = 0; v.y = 0;
+    if (hold_bottom && (D.bcflag[n] & BOUNDZ0)) v.z = 0;
+    D.vv[n] = v;
+}

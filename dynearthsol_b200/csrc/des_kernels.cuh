@@ -689,8 +689,8 @@ k_dt(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, DtParti
     double minl = DBL_MAX, dtm = DBL_MAX, dtd = DBL_MAX, gmin = DBL_MAX, vem = 0.0;
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < D.nelem; e += gridDim.x * blockDim.x) {
         const int4 c = D.conn[e];
-        const double4 a = D.xT[c.x], b = D.xT[c.y], cc = D.xT[c.z], d = D.xT[c.w];
-        const double4 v0 = D.vv[c.x], v1 = D.vv[c.y], v2 = D.vv[c.z], v3 = D.vv[c.w];
+        const double4 a = ld256_nc(D.xT + c.x), b = ld256_nc(D.xT + c.y), cc = ld256_nc(D.xT + c.z), d = ld256_nc(D.xT + c.w);
+        const double4 v0 = ld256_nc(D.vv + c.x), v1 = ld256_nc(D.vv + c.y), v2 = ld256_nc(D.vv + c.z), v3 = ld256_nc(D.vv + c.w);
         const double weight = 1.0 / 4;
         double vxe = 0.0, vye = 0.0, vze = 0.0;
         vxe += v0.x * weight; vye += v0.y * weight; vze += v0.z * weight;

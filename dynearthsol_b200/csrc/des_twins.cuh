@@ -186,6 +186,14 @@ int des_gpu_update_mesh(DesGpu *h, double dt)
     return DES_OK;
 }
 
+int des_gpu_isostasy_constrain_velocity(DesGpu *h)
+{
+    int rc = twin_ready(h); if (rc) return rc;
+    LAUNCH(KC_TWIN, k_isostasy_velocity, h->D.nnode, 256, h->D, h->hp.has_winkler_foundation ? 0 : 1);
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
 int des_gpu_compute_volume(DesGpu *h)
 {
     int rc = twin_ready(h); if (rc) return rc;

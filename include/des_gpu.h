@@ -248,6 +248,9 @@ int des_gpu_compute_volume(DesGpu *h);                              /* geometry.
 int des_gpu_compute_mass(DesGpu *h);                                /* geometry.cxx:1743 */
 int des_gpu_rotate_stress(DesGpu *h, double dt);                    /* fields.cxx:827 */
 int des_gpu_residual_force(DesGpu *h, double *l2);                  /* fields.cxx:700 */
+/* the velocity constraint inside isostasy_adjustment's loop (dynearthsol.cxx:522-533): vx = vy = 0,
+ * and vz = 0 on the bottom when there is no Winkler foundation */
+int des_gpu_isostasy_constrain_velocity(DesGpu *h);
 
 /* ---- multi-GPU: one handle per device, elements partitioned, ghost nodes exchanged --------
  * The reference has no distributed mode; this is the boundary a host (one process per GPU

@@ -29,6 +29,7 @@ def run(binary, cfg, wd):
 @pytest.mark.parametrize("cfg,model,frames", [
     ("t3d.cfg", "t3d", 6),                  # test-3d.cfg: 519 steps, tetgen mesh, Winkler, surface diffusion
     ("t3d-remesh.cfg", "t3dr", 5),          # test-3d-remesh.cfg: host remesh at step 300 + re-upload
+    ("t3d-iso.cfg", "t3di", 2),             # + isostasy spin-up before the step loop (51 twin-call iterations)
     ("orift.cfg", "orift", 4),              # oblique-rift-3d.cfg (300 steps): EVP, 2 materials, PREM, averaged fields
 ])
 def test_driver_matches_reference_frames(cfg, model, frames, tmp_path):
