@@ -275,6 +275,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--strong", action="store_true",
+                    help="N > 1: keep the --size mesh as it is and split it over the ranks (strong scaling), "
+                         "e.g. --size 200M --strong on 2/4/8 GPUs; default is weak scaling (size per GPU)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

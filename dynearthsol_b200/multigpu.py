@@ -179,7 +179,9 @@ def bench_main(a, rank, world, local_rank, W, K):
     from bench import SIZES, ClockSampler, alg_bytes_step, read_peaks      # bench.py is the main module's file
     size = a.size or "50M"
     xl, yl, zl, res = SIZES[size]
-    res = res / world ** (1.0 / 3.0)
+    strong = bool(getattr(a, "strong", False))
+    if not strong:
+        res = res / world ** (1.0 / 3.0)
     t0 = time.time()
     prob = build_box_rank((xl, yl, zl, res), rank, world)
     g = init_model(prob["mesh"], prob["phys"], prob["state"], prob["comp_p"], local_rank)
@@ -247,11 +249,12 @@ def bench_main(a, rank, world, local_rank, W, K):
         r = prob["nnode_global"] / E
         alg = alg_bytes_step(r)
         line = {"metric": "3D tet element-steps/sec", "value": value, "unit": "element-steps/s", "n_gpus": world,
-                "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+                "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if strong else "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": "box %s x%d (%dx%dx%d cells, %d tets, %d nodes): test-3d.cfg Mohr-Coulomb "
+                "config": {"workload": "box %s %s%d (%dx%dx%d cells, %d tets, %d nodes): test-3d.cfg Mohr-Coulomb "
                                        "elasto-plastic + thermal + mixed stress + surface diffusion, compute_dt "
-                                       "every 10 steps" % ((size, world) + prob["cells"] + (E, prob["nnode_global"])),
+                                       "every 10 steps" % ((size, "split over " if strong else "x", world) + prob["cells"]
+                                                           + (E, prob["nnode_global"])),
                            "element_order": "reference", "l2": "working set per GPU >> 126 MB L2",
                            "parallelism": "%d GPUs: RCB node-box partition, one-element halo, ghost-node exchange "
                                           "(NCCL send/recv) at the 3 nodal barriers + surface diffusion, allreduce(min/max) for dt" % world,
