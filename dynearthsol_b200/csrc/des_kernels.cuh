@@ -642,11 +642,22 @@ __global__ void k_surf_correct_elems(const __grid_constant__ Dev D)
     const double rdv = nv / D.volume[e];
     D.volume[e] = nv;
     if (rdv < 1.0) return;
-    D.plstrain[e] /= rdv;
+    // all 19 loads before the first store: the rows may alias as far as the compiler knows, and
+    // a load/divide/store chain per row was 19 dependent DRAM round trips (ncu: 890 cycles of
+    // long-scoreboard stall per issue; the top elements are isolated in every row)
+    double pl = D.plstrain[e], s[6], es[6], er[6];
+    #pragma unroll
     for (int j = 0; j < 6; j++) {
-        D.stress[size_t(j) * E + e] /= rdv;
-        D.strain[size_t(j) * E + e] /= rdv;
-        D.strain_rate[size_t(j) * E + e] /= rdv;
+        s[j] = D.stress[size_t(j) * E + e];
+        es[j] = D.strain[size_t(j) * E + e];
+        er[j] = D.strain_rate[size_t(j) * E + e];
+    }
+    D.plstrain[e] = pl / rdv;
+    #pragma unroll
+    for (int j = 0; j < 6; j++) {
+        D.stress[size_t(j) * E + e] = s[j] / rdv;
+        D.strain[size_t(j) * E + e] = es[j] / rdv;
+        D.strain_rate[size_t(j) * E + e] = er[j] / rdv;
     }
 }
 
