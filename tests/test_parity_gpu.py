@@ -15,7 +15,9 @@ FIELDS = ["coord", "vel", "temperature", "stress", "strain", "strain_rate", "pls
           "delta_plstrain", "volume", "volume_old", "force", "volume_n", "mass", "tmass",
           "dhacc", "edvacc_surf"]
 
-CASES = ["box-ep-tiny", "box-ep", "box-evp", "box-maxwell", "box-elastic-nomix"]
+# box-ep-100k: 103 680 tets -- many blocks per kernel, and more elements than the L2 prefetch
+# distance of the element kernels (65 536), so that path runs too
+CASES = ["box-ep-tiny", "box-ep", "box-evp", "box-maxwell", "box-elastic-nomix", "box-ep-100k"]
 
 
 def compare(got, d, prefix, fields, tol=TOL):
@@ -209,3 +211,50 @@ def test_average_fields():
     for a, b in zip(h.download_averages(), (coord0, strain0, stress_avg, dpl_avg)):
         assert np.array_equal(a, b)
     g.close(); h.close()
+
+
+def test_mesh_quality_reductions_at_scale():
+    """Size-independent check of the device reductions of bad_mesh_quality on a 1 M-tet box with
+    seeded node jitter (thousands of blocks, ties impossible to arrange by hand): the worst
+    element, its quality, the first tiny element and the first displaced bottom node equal a numpy
+    restatement of geometry.cxx:1873-1927 / remeshing.cxx:2764-2793 on the same arrays."""
+    import sys
+    from conftest import ROOT
+    sys.path.insert(0, ROOT)
+    import bench
+    from dynearthsol_b200 import boxmesh
+    prob = bench.build_problem("1M")
+    N, E = prob["nnode"], prob["nelem"]
+    rng = np.random.default_rng(20261104)
+    coord = prob["state"]["coord"].reshape(3, N).copy()
+    res = bench.SIZES["1M"][3]
+    coord += rng.uniform(-0.2, 0.2, size=coord.shape) * res
+    conn = prob["mesh"]["connectivity"].reshape(4, E)
+    vol = boxmesh.tet_volumes(coord, conn)
+    g, dt = bench.make_model(prob, 0)
+    g.upload_state(coord=coord, volume=vol)
+    p = [coord[:, conn[i]] for i in range(4)]
+
+    def area(a, b, c):
+        ab, ac = b - a, c - a
+        d0 = ab[1] * ac[2] - ab[2] * ac[1]
+        d1 = ab[2] * ac[0] - ab[0] * ac[2]
+        d2 = ab[0] * ac[1] - ab[1] * ac[0]
+        return np.sqrt(d0 * d0 + d1 * d1 + d2 * d2) / 2
+
+    asum = area(p[0], p[1], p[2]) + area(p[0], p[1], p[3]) + area(p[2], p[3], p[0]) + area(p[2], p[3], p[1])
+    quality = 216 * np.sqrt(3.0) * vol * vol / (asum * asum * asum)
+    xl, yl, zl, _ = bench.SIZES["1M"]
+    small_size = float(np.median(vol)) / (0.118 * res ** 3)       # half the elements are "too small"
+    code, idx, mq, q = g.mesh_quality(smallest_size=small_size, resolution=res, max_boundary_distortion=0.1,
+                                      min_quality=0.4, xlength=xl, ylength=yl, zlength=zl, remeshing_option=11)
+    smallest_vol = small_size * 0.118 * res ** 3
+    assert q.first_small_elem == int(np.nonzero(vol < smallest_vol)[0][0])
+    assert (code, idx) == (3, q.first_small_elem)
+    w = int(np.argmin(quality))
+    assert q.worst_elem == w
+    assert abs(q.worst_quality - quality[w]) <= 1e-13 * quality[w]
+    bottom = np.nonzero(((prob["mesh"]["bcflag"] & 16) != 0) & (np.abs(coord[2] + zl) > 0.1 * res))[0]
+    assert q.first_bottom_node == (int(bottom[0]) if len(bottom) else -1)
+    assert abs(q.bottom_value - coord[2, q.first_bottom_node]) == 0 if len(bottom) else True
+    g.close()
