@@ -226,9 +226,13 @@ def build_support(nnode, conn):
     return idx.astype(np.int32), arr, lidx
 
 
-def boundary_topology(coord, conn, bcflag, support=None):
+def boundary_topology(coord, conn, bcflag, support=None, elem_key=None):
     """bnodes, bfacets, connectivity_surface, top_elems, surface info, normals and edges.
-    Returns a dict with the DesMesh keys (dynearthsol_b200.core.DesGpu.upload_mesh)."""
+    Returns a dict with the DesMesh keys (dynearthsol_b200.core.DesGpu.upload_mesh).
+    elem_key [E]: sort key of the elements for the facet lists (default: the element id).  A
+    rank that stores its elements in another order than the global one (multigpu: interior
+    elements first) passes the global order here, so that every per-node sum over facets keeps
+    the single-GPU order."""
     N = coord.shape[1]
     E = conn.shape[1]
     m = {"nnode": N, "nelem": E, "connectivity": conn, "bcflag": bcflag}
@@ -248,7 +252,7 @@ def boundary_topology(coord, conn, bcflag, support=None):
                 fs.append(np.full(e.size, f, dtype=np.int32))
         if es:
             e = np.concatenate(es); f = np.concatenate(fs)
-            o = np.lexsort((f, e))
+            o = np.lexsort((f, e if elem_key is None else elem_key[e]))
             pairs = np.stack([e[o], f[o]], axis=1).reshape(-1)
         else:
             pairs = np.zeros(0, dtype=np.int32)

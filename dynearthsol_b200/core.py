@@ -130,6 +130,7 @@ ABI_SYMBOLS = [
     "des_gpu_event_record", "des_gpu_event_elapsed_ms",
     "des_gpu_step_segment", "des_gpu_set_stream", "des_gpu_set_halo", "des_gpu_halo_buffers",
     "des_gpu_halo_width", "des_gpu_halo_pack", "des_gpu_halo_unpack",
+    "des_gpu_set_interior", "des_gpu_step_segment_part",
     "des_gpu_mesh_quality", "des_quality_verdict", "des_gpu_average_fields",
     "des_gpu_download_averages",
     "des_gpu_build_support", "des_gpu_find_boundary_facets", "des_host_boundary_flags",
@@ -180,6 +181,8 @@ def load_library():
     L.des_gpu_event_elapsed_ms.argtypes = [H, C.c_int, C.c_int, _DP]
     L.des_gpu_step_segment.argtypes = [H, C.c_int, C.c_double, C.c_double]
     L.des_gpu_set_stream.argtypes = [H, C.c_void_p, C.c_int]
+    L.des_gpu_set_interior.argtypes = [H, C.c_int]
+    L.des_gpu_step_segment_part.argtypes = [H, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p]
     L.des_gpu_set_halo.argtypes = [H, C.c_int, _IP, C.c_int, _IP]
     L.des_gpu_halo_buffers.argtypes = [H, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
     L.des_gpu_halo_width.argtypes = [C.c_int]
@@ -499,6 +502,12 @@ class DesGpu:
 
     def step_segment(self, seg, dt, time=0.0):
         self._ck(self.lib.des_gpu_step_segment(self.h, int(seg), float(dt), float(time)))
+
+    def set_interior(self, n_interior):
+        self._ck(self.lib.des_gpu_set_interior(self.h, int(n_interior)))
+
+    def step_segment_part(self, seg, part, dt, time=0.0, stream_ptr=None):
+        self._ck(self.lib.des_gpu_step_segment_part(self.h, seg, part, dt, time, stream_ptr))
 
     def set_stream(self, stream_ptr):
         """Run on the caller's CUDA stream (an integer cudaStream_t; 0 = legacy default stream)."""

@@ -51,6 +51,8 @@ struct DesGpu {
     double *send_buf = nullptr, *recv_buf = nullptr;
     bool own_stream = true;
     bool seg_rot = false;               // rotation pending for segment 1 of the current step
+    bool seg_tail_mass = false;         // volume/mass of the previous step pending for segment 0
+    int n_interior = 0;                 // leading elements that touch no ghost node (des_gpu_set_interior)
     int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
     // internal element order: DES_ELEM_ORDER=1 stores elements sorted by smallest node index.
     // Off by default: measured on B200 it cuts the lines a warp's gathers touch by 40 % but the
@@ -458,6 +460,8 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     Dev &D = h->D;
     const int N = m->nnode, E = m->nelem;
     D.nnode = N; D.nelem = E;
+    D.e0 = 0; D.e1 = E;
+    h->n_interior = E;
     int rc;
     // internal element order: stable counting sort by smallest node index -- consecutive
     // elements then share nodes, so a warp's gathers touch ~40 % fewer 128-byte lines than in
@@ -749,36 +753,42 @@ int des_gpu_sync(DesGpu *h)
 //   segment 4: edvacc_surf, correct_surface_element (the host's surface-marker routines run
 //              here on quality-check steps, bc.cxx:1829-1843, between segments 4 and 5)
 //   segment 5: volume swap; defers compute_volume / compute_mass / rotate_stress (no kernel)
-int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
+// part: -1 = the whole segment; segments 0..2 also run in three parts so that a multi-GPU host
+// can overlap the ghost exchange that precedes the segment with most of its element kernel:
+// 0 = element kernel on the elements that touch no ghost node (des_gpu_set_interior),
+// 1 = element kernel on the others, 2 = the rest of the segment (node kernel).
+static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
 {
-    if (!h) return DES_E_ARG;
-    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
-    if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
-    if (seg < 0 || seg > 5) return fail(h, DES_E_ARG, "segment must be 0..5");
-    if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
-    Dev &D = h->D;
-    const int N = D.nnode, E = D.nelem;
+    Dev &D0 = h->D;
+    const int N = D0.nnode;
     const int mm = h->hp.has_moving_mesh;
     const int hf = head_flags(h);
+    const bool do_elem = part != 2, do_node = part == -1 || part == 2;
+    Dev D = D0;                                 // the element kernels' view: range [e0, e1)
+    if (part == 0) D.e1 = h->n_interior;
+    else if (part == 1) D.e0 = h->n_interior;
+    const int E = D.e1 - D.e0;                  // launch size of the element kernels
     if (seg == 0) {
-    const bool tail = h->tail_pending;
-    const bool tail_mass = tail && mm;
-    h->seg_rot = tail && (h->hp.rheol_type & DES_RH_ELASTIC);
+    if (part <= 0) {
+        const bool tail = h->tail_pending;
+        h->seg_tail_mass = tail && mm;
+        h->seg_rot = tail && (h->hp.rheol_type & DES_RH_ELASTIC);
+    }
     // E-A / N-A
-    if (tail_mass) {
-        LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, DES_EA_BLOCK, h->P, D, 3, hf);
-        LAUNCH(KC_NODE_A, (k3_node_a<true>), N, 256, h->P, D, dt, hf);
+    if (h->seg_tail_mass) {
+        if (do_elem) LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, DES_EA_BLOCK, h->P, D, 3, hf);
+        if (do_node) LAUNCH(KC_NODE_A, (k3_node_a<true>), N, 256, h->P, D0, dt, hf);
     }
     else {
-        LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, DES_EA_BLOCK, h->P, D, 0, hf);
-        LAUNCH(KC_NODE_A, (k3_node_a<false>), N, 256, h->P, D, dt, hf);
+        if (do_elem) LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, DES_EA_BLOCK, h->P, D, 0, hf);
+        if (do_node) LAUNCH(KC_NODE_A, (k3_node_a<false>), N, 256, h->P, D0, dt, hf);
     }
-    h->tail_pending = false;
+    if (do_node) h->tail_pending = false;
     }
     else if (seg == 1) {
     const bool rot = h->seg_rot;
     // E-B / N-B
-    {
+    if (do_elem) {
         const double dtr = rot ? h->dt_prev : 0.0;
 #define EB_CASE(S, R, A) switch (h->hp.rheol_type) { \
         case DES_RH_ELASTIC: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_ELASTIC, A>), E, 128, h->P, D, dt, dtr, afirst); break; \
@@ -787,9 +797,9 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
         default:             LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EVP, A>), E, 128, h->P, D, dt, dtr, afirst); break; }
         const bool single = h->hp.nmat == 1;
         // a deferred Output::average_fields rides on the rotation (des_gpu_average_fields)
+        if (!rot && h->avg_pending) { int rc = average_now(h); if (rc) return rc; }
         const bool avg = rot && h->avg_pending != 0;
         const int afirst = (h->avg_pending == 2) ? 1 : 0;
-        if (!rot && h->avg_pending) { int rc = average_now(h); if (rc) return rc; }
         if (single && avg) EB_CASE(true, true, true)
         else if (avg) EB_CASE(false, true, true)
         else if (single && rot) EB_CASE(true, true, false)
@@ -797,43 +807,80 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
         else if (rot) EB_CASE(false, true, false)
         else EB_CASE(false, false, false)
 #undef EB_CASE
-        if (avg) h->avg_pending = 0;
+        if (avg && (part == -1 || part == 1)) h->avg_pending = 0;      // both element parts have taken it
     }
-    if (h->hp.is_using_mixed_stress) {
-        LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
+    if (do_node && h->hp.is_using_mixed_stress) {
+        LAUNCH(KC_NODE_B, k_node_b, N, 256, D0);
     }
     }
     else if (seg == 2) {
     // E-C / N-C
-    LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
+    if (do_elem) {
     if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
     else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
+    }
+    if (do_node) {
+    LAUNCH(KC_SBC, k_sbc_facets, D0.nsbc_facets, 128, h->P, D0, h->compensation_pressure);
     int bc_z1 = h->hp.vbc_types[5];
     if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
-    LAUNCH(KC_NODE_C, k3_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
+    LAUNCH(KC_NODE_C, k3_node_c, N, 256, h->P, D0, dt, bc_z1, mm ? 15 : 7);
+    }
     }
     else if (seg == 3) {
-    if (mm && h->hp.surface_process_option == 1 && D.ntop > 0) {
-        CK(cudaMemsetAsync(D.maxdh_bits, 0, sizeof(unsigned long long), h->stream));
-        LAUNCH(KC_SURFACE, k_surf_facets, D.etop, 128, D);
-        LAUNCH(KC_SURFACE, k_surf_nodes, D.ntop, 128, h->P, D, dt);
+    if (mm && h->hp.surface_process_option == 1 && D0.ntop > 0) {
+        CK(cudaMemsetAsync(D0.maxdh_bits, 0, sizeof(unsigned long long), h->stream));
+        LAUNCH(KC_SURFACE, k_surf_facets, D0.etop, 128, D0);
+        LAUNCH(KC_SURFACE, k_surf_nodes, D0.ntop, 128, h->P, D0, dt);
         h->surf_ran = true;
     }
     }
     else if (seg == 4) {
     if (mm) {
-        if (h->hp.surface_process_option == 1 && D.ntop > 0) LAUNCH(KC_SURFACE, k_surf_edvacc, D.etop, 128, D);
-        LAUNCH(KC_SURFACE, k_surf_correct_elems, D.ntop_elems, 128, D);
+        if (h->hp.surface_process_option == 1 && D0.ntop > 0) LAUNCH(KC_SURFACE, k_surf_edvacc, D0.etop, 128, D0);
+        LAUNCH(KC_SURFACE, k_surf_correct_elems, D0.ntop_elems, 128, D0);
     }
     }
     else {
-    if (mm) std::swap(D.volume, D.volume_old);      // dynearthsol.cxx:466-470
+    if (mm) std::swap(D0.volume, D0.volume_old);      // dynearthsol.cxx:466-470
     h->tail_pending = true;
     h->dt_prev = dt;
     h->last_dt = dt;
     }
     CK(cudaGetLastError());
     return DES_OK;
+}
+
+int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
+{
+    if (!h) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
+    if (seg < 0 || seg > 5) return fail(h, DES_E_ARG, "segment must be 0..5");
+    if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
+    return segment_impl(h, seg, -1, dt, time);
+}
+
+int des_gpu_set_interior(DesGpu *h, int n_interior)
+{
+    if (!h) return DES_E_ARG;
+    if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    if (n_interior < 0 || n_interior > h->D.nelem) return fail(h, DES_E_ARG, "n_interior out of range");
+    h->n_interior = n_interior;
+    return DES_OK;
+}
+
+int des_gpu_step_segment_part(DesGpu *h, int seg, int part, double dt, double time, void *cuda_stream)
+{
+    if (!h) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
+    if (seg < 0 || seg > 2 || part < 0 || part > 2) return fail(h, DES_E_ARG, "segment 0..2, part 0..2");
+    if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
+    cudaStream_t keep = h->stream;
+    if (cuda_stream) h->stream = static_cast<cudaStream_t>(cuda_stream);
+    const int rc = segment_impl(h, seg, part, dt, time);
+    h->stream = keep;
+    return rc;
 }
 
 int des_gpu_step(DesGpu *h, double dt, double time, int steps)

@@ -62,6 +62,9 @@ struct Dev {
     const unsigned char *ghost;
     // Output::average_fields accumulators (des_aux.cuh), NULL until des_gpu_average_fields is used
     double *avg_stress, *avg_strain0, *avg_dpl;     // [6E], [6E], [E]
+    // element range [e0, e1) the v2 element kernels (k2_elem_a, k2_elem_b, k_elem_c) work on:
+    // the whole mesh, or -- multi-GPU overlap -- the elements that touch no ghost node / the rest
+    int e0, e1;
     // L2 prefetch distance of the element kernels, in elements (0 = off): thread e asks L2 for
     // the streamed rows of element e + pf, so that block finds them in L2 instead of HBM
     int pf;
@@ -377,8 +380,8 @@ template <bool SINGLE, bool MIXED>
 __global__ void __launch_bounds__(256)
 k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
 {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= D.nelem) return;
+    const int e = D.e0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= D.e1) return;
     const int nmat = SINGLE ? 1 : P.nmat;
     const int E = D.nelem;
     // all loads first: the stores of the corrected stress diagonal below would otherwise

@@ -47,8 +47,8 @@ __global__ void DES_EA_BOUNDS
 k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int tail_flags, int head_flags)
 {
     // tail_flags: 1 volume, 2 mass contributions;  head_flags: 1 T-diffusion, 4 tr(edot)*vol
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= D.nelem) return;
+    const int e = D.e0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= D.e1) return;
     const int nmat = SINGLE ? 1 : P.nmat;
     // every load of the kernel is issued here, before the first use of any of them: the
     // mid-kernel store of volume[e] (which may alias, as far as the compiler knows) and the
@@ -163,8 +163,8 @@ __global__ void DES_EB_BOUNDS
 k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot,
           int avg_first = 0)
 {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= D.nelem) return;
+    const int e = D.e0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= D.e1) return;
     const int nmat = SINGLE ? 1 : P.nmat;
     const int E = D.nelem;
     const int4 c = D.conn[e];

@@ -59,7 +59,7 @@ HALO_WIDTH = (2, 1, 6, 2)   # des_gpu_halo_width(phase)
 class DistModel:
     """The reference's step loop on one rank of an element-partitioned mesh."""
 
-    def __init__(self, g, plan, device, group=None):
+    def __init__(self, g, plan, device, group=None, n_interior=None, overlap=None):
         import torch
         self.g, self.plan, self.group = g, plan, group
         self.device = torch.device("cuda", device)
@@ -74,6 +74,17 @@ class DistModel:
         self.recv_buf = device_tensor(rp, plan.recv_nodes.size * 7, self.device)
         self.x = HaloExchanger(plan, self.send_buf, self.recv_buf, group)
         self.exchanges = 0
+        # overlap of the exchanges that precede E-B and E-C with those kernels' run over the
+        # elements that touch no ghost node (the first n_interior, partition.interior_first):
+        # they go to a side stream while the messages are in flight (DES_OVERLAP=0 turns it off)
+        if overlap is None:
+            overlap = os.environ.get("DES_OVERLAP", "1") != "0"
+        self.overlap = bool(overlap) and n_interior is not None and 0 < n_interior
+        if self.overlap:
+            g.set_interior(n_interior)
+            self.side = torch.cuda.Stream(self.device)
+            self.ev_main = torch.cuda.Event()
+            self.ev_side = torch.cuda.Event()
 
     def exchange(self, phase):
         self.g.halo_pack(phase)
@@ -81,15 +92,35 @@ class DistModel:
         self.g.halo_unpack(phase)
         self.exchanges += 1
 
+    def exchange_then_segment(self, phase, seg, dt, time):
+        """exchange(phase) followed by segment seg, with the segment's element kernel on the
+        interior elements running while the messages are in flight."""
+        g = self.g
+        if not self.overlap:
+            self.exchange(phase)
+            g.step_segment(seg, dt, time)
+            return
+        g.halo_pack(phase)
+        self.ev_main.record(self.stream)
+        self.side.wait_event(self.ev_main)              # the previous node kernel has finished
+        g.step_segment_part(seg, 0, dt, time, self.side.cuda_stream)
+        self.ev_side.record(self.side)
+        self.x.exchange(HALO_WIDTH[phase])
+        g.halo_unpack(phase)
+        g.step_segment_part(seg, 1, dt, time)           # the elements that read ghost nodes
+        self.stream.wait_event(self.ev_side)
+        g.step_segment_part(seg, 2, dt, time)           # the node gather needs both
+        self.exchanges += 1
+
     def step(self, dt, time=0.0, steps=0):
         g = self.g
         mixed = bool(g.param.is_using_mixed_stress)
         g.step_segment(0, dt, time)
-        self.exchange(0)
-        g.step_segment(1, dt, time)
+        self.exchange_then_segment(0, 1, dt, time)
         if mixed:
-            self.exchange(1)
-        g.step_segment(2, dt, time)
+            self.exchange_then_segment(1, 2, dt, time)
+        else:
+            g.step_segment(2, dt, time)
         self.exchange(2)
         g.step_segment(3, dt, time)
         if g.param.surface_process_option == 1 and g.param.has_moving_mesh:
@@ -128,11 +159,19 @@ class DistModel:
         return dt, time, steps
 
 
-def local_mesh(coord, conn, bcflag):
+def local_mesh(coord, conn, bcflag, perm=None):
     """DesMesh dict of a rank's sub-mesh (box boundaries: flags decide what is a boundary
-    facet, exactly as on the global mesh, so partition cuts create none)."""
+    facet, exactly as on the global mesh, so partition cuts create none).  conn is in the global
+    relative order; perm (partition.interior_first) is the order the device stores the elements
+    in -- the support and facet lists keep the GLOBAL order, which is the summation order."""
     sup = core.host_build_support(coord.shape[1], conn)
-    return bm.boundary_topology(coord, conn, bcflag, support=sup)
+    if perm is None:
+        return bm.boundary_topology(coord, conn, bcflag, support=sup)
+    inv = np.empty(perm.size, dtype=np.int32)
+    inv[perm] = np.arange(perm.size, dtype=np.int32)
+    sup = (sup[0], inv[sup[1]], sup[2])
+    return bm.boundary_topology(coord, np.ascontiguousarray(conn[:, perm]), bcflag, support=sup,
+                                elem_key=np.asarray(perm))
 
 
 def init_model(mesh, phys, state, comp_p, device):
@@ -153,7 +192,9 @@ def build_box_rank(dims, rank, world, phys_overrides=None):
     boxes = partition.grid_boxes(nx, ny, nz, (xl, yl, zl), world)
     coord, conn, bcflag, key, owner = bm.regular_box_part(xl, yl, zl, nx, ny, nz, rank, boxes)
     plan = partition.halo_plan(rank, conn, owner, key)
-    mesh = local_mesh(coord, conn, bcflag)
+    perm, n_interior = partition.interior_first(conn, owner, rank)
+    mesh = local_mesh(coord, conn, bcflag, perm)
+    conn = mesh["connectivity"]                  # device order from here on
     phys = dict(bm.TEST3D_PHYSICS)
     phys["zlength"] = zl
     if phys_overrides:
@@ -164,6 +205,7 @@ def build_box_rank(dims, rank, world, phys_overrides=None):
     own_elems = int((owner[conn].min(axis=0) == rank).sum())     # each element counted on one rank
     return dict(mesh=mesh, phys=phys, state=state, comp_p=comp_p, plan=plan, owner=owner, key=key,
                 nelem_local=conn.shape[1], nnode_local=coord.shape[1], nelem_owned=own_elems,
+                n_interior=n_interior,
                 cells=(nx - 1, ny - 1, nz - 1), nelem_global=(nx - 1) * (ny - 1) * (nz - 1) * 5,
                 nnode_global=nx * ny * nz)
 
@@ -185,7 +227,7 @@ def bench_main(a, rank, world, local_rank, W, K):
     t0 = time.time()
     prob = build_box_rank((xl, yl, zl, res), rank, world)
     g = init_model(prob["mesh"], prob["phys"], prob["state"], prob["comp_p"], local_rank)
-    m = DistModel(g, prob["plan"], local_rank)
+    m = DistModel(g, prob["plan"], local_rank, n_interior=prob["n_interior"])
     g.call("apply_vbcs", 0.0)
     g.call("compute_mass")
     dt0 = m.compute_dt()
@@ -257,7 +299,9 @@ def bench_main(a, rank, world, local_rank, W, K):
                                                            + (E, prob["nnode_global"])),
                            "element_order": "reference", "l2": "working set per GPU >> 126 MB L2",
                            "parallelism": "%d GPUs: RCB node-box partition, one-element halo, ghost-node exchange "
-                                          "(NCCL send/recv) at the 3 nodal barriers + surface diffusion, allreduce(min/max) for dt" % world,
+                                          "(NCCL send/recv) at the 3 nodal barriers + surface diffusion%s, allreduce(min/max) for dt"
+                                          % (world, ", the two exchanges before E-B / E-C overlapped with those kernels' interior elements"
+                                             if m.overlap else ""),
                            "redundant_element_fraction": float(stats[0].item()) / E - 1.0,
                            "ghost_nodes_sent_per_step_total": float(stats[1].item())},
                 "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,

@@ -70,6 +70,16 @@ def local_subset(conn, owner, rank):
     return elem_gid, node_gid, conn_local
 
 
+def interior_first(conn_local, owner_local, rank):
+    """Stable reordering of a rank's elements: those that touch no ghost node first.  Returns
+    (perm, n_interior) with new element i = old element perm[i].  The ghost exchange that
+    precedes an element kernel can then overlap with the kernel's run over [0, n_interior)."""
+    ghost = owner_local != rank
+    dep = ghost[conn_local[0]] | ghost[conn_local[1]] | ghost[conn_local[2]] | ghost[conn_local[3]]
+    perm = np.concatenate([np.nonzero(~dep)[0], np.nonzero(dep)[0]]).astype(np.int64)
+    return perm, int((~dep).sum())
+
+
 class HaloPlan:
     """Who sends what to whom.  For neighbour ranks in ascending order:
     send_nodes / recv_nodes are local node indices concatenated over neighbours, each

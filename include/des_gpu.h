@@ -270,6 +270,15 @@ int des_gpu_isostasy_constrain_velocity(DesGpu *h);
  *   des_gpu_halo_pack / _unpack   gather into / scatter from the buffers, after segment
  *                        `phase` of des_gpu_step_segment */
 int des_gpu_set_stream(DesGpu *h, void *cuda_stream, int own);
+/* Overlap of a ghost exchange with the element kernel that follows it.  The host orders its
+ * local elements so that the first n_interior touch no ghost node (des_gpu_set_interior) and
+ * runs segments 0..2 in parts: 0 = element kernel on those elements, on `cuda_stream` (NULL =
+ * the handle's stream) -- it needs nothing the exchange delivers, so it runs while the messages
+ * are in flight; 1 = element kernel on the remaining elements, after the unpack; 2 = the rest
+ * of the segment (its node gather), after both.  Ordering between streams is the host's job
+ * (events).  Parts 0,1,2 in order == des_gpu_step_segment(seg). */
+int des_gpu_set_interior(DesGpu *h, int n_interior);
+int des_gpu_step_segment_part(DesGpu *h, int seg, int part, double dt, double time, void *cuda_stream);
 int des_gpu_set_halo(DesGpu *h, int nsend, const int *send_nodes, int nrecv, const int *recv_nodes);
 int des_gpu_halo_buffers(DesGpu *h, void **send_buf, void **recv_buf);
 int des_gpu_halo_width(int phase);

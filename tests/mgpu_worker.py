@@ -17,7 +17,7 @@ torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
 prob = mg.build_box_rank(BOX, rank, world)
 g = mg.init_model(prob["mesh"], prob["phys"], prob["state"], prob["comp_p"], lr)
-m = mg.DistModel(g, prob["plan"], lr)
+m = mg.DistModel(g, prob["plan"], lr, n_interior=prob["n_interior"])
 g.call("apply_vbcs", 0.0)
 g.call("compute_mass")
 dt = m.compute_dt()

@@ -299,3 +299,36 @@ def test_two_ranks_nccl_bit_identical(tmp_path):
             pos = inv[np.searchsorted(gkey[inv], d["key"][own])]
             got[:, pos] = d[k].reshape(c, -1)[:, own]
         assert np.array_equal(got.reshape(-1), ref[k]), k
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_interior_first_order_keeps_the_summation_order(world):
+    """The device order of a rank's elements (ghost-free elements first, for the overlap of the
+    exchanges with E-B / E-C) must not change any per-node sum: support and facet lists stay in
+    the global element order."""
+    from dynearthsol_b200 import multigpu as mg
+    xl, yl, zl, res = BOX
+    nx, ny, nz = bm.grid_dims(xl, yl, zl, res)
+    boxes = pt.grid_boxes(nx, ny, nz, (xl, yl, zl), world)
+    for rank in range(world):
+        coord, conn, bcflag, key, owner = bm.regular_box_part(xl, yl, zl, nx, ny, nz, rank, boxes)
+        perm, nint = pt.interior_first(conn, owner, rank)
+        E = conn.shape[1]
+        assert sorted(perm.tolist()) == list(range(E))
+        ghost = owner != rank
+        dep = ghost[conn].any(axis=0)
+        assert not dep[perm[:nint]].any() and dep[perm[nint:]].all()
+        assert np.all(np.diff(perm[:nint]) > 0) and np.all(np.diff(perm[nint:]) > 0)      # stable
+        plain = mg.local_mesh(coord, conn, bcflag)
+        re = mg.local_mesh(coord, conn, bcflag, perm)
+        assert np.array_equal(re["connectivity"], conn[:, perm])
+        # same support entries, in the same (global) order, renamed
+        assert np.array_equal(re["support_idx"], plain["support_idx"])
+        assert np.array_equal(perm[re["support_arr"]], plain["support_arr"])
+        assert np.array_equal(re["support_lidx"], plain["support_lidx"])
+        for b in range(10):
+            a, p = re["bfacets%d" % b].reshape(-1, 2), plain["bfacets%d" % b].reshape(-1, 2)
+            assert np.array_equal(perm[a[:, 0]], p[:, 0]) and np.array_equal(a[:, 1], p[:, 1])
+        assert np.array_equal(re["connectivity_surface"], plain["connectivity_surface"])
+        assert np.array_equal(re["elem_and_nodes"], plain["elem_and_nodes"])
+        assert np.array_equal(re["support_surf_arr"], plain["support_surf_arr"])
