@@ -182,10 +182,13 @@ def _owned_merge(parts, outs, N, E):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("nparts", [2, 3])
-def test_parts_on_one_gpu_bit_identical(nparts):
+@pytest.mark.parametrize("nparts,overlap", [(2, False), (3, False), (2, True), (3, True)])
+def test_parts_on_one_gpu_bit_identical(nparts, overlap):
     """Ranks emulated sequentially on one device (no kernel waits on another): the segments,
-    pack/unpack kernels and the exchange plan give the single-handle result bit for bit."""
+    pack/unpack kernels and the exchange plan give the single-handle result bit for bit.
+    overlap: every part stores its ghost-free elements first and runs E-B / E-C over them
+    BEFORE the exchange they overlap with in the real run delivers the ghost values
+    (des_gpu_set_interior, des_gpu_step_segment_part)."""
     import torch
     from dynearthsol_b200 import core, multigpu as mg
     coord, conn, bcflag, phys, state, comp_p = _problem()
@@ -207,8 +210,14 @@ def test_parts_on_one_gpu_bit_identical(nparts):
     dev = torch.device("cuda", 0)
     gs, bufs = [], []
     for p in parts:
+        perm, nint = (pt.interior_first(p["conn"], p["owner"], p["rank"]) if overlap else (None, 0))
+        if overlap:
+            p["elem_gid"] = p["elem_gid"][perm]
         st = pt.restrict_state(state, p["elem_gid"], p["node_gid"], N, E)
-        g = mg.init_model(mg.local_mesh(p["coord"], p["conn"], p["bcflag"]), phys, st, comp_p, 0)
+        g = mg.init_model(mg.local_mesh(p["coord"], p["conn"], p["bcflag"], perm), phys, st, comp_p, 0)
+        if overlap:
+            assert 0 < nint < p["conn"].shape[1]
+            g.set_interior(nint)
         g.set_halo(p["plan"].send_nodes, p["plan"].recv_nodes)
         sp, rp = g.halo_buffers()
         bufs.append((mg.device_tensor(sp, p["plan"].send_nodes.size * 7, dev),
@@ -248,8 +257,17 @@ def test_parts_on_one_gpu_bit_identical(nparts):
     for s in range(1, 13):
         t += dt
         for seg in range(6):
-            for g in gs:
-                g.step_segment(seg, dt, t)
+            if overlap and seg in (1, 2):
+                # part 0 ran before exchange(seg - 1) below; the ghost-dependent rest follows it
+                for g in gs:
+                    g.step_segment_part(seg, 1, dt, t)
+                    g.step_segment_part(seg, 2, dt, t)
+            else:
+                for g in gs:
+                    g.step_segment(seg, dt, t)
+            if overlap and seg in (0, 1):
+                for g in gs:
+                    g.step_segment_part(seg + 1, 0, dt, t)      # interior elements: ghosts still stale
             if seg < 4:
                 exchange(seg)
         if s % 10 == 0:
