@@ -159,8 +159,8 @@ def run_steps(g, n, dt, t, s):
 
 def read_traffic():
     """DRAM bytes per element and launch of each kernel, from the committed ncu --set full
-    capture (profiles/r01_v6_traffic.json); None if absent."""
-    p = os.path.join(ROOT, "profiles", "r01_v6_traffic.json")
+    capture (profiles/r01_v8_traffic.json); None if absent."""
+    p = os.path.join(ROOT, "profiles", "r01_v8_traffic.json")
     if os.path.exists(p):
         return json.load(open(p))
     return None
