@@ -217,3 +217,27 @@ def test_host_topology_builders_match_reference():
                                    d["mesh_connectivity_surface"])
     for k in ("top_nodes", "top_elems", "elem_and_nodes", "support_surf_idx", "support_surf_arr"):
         assert np.array_equal(s[k], d["mesh_" + k]), k
+
+
+def test_new_entry_points_reject_bad_arguments_and_have_no_cpu_path():
+    """The device-side builders / reductions fail loudly: NULL arguments -> DES_E_ARG, and on a
+    box without a GPU the two device builders return DES_E_NODEVICE instead of computing on
+    the host."""
+    L = core.load_library()
+    assert L.des_gpu_mesh_quality(None, None, None) == 3
+    assert L.des_gpu_average_fields(None, 0) == 3
+    assert L.des_gpu_download_averages(None, None, None, None, None) == 3
+    assert L.des_gpu_set_interior(None, 0) == 3
+    assert L.des_gpu_step_segment_part(None, 1, 0, 1.0, 0.0, None) == 3
+    assert L.des_gpu_isostasy_constrain_velocity(None) == 3
+    assert L.des_gpu_build_support(0, 4, 1, None, None, None, None) == 3
+    assert L.des_host_boundary_flags(4, 1, None, None, None) == 3
+    # out-of-range segment node
+    seg = np.array([0, 1, 9], dtype=np.int32); flg = np.array([1], dtype=np.int32); bc = np.zeros(4, dtype=np.uint32)
+    assert L.des_host_boundary_flags(4, 1, core._ptr(seg, C.c_int), core._ptr(flg, C.c_int), core._ptr(bc, C.c_uint)) == 3
+    if not have_gpu():
+        conn = np.array([[0], [1], [2], [3]], dtype=np.int32)
+        idx = np.zeros(5, dtype=np.int32); arr = np.zeros(4, dtype=np.int32); lidx = np.zeros(4, dtype=np.int32)
+        rc = L.des_gpu_build_support(0, 4, 1, core._ptr(conn, C.c_int), core._ptr(idx, C.c_int),
+                                     core._ptr(arr, C.c_int), core._ptr(lidx, C.c_int))
+        assert rc == 1
