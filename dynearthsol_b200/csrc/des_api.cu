@@ -205,8 +205,8 @@ int fill_dev_params(DesGpu *h)
     default: return fail(h, DES_E_UNSUPPORTED, "rheology type outside the hot-path scope "
                          "(viscous / rate-and-state / plane strain)");
     }
-    if (p.damping_option < 0 || p.damping_option > 3)
-        return fail(h, DES_E_UNSUPPORTED, "damping_option must be 0..3 (4 = Rayleigh is not built)");
+    if (p.damping_option < 0 || p.damping_option > 4)
+        return fail(h, DES_E_UNSUPPORTED, "damping_option must be 0..4");
     if (p.surface_process_option != 0 && p.surface_process_option != 1)
         return fail(h, DES_E_UNSUPPORTED, "surface_process_option must be 0 or 1 in 3D");
     if (p.ref_pressure_option < 0 || p.ref_pressure_option > 2)
@@ -352,6 +352,17 @@ int tail_flags(const DesGpu *h)
 int head_flags(const DesGpu *h) { return (h->hp.has_thermal_diffusion ? 1 : 0) | 2 | 4; }
 
 // Completes the deferred end-of-step element work (volume, mass, rotation) on its own.
+// compute_mass's ymass column (geometry.cxx:1833,1850-1866), needed only by Rayleigh damping:
+// runs wherever the mass is recomputed.  D.etmp is free at all of those points.
+int ymass_update(DesGpu *h)
+{
+    if (h->hp.damping_option != 4) return DES_OK;
+    LAUNCH(KC_TWIN, k_ymass_elem, h->D.nelem, 256, h->P, h->D, h->D.etmp);
+    LAUNCH(KC_TWIN, k_ymass_node, h->D.nnode, 256, h->D, (const double *)h->D.etmp);
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
 // Output::average_fields on the current device state (output.cxx:317-350), as its own kernels
 int average_now(DesGpu *h)
 {
@@ -380,6 +391,7 @@ int flush_tail(DesGpu *h)
     const int mm = h->hp.has_moving_mesh;
     LAUNCH(KC_ELEM_A, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, h->dt_prev, tail_flags(h), 0);
     if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, false>), h->D.nnode, 256, h->P, h->D, 0.0, 0);
+    if (mm) { int rc = ymass_update(h); if (rc) return rc; }
     h->tail_pending = false;
     CK(cudaGetLastError());
     return average_now(h);      // a deferred average_fields wanted exactly this (rotated) state
@@ -526,6 +538,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     if ((rc = dalloc(h, &D.coord0, h->hp.has_elastic_foundation ? N : 1))) return rc;
     if ((rc = dalloc(h, &D.force, size_t(N) * 3, "force"))) return rc;
     if ((rc = dalloc(h, &D.mass, N, "mass"))) return rc;
+    if (h->hp.damping_option == 4 && (rc = dalloc(h, &D.ymass, N, "ymass"))) return rc;
     if ((rc = dalloc(h, &D.tmass, N, "tmass"))) return rc;
     if ((rc = dalloc(h, &D.volume_n, N, "volume_n"))) return rc;
     if ((rc = dalloc(h, &D.ntmp, N, "ntmp"))) return rc;
@@ -683,6 +696,7 @@ int des_gpu_upload_state(DesGpu *h, const DesState *s)
     UPE(radiogenic_source, const_cast<double *>(D.radiogenic), 1)
 #undef UPE
     UP(force, D.force, N * 3) UP(volume_n, D.volume_n, N) UP(mass, D.mass, N) UP(tmass, D.tmass, N)
+    if (s->mass && (rc = ymass_update(h))) return rc;       // ymass is not part of DesState: rebuilt with the mass
     UP(ntmp, D.ntmp, N) UP(dhacc, D.dhacc, N) UP(edvacc_surf, D.edvacc_surf, size_t(D.etop))
 #undef UP
     CK(cudaStreamSynchronize(h->stream));
@@ -778,6 +792,7 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
     if (h->seg_tail_mass) {
         if (do_elem) LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, DES_EA_BLOCK, h->P, D, 3, hf);
         if (do_node) LAUNCH(KC_NODE_A, (k3_node_a<true>), N, 256, h->P, D0, dt, hf);
+        if (do_node) { int rc = ymass_update(h); if (rc) return rc; }
     }
     else {
         if (do_elem) LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, DES_EA_BLOCK, h->P, D, 0, hf);
@@ -906,6 +921,7 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
         LAUNCH(KC_ELEM_A, (k_elem_a<true, true>), E, 256, h->P, D, h->dt_prev, tail_flags(h), hf);
         if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, true>), N, 256, h->P, D, dt, hf);
         else    LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
+        if (mm) { int rc = ymass_update(h); if (rc) return rc; }
         h->tail_pending = false;
     }
     else {

@@ -102,3 +102,31 @@ __global__ void k_isostasy_velocity(const __grid_constant__ Dev D, int hold_bott
     if (hold_bottom && (D.bcflag[n] & BOUNDZ0)) v.z = 0;
     D.vv[n] = v;
 }
+
+// ---------------------------------------------------------------------------------------
+// ymass for Rayleigh damping (control.damping_option 4): compute_mass's fifth column,
+// geometry.cxx:1833 (element: Young's modulus / 4, material only) and :1850-1866 (nodal sum in
+// support order).  Two small kernels run wherever the mass is recomputed; off the hot path.
+// ---------------------------------------------------------------------------------------
+__global__ void k_ymass_elem(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double *ym)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= D.nelem) return;
+    Markers mk;
+    load_markers(D.elemmarkers, e, P.nmat, mk);
+    const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, P.nmat);
+    const double shearm = harm_mean(P.shear_modulus, mk.cnt, P.nmat);
+    ym[e] = 9 * bulkm * shearm / (3 * bulkm + shearm) / 4;
+}
+__global__ void k_ymass_node(const __grid_constant__ Dev D, const double *__restrict__ ym)
+{
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= D.nnode) return;
+    double acc = 0;
+    for (int k = D.sup_idx[n]; k < D.sup_idx[n + 1]; ++k) {
+        const int ent = D.sup_ent[k];
+        if (ent < 0) break;     // padding
+        acc += ym[ent >> 2];
+    }
+    D.ymass[n] = acc;
+}

@@ -764,11 +764,20 @@ __device__ __forceinline__ void vbc_node(const DevParams &P, unsigned flag, doub
     }
 }
 
-// apply_damping for one component, fields.cxx:483-579 (options 0..3)
-__device__ __forceinline__ double damp(const DevParams &P, double f, double v)
+// apply_damping for one component, fields.cxx:483-579 (options 0..4)
+// crit = 2 sqrt(mass * ymass) of the node (option 4 only)
+__device__ __forceinline__ double damp(const DevParams &P, double f, double v, double crit = 0)
 {
     const double small_vel = 1e-13;
     switch (P.damping_option) {
+    case 4:     // Rayleigh, fields.cxx:547-570
+        if (fabs(v) > small_vel) {
+            const double f_C = P.damping_factor * copysign(f, v);
+            const double f_V = crit * v;
+            const double f_damping = (fabs(f_C) < fabs(f_V)) ? f_V : f_C;
+            f -= f_damping;
+        }
+        break;
     case 1:
         if (fabs(v) > small_vel) f -= P.damping_factor * copysign(f, v);
         break;

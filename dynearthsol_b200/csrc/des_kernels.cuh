@@ -29,6 +29,7 @@ struct Dev {
     double4 *vv;                // {vx, vy, vz, unused}
     double *force;              // [3N] SoA (derived, host-visible)
     double *mass, *tmass, *volume_n, *ntmp;
+    double *ymass;              // nodal sum of Young's moduli, only for damping option 4 (else NULL)
     double4 *coord0;            // only for the elastic foundation
     // element fields (SoA, component-major)
     double *stress, *strain, *strain_rate;      // [6E]
@@ -532,9 +533,10 @@ k_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
         }
         if (P.has_elastic_foundation && (flag & BOUNDZ0))
             f[2] -= P.elastic_foundation_constant * (x.z - D.coord0[n].z);
+        const double crit = (P.damping_option == 4) ? 2.0 * sqrt(D.mass[n] * D.ymass[n]) : 0.0;
         #pragma unroll
         for (int j = 0; j < 3; ++j) {
-            f[j] = damp(P, f[j], v[j]);
+            f[j] = damp(P, f[j], v[j], crit);
             D.force[size_t(j) * N + n] = f[j];
         }
     }

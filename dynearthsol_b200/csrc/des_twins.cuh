@@ -182,6 +182,7 @@ int des_gpu_update_mesh(DesGpu *h, double dt)
     std::swap(h->D.volume, h->D.volume_old);
     LAUNCH(KC_TWIN, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, 0.0, 3, 0);
     LAUNCH(KC_TWIN, (k_node_a<true, false>), h->D.nnode, 256, h->P, h->D, 0.0, 0);
+    if ((rc = ymass_update(h))) return rc;
     CK(cudaGetLastError());
     return DES_OK;
 }
@@ -207,6 +208,7 @@ int des_gpu_compute_mass(DesGpu *h)
     int rc = twin_ready(h); if (rc) return rc;
     LAUNCH(KC_TWIN, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, 0.0, 2, 0);
     LAUNCH(KC_TWIN, (k_node_a<true, false>), h->D.nnode, 256, h->P, h->D, 0.0, 0);
+    if ((rc = ymass_update(h))) return rc;
     CK(cudaGetLastError());
     return DES_OK;
 }

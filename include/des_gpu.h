@@ -56,7 +56,7 @@ typedef struct DesParam {
     double dt_fraction;             /* control.dt_fraction */
     double fixed_dt;                /* control.fixed_dt (0 = dynamic) */
     double characteristic_speed;    /* control.characteristic_speed (0 = use max_vbc_val) */
-    int damping_option;             /* control.damping_option 0..4, fields.cxx:490-575 */
+    int damping_option;             /* control.damping_option 0..4 (4 = Rayleigh), fields.cxx:490-575 */
     int is_quasi_static;            /* control.is_quasi_static */
     int has_thermal_diffusion;      /* control.has_thermal_diffusion */
     int is_using_mixed_stress;      /* control.is_using_mixed_stress -> NMD_stress */

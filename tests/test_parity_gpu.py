@@ -258,3 +258,20 @@ def test_mesh_quality_reductions_at_scale():
     assert q.first_bottom_node == (int(bottom[0]) if len(bottom) else -1)
     assert abs(q.bottom_value - coord[2, q.first_bottom_node]) == 0 if len(bottom) else True
     g.close()
+
+
+@pytest.mark.parametrize("option", [0, 2, 3, 4])
+def test_damping_options(option):
+    """apply_damping (fields.cxx:483-579), the non-default branches: none, proportional, the
+    asymmetric one, and Rayleigh (4), which needs compute_mass's ymass column
+    (geometry.cxx:1833-1866).  One and twenty steps against the reference run with the same
+    control.damping_option."""
+    d = ref_dump("box-ep", [1, 20], sets=(("damping_option", option),))
+    assert int(d["p_damping_option"]) == option
+    g = refmodel.model_from_dump(d)
+    dt = float(d["s0_dt"])
+    g.step(dt, dt, 1)
+    compare(g.download_state(*FIELDS), d, "s1_", FIELDS)
+    g.run(19, dt, dt, 1)
+    compare(g.download_state(*FIELDS), d, "s20_", FIELDS, tol=1e-9)
+    g.close()
