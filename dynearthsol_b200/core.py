@@ -132,7 +132,7 @@ ABI_SYMBOLS = [
     "des_gpu_halo_width", "des_gpu_halo_pack", "des_gpu_halo_unpack",
     "des_gpu_set_interior", "des_gpu_step_segment_part",
     "des_gpu_mesh_quality", "des_quality_verdict", "des_gpu_average_fields",
-    "des_gpu_download_averages",
+    "des_gpu_download_averages", "des_gpu_check_nan",
     "des_gpu_build_support", "des_gpu_find_boundary_facets", "des_host_boundary_flags",
     "des_host_boundary_nodes", "des_host_bucket_facets", "des_host_surface_topology",
 ]
@@ -204,6 +204,7 @@ def load_library():
                                          C.POINTER(C.c_int * (DES_NBDRY + 1)), _IP, _IP]
     L.des_host_surface_topology.argtypes = [C.c_int, C.c_int, _IP, _DP, _IP, _IP, C.c_int, _IP, _IP,
                                             C.c_int, _IP, _IP, _IP, _IP, _IP]
+    L.des_gpu_check_nan.argtypes = [H, C.POINTER(C.c_int)]
     L.des_gpu_average_fields.argtypes = [H, C.c_int]
     L.des_gpu_download_averages.argtypes = [H, _DP, _DP, _DP, _DP]
     for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions, DesQualityParam, DesQuality)):
@@ -555,6 +556,12 @@ class DesGpu:
         code = self.lib.des_quality_verdict(C.byref(qp), C.byref(q), C.byref(idx), C.byref(mq))
         mqv = None if mq.value != mq.value else mq.value
         return code, (None if idx.value == -12345 else idx.value), mqv, q
+
+    def check_nan(self):
+        """check_nan (utils.hpp:323): how many NaN entries the arrays the reference scans hold."""
+        c = C.c_int()
+        self._ck(self.lib.des_gpu_check_nan(self.h, C.byref(c)))
+        return c.value
 
     def average_fields(self, first):
         """Output::average_fields (output.cxx:312) with device-resident accumulators."""

@@ -571,6 +571,10 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     CK(cudaMemsetAsync(D.dpressure, 0, sizeof(double) * E, h->stream));
     CK(cudaMemsetAsync(D.delta_plstrain, 0, sizeof(double) * E, h->stream));
     CK(cudaMemsetAsync(D.ca, 0, sizeof(double) * 8 * E, h->stream));
+    // never-uploaded rows must not hold NaN bit patterns (viscosity is only written by the
+    // Maxwell / EVP branches; des_gpu_check_nan scans it like the reference does)
+    for (double *r : {D.viscosity, D.plstrain, D.volume, D.volume_old, D.edvoldt})
+        CK(cudaMemsetAsync(r, 0, sizeof(double) * E, h->stream));
     // slant-boundary tables
     for (int i = 0; i < DES_NBDRY; ++i)
         for (int d = 0; d < 3; ++d)
@@ -1074,6 +1078,22 @@ int des_quality_verdict(const DesQualityParam *qp, const DesQuality *q, int *ind
     if (min_quality) *min_quality = qq;
     if (qq < qp->min_quality) { if (index) *index = q->worst_elem; return 1; }
     return 0;
+}
+
+// check_nan (utils.hpp:323-385; Output::write_exact_error): integer count, so exact
+int des_gpu_check_nan(DesGpu *h, int *count)
+{
+    if (!h || !count) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    CK(cudaSetDevice(h->device));
+    int rc = flush_tail(h);
+    if (rc) return rc;
+    if (!h->q_nodes) CK(cudaMalloc(&h->q_nodes, sizeof(int) * 2));
+    CK(cudaMemsetAsync(h->q_nodes, 0, sizeof(int), h->stream));
+    LAUNCH(KC_DT, k_check_nan, std::max(h->D.nelem, h->D.nnode), 256, h->D, h->q_nodes);
+    CK(cudaMemcpyAsync(count, h->q_nodes, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DES_OK;
 }
 
 int des_gpu_average_fields(DesGpu *h, int first)

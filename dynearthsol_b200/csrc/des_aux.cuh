@@ -130,3 +130,28 @@ __global__ void k_ymass_node(const __grid_constant__ Dev D, const double *__rest
     }
     D.ymass[n] = acc;
 }
+
+// ---------------------------------------------------------------------------------------
+// check_nan, utils.hpp:323-385: number of NaN entries in the arrays the reference scans
+// (volume, dpressure, viscosity, stress; temperature, tmass, force, vel, coord)
+// ---------------------------------------------------------------------------------------
+__global__ void k_check_nan(const __grid_constant__ Dev D, int *count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t E = D.nelem, N = D.nnode;
+    int c = 0;
+    if (i < D.nelem) {
+        c += isnan(D.volume[i]) + isnan(D.dpressure[i]) + isnan(D.viscosity[i]);
+        #pragma unroll
+        for (int j = 0; j < 6; ++j) c += isnan(D.stress[size_t(j) * E + i]);
+    }
+    if (i < D.nnode) {
+        const double4 x = D.xT[i], v = D.vv[i];
+        c += isnan(x.w) + isnan(D.tmass[i]);
+        c += isnan(x.x) + isnan(x.y) + isnan(x.z) + isnan(v.x) + isnan(v.y) + isnan(v.z);
+        #pragma unroll
+        for (int j = 0; j < 3; ++j) c += isnan(D.force[size_t(j) * N + i]);
+    }
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}

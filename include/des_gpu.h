@@ -221,6 +221,10 @@ int des_gpu_mesh_quality(DesGpu *h, const DesQualityParam *qp, DesQuality *out);
  * only written when the ladder reaches the distortion check) */
 int des_quality_verdict(const DesQualityParam *qp, const DesQuality *q, int *index, double *min_quality);
 
+/* check_nan (utils.hpp:323-385, called by Output::write_exact_error): the number of NaN entries
+ * in volume, dpressure, viscosity, stress, temperature, tmass, force, vel and coord */
+int des_gpu_check_nan(DesGpu *h, int *count);
+
 /* Output::average_fields (dynearthsol.cxx:903; output.cxx:312-352) with device-resident
  * accumulators.  first != 0 (steps % average_interval == 1): snapshot coord, strain, stress,
  * delta_plstrain; otherwise stress_avg += stress, delta_plstrain_avg += delta_plstrain. */

@@ -230,6 +230,7 @@ def test_new_entry_points_reject_bad_arguments_and_have_no_cpu_path():
     assert L.des_gpu_set_interior(None, 0) == 3
     assert L.des_gpu_step_segment_part(None, 1, 0, 1.0, 0.0, None) == 3
     assert L.des_gpu_isostasy_constrain_velocity(None) == 3
+    assert L.des_gpu_check_nan(None, None) == 3
     assert L.des_gpu_build_support(0, 4, 1, None, None, None, None) == 3
     assert L.des_host_boundary_flags(4, 1, None, None, None) == 3
     # out-of-range segment node

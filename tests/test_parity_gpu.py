@@ -275,3 +275,21 @@ def test_damping_options(option):
     g.run(19, dt, dt, 1)
     compare(g.download_state(*FIELDS), d, "s20_", FIELDS, tol=1e-9)
     g.close()
+
+
+def test_check_nan():
+    """check_nan (utils.hpp:323-385) as a device count: zero on a healthy state, and exactly the
+    number of poisoned entries in the arrays the reference scans."""
+    d = ref_dump("box-ep", [1, 20])
+    g = refmodel.model_from_dump(d)
+    dt = float(d["s0_dt"])
+    g.run(3, dt)
+    assert g.check_nan() == 0
+    s = g.download_state("stress", "temperature", "vel", "volume")
+    s["stress"][[5, 2880 + 7, 5 * 2880 + 11]] = np.nan
+    s["temperature"][3] = np.nan
+    s["vel"][[0, 819 + 1]] = np.nan
+    s["volume"][17] = np.nan
+    g.upload_state(**s)
+    assert g.check_nan() == 7
+    g.close()
