@@ -294,11 +294,19 @@ def main():
         cpu_steps = max(1, min(K, 20))
         rate, cores, desc = reference_cpu(cpu_steps, min(W, 3), a.cpu_sample, target_seconds=15.0)
         xl, yl, zl, res = SIZES[size]
+        from dynearthsol_b200 import boxmesh as bm
+        nx, ny, nz = bm.grid_dims(xl, yl, zl, res)
+        nelem_workload = (nx - 1) * (ny - 1) * (nz - 1) * 5
+        # one step of the named workload at the measured rate (the reference cannot initialise a
+        # mesh of that size, so its rate is measured on the bounded sample and is size-independent
+        # to first order: SURVEY.md section 8d)
+        ms_step = (nelem_workload / rate * 1e3) if rate else None
         line = {"impl": "reference", "metric": metric, "value": rate, "unit": unit, "n_gpus": a.gpus,
-                "steps": K, "warmup": W, "ms_per_step": None, "higher_is_better": True,
+                "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": "box %s: test-3d.cfg Mohr-Coulomb + thermal + NMD + surface diffusion" % size,
-                           "sample": desc},
+                           "sample": desc,
+                           "ms_per_step": "extrapolated: %d tets of the named workload / the measured rate" % nelem_workload},
                 "cpu_baseline": {"value": rate, "unit": unit, "cores": cores, "kind": "reference", "sample": desc},
                 "e2e": {"value": rate, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         if rate is None:
