@@ -234,7 +234,9 @@ int fill_dev_params(DesGpu *h)
     P.ref_pressure_option = p.ref_pressure_option;
     P.has_winkler_foundation = p.has_winkler_foundation;
     P.has_water_loading = p.has_water_loading;
-    P.has_elastic_foundation = p.has_elastic_foundation;
+    // the foundation force lives inside apply_stress_bcs, which returns at its first statement
+    // without gravity (bc.cxx:667): no gravity, no foundation force
+    P.has_elastic_foundation = p.has_elastic_foundation && p.gravity != 0;
     P.rheol_type = p.rheol_type; P.nmat = p.nmat; P.mattype_ref = p.mattype_ref;
     int nmemo = 0;
     for (int m = 0; m < p.nmat; ++m) {
@@ -338,6 +340,59 @@ int build_stress_bcs(DesGpu *h, const DesMesh *m)
     if ((rc = upload_new(h, &D.sbc_idx, idx.data(), idx.size()))) return rc;
     if ((rc = upload_new(h, &D.sbc_ent, ent.data(), ent.size()))) return rc;
     CK(cudaStreamSynchronize(h->stream));   // the std::vectors above die here
+    return DES_OK;
+}
+
+// Every index list of DesMesh becomes a gather/scatter index on the device: a malformed mesh
+// (e.g. from a faulty remesh) must come back as DES_E_ARG, not as a sticky CUDA fault.
+int validate_mesh(DesGpu *h, const DesMesh *m)
+{
+    const int N = m->nnode, E = m->nelem;
+    if (!m->connectivity || !m->bcflag || !m->support_idx || !m->support_arr || !m->support_lidx)
+        return fail(h, DES_E_ARG, "null topology array");
+    const size_t n4 = size_t(E) * 4;
+    bool ok = true;
+    #pragma omp parallel for reduction(&&:ok)
+    for (long long k = 0; k < (long long)n4; ++k) {
+        ok = ok && (unsigned)m->connectivity[k] < (unsigned)N;
+        ok = ok && (unsigned)m->support_arr[k] < (unsigned)E && (unsigned)m->support_lidx[k] < 4u;
+    }
+    if (!ok) return fail(h, DES_E_ARG, "connectivity / support entry out of range");
+    if (m->support_idx[0] != 0) return fail(h, DES_E_ARG, "support_idx[0] != 0");
+    for (int n = 0; n < N; ++n)
+        if (m->support_idx[n + 1] < m->support_idx[n]) return fail(h, DES_E_ARG, "support_idx not monotone");
+    for (int i = 0; i < DES_NBDRY; ++i) {
+        if (m->nbfacets[i] < 0 || m->nbnodes[i] < 0 || (m->nbfacets[i] && !m->bfacets[i]) || (m->nbnodes[i] && !m->bnodes[i]))
+            return fail(h, DES_E_ARG, "bad boundary list");
+        for (int k = 0; k < m->nbfacets[i]; ++k)
+            if ((unsigned)m->bfacets[i][2*k] >= (unsigned)E || (unsigned)m->bfacets[i][2*k + 1] >= 4u)
+                return fail(h, DES_E_ARG, "boundary facet out of range");
+        for (int k = 0; k < m->nbnodes[i]; ++k)
+            if ((unsigned)m->bnodes[i][k] >= (unsigned)N) return fail(h, DES_E_ARG, "boundary node out of range");
+    }
+    if (m->ntop < 0 || m->etop < 0 || m->ntop_elems < 0) return fail(h, DES_E_ARG, "negative surface count");
+    if ((m->ntop_elems && !m->top_elems) || (m->ntop && !m->top_nodes) ||
+        (m->etop && (!m->elem_and_nodes || !m->connectivity_surface || !m->support_surf_arr)))
+        return fail(h, DES_E_ARG, "null surface array");
+    for (int k = 0; k < m->ntop_elems; ++k)
+        if ((unsigned)m->top_elems[k] >= (unsigned)E) return fail(h, DES_E_ARG, "top element out of range");
+    for (int k = 0; k < m->ntop; ++k)
+        if ((unsigned)m->top_nodes[k] >= (unsigned)N) return fail(h, DES_E_ARG, "top node out of range");
+    if (m->ntop > 0) {
+        if (!m->support_surf_idx || m->support_surf_idx[0] != 0) return fail(h, DES_E_ARG, "bad support_surf_idx");
+        for (int k = 0; k < m->ntop; ++k)
+            if (m->support_surf_idx[k + 1] < m->support_surf_idx[k]) return fail(h, DES_E_ARG, "support_surf_idx not monotone");
+        for (int k = 0; k < m->support_surf_idx[m->ntop]; ++k)
+            if ((unsigned)m->support_surf_arr[k] >= (unsigned)m->etop) return fail(h, DES_E_ARG, "support_surf entry out of range");
+    }
+    for (size_t k = 0; k < size_t(m->etop) * 3; ++k) {
+        if ((unsigned)m->elem_and_nodes[k] >= (unsigned)m->ntop) return fail(h, DES_E_ARG, "elem_and_nodes entry out of range");
+        if ((unsigned)m->connectivity_surface[k] >= (unsigned)N) return fail(h, DES_E_ARG, "connectivity_surface entry out of range");
+    }
+    if (m->edge_slot)
+        for (int k = 0; k < 100; ++k)
+            if (m->edge_slot[k] >= 0 && (m->edge_slot[k] + 1) * 3 > m->n_edge_vec)
+                return fail(h, DES_E_ARG, "edge_slot points past edge_vec");
     return DES_OK;
 }
 
@@ -475,6 +530,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     D.e0 = 0; D.e1 = E;
     h->n_interior = E;
     int rc;
+    if ((rc = validate_mesh(h, m))) return rc;
     // internal element order: stable counting sort by smallest node index -- consecutive
     // elements then share nodes, so a warp's gathers touch ~40 % fewer 128-byte lines than in
     // the mesh generators' orders (measured: profiles/)
@@ -1172,6 +1228,9 @@ int des_gpu_set_halo(DesGpu *h, int nsend, const int *send_nodes, int nrecv, con
 {
     if (!h || nsend < 0 || nrecv < 0 || (nsend && !send_nodes) || (nrecv && !recv_nodes)) return DES_E_ARG;
     if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    // the halo tables live until the next upload_mesh (pointers handed out by
+    // des_gpu_halo_buffers must stay valid): one plan per uploaded mesh
+    if (h->send_idx || h->recv_idx) return fail(h, DES_E_STATE, "halo already set for this mesh (upload_mesh resets it)");
     CK(cudaSetDevice(h->device));
     for (int i = 0; i < nsend; ++i)
         if (send_nodes[i] < 0 || send_nodes[i] >= h->D.nnode) return fail(h, DES_E_ARG, "send node out of range");

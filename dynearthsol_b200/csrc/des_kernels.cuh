@@ -615,10 +615,12 @@ __global__ void k_surf_nodes(const __grid_constant__ DevParams P, const __grid_c
     dh -= conv;
     D.dh[i] = dh;
     D.xT[n].z += dh;
-    D.dhacc[n] += dh;
-    // a ghost's dh is a partial sum (it is overwritten by the owner's): keep it out of max|dh|
-    if (!D.ghost || !D.ghost[n])
+    // a ghost's dh is a partial sum (it is overwritten by the owner's, and dhacc then takes the
+    // owner's value in k_halo_unpack): keep it out of dhacc and of max|dh|
+    if (!D.ghost || !D.ghost[n]) {
+        D.dhacc[n] += dh;
         atomicMax(D.maxdh_bits, (unsigned long long)__double_as_longlong(fabs(dh)));
+    }
 }
 
 // edvacc_surf loop, bc.cxx:1787-1797 (after the coordinate update)

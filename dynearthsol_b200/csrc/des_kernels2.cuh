@@ -540,6 +540,6 @@ __global__ void k_halo_unpack(int phase, int n, const int *__restrict__ idx, con
     else {
         D.xT[node].z = buf[2 * j];
         const int t = top_of_node[node];
-        if (t >= 0) D.dh[t] = buf[2 * j + 1];
+        if (t >= 0) { D.dh[t] = buf[2 * j + 1]; D.dhacc[node] += buf[2 * j + 1]; }     // the owner's dhacc += dh
     }
 }

@@ -4,7 +4,7 @@
 // oracle/Makefile into oracle/_ref/libdesref.so).  It lets tests/ and the cpu_baseline
 // leg of bench.py drive the reference's own hot functions one by one and read/write
 // the reference's own `Variables` arrays, so that
-//   * the C restatement in oracle/des_oracle.c is pinned against the real thing, and
+//   * the golden fixtures under tests/golden are dumps of the real thing, and
 //   * the CUDA path is compared with the real thing on the GPU box's host cores.
 //
 // It re-states nothing: every numeric statement executed here lives in the reference
@@ -282,6 +282,10 @@ int desref_set(const char *name, const void *in, long nbytes)
                 (*g_var->elemmarkers)[e][m] = src[size_t(e)*nmat + m];
         return 0;
     }
+    if (std::string(name) == "edge_vec") {     // a std::vector the test may grow
+        g_var->edge_vec.assign(static_cast<const double*>(in), static_cast<const double*>(in) + nbytes / sizeof(double));
+        return 0;
+    }
     View w = lookup(name);
     if (!w.p || long(w.nbytes) != nbytes) return -1;
     std::memcpy(w.p, in, w.nbytes);
@@ -329,8 +333,32 @@ int desref_set_int(const char *name, int val)
     else if (n == "has_thermal_diffusion") p.control.has_thermal_diffusion = val;
     else if (n == "surface_process_option") p.control.surface_process_option = val;
     else if (n == "is_quasi_static") p.control.is_quasi_static = val;
+    else if (n == "has_moving_mesh") p.control.has_moving_mesh = val;
+    else if (n == "ref_pressure_option") p.control.ref_pressure_option = val;
+    else if (n == "PT_jump") p.control.PT_jump = val;
+    else if (n == "has_winkler_foundation") p.bc.has_winkler_foundation = val;
+    else if (n == "has_water_loading") p.bc.has_water_loading = val;
+    else if (n == "has_elastic_foundation") p.bc.has_elastic_foundation = val;
     else if (n == "steps") g_var->steps = val;
     else return -1;
+    return 0;
+}
+
+// apply_vbcs reads the x/y/z face types and values from Param.bc (bc.cxx:313-330) and the
+// slant ones from Variables (vbc_types / vbc_values, filled once by init_var,
+// dynearthsol.cxx:62-84).  After a test has written var.vbc_types / var.vbc_values through
+// desref_set, this carries entries 0..5 back into Param.bc so both views agree again.
+int desref_sync_vbc()
+{
+    BC &bc = g_param->bc; Variables &v = *g_var;
+    bc.vbc_x0 = v.vbc_types[0]; bc.vbc_x1 = v.vbc_types[1]; bc.vbc_y0 = v.vbc_types[2];
+    bc.vbc_y1 = v.vbc_types[3]; bc.vbc_z0 = v.vbc_types[4]; bc.vbc_z1 = v.vbc_types[5];
+    bc.vbc_n0 = v.vbc_types[6]; bc.vbc_n1 = v.vbc_types[7]; bc.vbc_n2 = v.vbc_types[8];
+    bc.vbc_n3 = v.vbc_types[9];
+    bc.vbc_val_x0 = v.vbc_values[0]; bc.vbc_val_x1 = v.vbc_values[1]; bc.vbc_val_y0 = v.vbc_values[2];
+    bc.vbc_val_y1 = v.vbc_values[3]; bc.vbc_val_z0 = v.vbc_values[4]; bc.vbc_val_z1 = v.vbc_values[5];
+    bc.vbc_val_n0 = v.vbc_values[6]; bc.vbc_val_n1 = v.vbc_values[7]; bc.vbc_val_n2 = v.vbc_values[8];
+    bc.vbc_val_n3 = v.vbc_values[9];
     return 0;
 }
 

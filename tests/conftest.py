@@ -31,25 +31,69 @@ def have_gpu():
     return cuda.cudaGetDeviceCount(ctypes.byref(n)) == 0 and n.value > 0
 
 
-def ref_dump(case, steps, sets=()):
+def cfg_variant(case, over):
+    """tests/cfg/<case>.cfg with `section.key = value` entries replaced (or added to their
+    section): the same file the reference would be given for that variant.  Returns its path."""
+    import hashlib
+    lines = open(os.path.join(HERE, "cfg", case + ".cfg")).read().splitlines()
+    todo = {k: str(v) for k, v in over.items()}
+    out, sec = [], None
+    pending = {}                                    # section -> lines to add under its header
+    for k, v in todo.items():
+        pending.setdefault(k.split(".", 1)[0], {})[k.split(".", 1)[1]] = v
+    for ln in lines:
+        st = ln.strip()
+        if st.startswith("[") and st.endswith("]"):
+            sec = st[1:-1]
+            out.append(ln)
+            continue
+        if sec in pending and "=" in st and not st.startswith("#"):
+            key = st.split("=", 1)[0].strip()
+            if key in pending[sec]:
+                out.append("%s = %s" % (key, pending[sec].pop(key)))
+                continue
+        out.append(ln)
+    final, sec = [], None
+    for ln in out:
+        final.append(ln)
+        st = ln.strip()
+        if st.startswith("[") and st.endswith("]") and st[1:-1] in pending:
+            for key, v in pending.pop(st[1:-1]).items():
+                final.append("%s = %s" % (key, v))
+    for sec, kv in pending.items():
+        if kv:
+            final.append("[%s]" % sec)
+            final += ["%s = %s" % (k, v) for k, v in kv.items()]
+    text = "\n".join(final) + "\n"
+    tag = hashlib.sha1(text.encode()).hexdigest()[:10]
+    path = os.path.join("/tmp", "descfg_%s_%s.cfg" % (case, tag))
+    with open(path, "w") as f:
+        f.write(text)
+    return path, tag
+
+
+def ref_dump(case, steps, sets=(), over=None):
     """Reference inputs/outputs for tests/cfg/<case>.cfg: generated LIVE from the unmodified
     reference when oracle/_ref/libdesref.so is present (one subprocess per dump: the
-    reference keeps process-wide state), else the committed golden fixture."""
-    key = (case, tuple(steps), tuple(sets))
+    reference keeps process-wide state), else the committed golden fixture.
+    over: {"section.key": value} cfg entries replaced before the reference reads the file;
+    sets: (name, int) switches flipped after init() (refdump.py --set)."""
+    key = (case, tuple(steps), tuple(sets), tuple(sorted((over or {}).items())))
     if key in _cache:
         return _cache[key]
     golden = os.path.join(HERE, "golden", case + ".npz")
     if os.path.exists(REFLIB):
-        out = os.path.join("/tmp", "desref_%s_%s_%s.npz" % (
-            case, "-".join(map(str, steps)), "-".join("%s%d" % s for s in sets)))
-        cmd = [sys.executable, os.path.join(HERE, "refdump.py"), os.path.join(HERE, "cfg", case + ".cfg"),
+        cfg, tag = (os.path.join(HERE, "cfg", case + ".cfg"), "") if not over else cfg_variant(case, over)
+        out = os.path.join("/tmp", "desref_%s%s_%s_%s.npz" % (
+            case, tag, "-".join(map(str, steps)), "-".join("%s%d" % s for s in sets)))
+        cmd = [sys.executable, os.path.join(HERE, "refdump.py"), cfg,
                out, "--steps", ",".join(map(str, steps))]
         for s in sets:
             cmd += ["--set", "%s=%d" % s]
         subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE,
                        env=dict(os.environ, OMP_NUM_THREADS="4"))
         d = dict(np.load(out))
-    elif os.path.exists(golden) and not sets:
+    elif os.path.exists(golden) and not sets and not over:
         d = dict(np.load(golden))
         missing = [k for k in steps if ("s%d_coord" % k) not in d]
         if missing:
@@ -58,3 +102,19 @@ def ref_dump(case, steps, sets=()):
         pytest.skip("no reference for case %s (libdesref.so absent, no golden fixture)" % case)
     _cache[key] = d
     return d
+
+
+def ref_branches(suite, case="box-ep"):
+    """Branch-level reference vectors (tests/refbranches.py), generated live from the unmodified
+    reference in a subprocess; skipped where libdesref.so is absent."""
+    key = ("branches", suite, case)
+    if key in _cache:
+        return _cache[key]
+    if not os.path.exists(REFLIB):
+        pytest.skip("oracle/_ref/libdesref.so absent: no reference to generate the %s vectors" % suite)
+    out = os.path.join("/tmp", "desref_branches_%s_%s.npz" % (suite, case))
+    subprocess.run([sys.executable, os.path.join(HERE, "refbranches.py"), suite,
+                    os.path.join(HERE, "cfg", case + ".cfg"), out], check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, env=dict(os.environ, OMP_NUM_THREADS="4"))
+    _cache[key] = dict(np.load(out))
+    return _cache[key]

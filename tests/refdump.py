@@ -130,6 +130,8 @@ def dump(cfg, out_path, steps=(1,), sets=(), by_function=True):
                     continue
                 if fn == "rotate_stress" and not (r.int("rheol_type") & 1):
                     continue
+                if fn == "update_mesh" and not r.int("has_moving_mesh"):
+                    continue
                 r.call(fn)
                 for a in writes:
                     out["f_%s_%s" % (fn, a)] = r.get(a)

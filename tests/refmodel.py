@@ -42,10 +42,10 @@ def mesh_from_dump(d):
     return m
 
 
-def model_from_dump(d, prefix="s0_", device=0, **override):
+def model_from_dump(d, prefix="s0_", device=0, mesh=None, **override):
     """Create the device model and upload mesh + the state snapshot `prefix`."""
     g = core.DesGpu(param_from_dump(d, **override), device)
-    g.upload_mesh(mesh_from_dump(d))
+    g.upload_mesh(mesh if mesh is not None else mesh_from_dump(d))
     g.upload_elemmarkers(d["elemmarkers"])
     g.set_compensation_pressure(float(d["p_compensation_pressure"]))
     g.upload_state(**{k: d[prefix + k] for k in UPLOAD})

@@ -1,0 +1,193 @@
+"""GPU parity for the device branches the named configs never reach ("parity
+holes"): every case runs the UNMODIFIED reference on a variant of tests/cfg/box-ep.cfg -- the
+cfg entries are replaced before the reference reads the file, so init() is consistent with
+them -- or drives one reference function on hand-made inputs (tests/refbranches.py), and
+compares the CUDA path, called through the C-ABI, with what the reference wrote.
+Tolerance: 1e-10 relative after one step (north star), 1e-9 after twenty, per field
+(max|a-b|/max|b|, the compare.py measure)."""
+import numpy as np
+import pytest
+
+import refmodel
+from conftest import ref_dump, ref_branches
+from test_parity_gpu import FIELDS, compare
+
+pytestmark = pytest.mark.gpu
+
+TWO_MAT = {"mat.num_materials": 2, "mat.rho0": "[2700, 3200]", "ic.mattype_option": 1,
+           "ic.mattype_layer_depths": "[0.45]", "mat.cohesion0": "[4.4e7, 3e7]",
+           "mat.bulk_modulus": "[50e9, 70e9]", "mat.friction_angle0": "[30, 20]",
+           "mat.friction_angle1": "[30, 10]", "mat.alpha": "[3e-5, 2e-5]",
+           "mat.heat_capacity": "[1000, 1200]", "mat.therm_cond": "[3.3, 2.5]"}
+LITHO = dict(TWO_MAT, **{"bc.vbc_x0": 0, "bc.vbc_x1": 2, "bc.vbc_y0": 4, "bc.vbc_val_y0": "1e-10",
+                         "bc.vbc_y1": 0})
+
+# name -> (cfg overrides, what the variant reaches)
+VARIANTS = {
+    # apply_stress_bcs (bc.cxx:661-827)
+    "water-loading": ({"bc.has_water_loading": "yes", "control.surf_base_level": "800"},
+                      "z1 facets under sea level: hydrostatic load (bc.cxx:748-755)"),
+    "elastic-foundation": ({"bc.has_elastic_foundation": "yes", "bc.elastic_foundation_constant": "1e7"},
+                           "restoring force on the bottom nodes (bc.cxx:817-823)"),
+    "elastic-foundation-no-gravity": ({"control.gravity": "0", "bc.has_elastic_foundation": "yes",
+                                       "bc.elastic_foundation_constant": "1e7"},
+                                      "gravity == 0: apply_stress_bcs returns first (bc.cxx:667), no foundation force"),
+    "lithostatic-walls-refp0": (dict(LITHO, **{"control.ref_pressure_option": 0}),
+                                "sidewall types 0/2/4: rho0 g depth support (matprops.cxx:153-174), EP with 2 materials"),
+    "lithostatic-walls-prem": (dict(LITHO, **{"control.ref_pressure_option": 1}), "PREM table (matprops.cxx:12-100)"),
+    "lithostatic-walls-prem-modified": (dict(LITHO, **{"control.ref_pressure_option": 2}),
+                                        "modified PREM (continental crust entries)"),
+    # apply_vbcs (bc.cxx:396-651): lateral types 2 3 4 5 7, z0 types 1..3, z1 types 1..3
+    "vbc-3-5-7-2-z1-z2": ({"bc.vbc_x0": 3, "bc.vbc_x1": 5, "bc.vbc_val_x1": "2e-10", "bc.vbc_y0": 7,
+                           "bc.vbc_val_y0": "-1e-10", "bc.vbc_y1": 2, "bc.has_winkler_foundation": "no",
+                           "bc.vbc_z0": 1, "bc.vbc_val_z0": "1e-11", "bc.vbc_z1": 2}, ""),
+    "vbc-5-7-3-4-z3-z1": ({"bc.vbc_x0": 5, "bc.vbc_val_x0": "3e-10", "bc.vbc_x1": 7, "bc.vbc_y0": 3,
+                           "bc.vbc_val_y0": "1e-10", "bc.vbc_y1": 4, "bc.vbc_val_y1": "2e-10",
+                           "bc.has_winkler_foundation": "no", "bc.vbc_z0": 3, "bc.vbc_val_z0": "-1e-11",
+                           "bc.vbc_z1": 1, "bc.vbc_val_z1": "1e-11"}, ""),
+    "vbc-z2-z3-loading-period": ({"bc.has_winkler_foundation": "no", "bc.vbc_z0": 2, "bc.vbc_z1": 3,
+                                  "bc.vbc_val_z1": "-2e-11", "bc.vbc_val_z1_loading_period": "5e8"},
+                                 "z1 bc switched off after ~8.7 steps (bc.cxx:346)"),
+    # control switches
+    "no-thermal-diffusion": ({"control.has_thermal_diffusion": "no"}, "tmass = 0 quirk (geometry.cxx:1836)"),
+    "not-quasi-static": ({"control.is_quasi_static": "no"}, "true density in compute_mass, elastic dt"),
+    "fixed-mesh": ({"control.has_moving_mesh": "no"}, "no update_mesh: volume/mass never recomputed"),
+}
+
+
+@pytest.mark.parametrize("name", sorted(VARIANTS))
+def test_cfg_variant(name):
+    over = VARIANTS[name][0]
+    d = ref_dump("box-ep", [1, 20], over=over)
+    g = refmodel.model_from_dump(d)
+    dt = float(d["s0_dt"])
+    g.step(dt, dt, 1)
+    compare(g.download_state(*FIELDS), d, "s1_", FIELDS)
+    dt2, time, steps = g.run(19, dt, dt, 1)
+    assert abs(dt2 - float(d["s20_dt"])) <= 1e-12 * abs(dt2), (dt2, float(d["s20_dt"]))
+    compare(g.download_state(*FIELDS), d, "s20_", FIELDS, tol=1e-9)
+    g.close()
+
+
+def test_variants_reach_their_branch():
+    """The variants are not no-ops: each moves the reference's result away from the base run."""
+    base = ref_dump("box-ep", [1, 20])
+    for name in ("water-loading", "elastic-foundation", "elastic-foundation-no-gravity",
+                 "lithostatic-walls-refp0", "vbc-3-5-7-2-z1-z2", "not-quasi-static", "fixed-mesh"):
+        d = ref_dump("box-ep", [1, 20], over=VARIANTS[name][0])
+        assert not np.array_equal(d["s20_force"], base["s20_force"]), name
+    a = ref_dump("box-ep", [1, 20], over=VARIANTS["lithostatic-walls-refp0"][0])
+    for other in ("lithostatic-walls-prem", "lithostatic-walls-prem-modified"):
+        b = ref_dump("box-ep", [1, 20], over=VARIANTS[other][0])
+        assert int(b["p_ref_pressure_option"]) in (1, 2)
+        assert not np.array_equal(a["s1_force"], b["s1_force"]), other
+    d = ref_dump("box-ep", [1, 20], over=VARIANTS["no-thermal-diffusion"][0])
+    assert np.all(d["s1_tmass"] == 0)
+
+
+YIELDING = {
+    # Mohr-Coulomb with two materials (mixed elements at the layer interface: the harmonic /
+    # arithmetic means of matprops.cxx:115-150 with counts > 1 material; material 1 weakens
+    # its friction angle 20 -> 10 degrees)
+    "two-materials": TWO_MAT,
+    # friction and dilation angles that weaken with plastic strain: sin/tan of an angle that is
+    # none of the configured ones, i.e. CUDA's libm instead of the host memo (matprops.cxx:589-606)
+    "weakening-angles": {"mat.pls1": "[1.0]", "mat.friction_angle1": "[15]", "mat.dilation_angle0": "[6]",
+                         "mat.dilation_angle1": "[1]"},
+}
+
+
+@pytest.mark.parametrize("name", sorted(YIELDING))
+def test_yielding_variant(name):
+    """From the reference's state at step 250 (hundreds of elements on the yield surface)."""
+    d = ref_dump("box-ep", [1, 20, 250, 251, 270], over=YIELDING[name])
+    nyield = int((d["s251_delta_plstrain"] > 0).sum())
+    assert nyield > 100, nyield
+    if name == "weakening-angles":
+        pls = d["s250_plstrain"]
+        assert ((pls > 0) & (pls < 1.0) & (d["s251_delta_plstrain"] > 0)).sum() > 50    # mid-ramp and yielding
+    else:
+        em = d["elemmarkers"].reshape(-1, 2)
+        assert ((em > 0).sum(axis=1) > 1).sum() > 100                                   # mixed elements exist
+    # from the start
+    g = refmodel.model_from_dump(d)
+    dt0 = float(d["s0_dt"])
+    g.step(dt0, dt0, 1)
+    compare(g.download_state(*FIELDS), d, "s1_", FIELDS)
+    g.run(19, dt0, dt0, 1)
+    compare(g.download_state(*FIELDS), d, "s20_", FIELDS, tol=1e-9)
+    g.close()
+    # from the yielding state
+    g = refmodel.model_from_dump(d, prefix="s250_")
+    dt, time = float(d["s250_dt"]), float(d["s250_time"])
+    g.step(dt, time + dt, 251)
+    compare(g.download_state(*FIELDS), d, "s251_", FIELDS)
+    g.run(19, dt, time + dt, 251)
+    compare(g.download_state(*FIELDS), d, "s270_", FIELDS, tol=1e-9)
+    g.close()
+
+
+def test_apply_vbcs_every_branch():
+    """apply_vbcs (bc.cxx:396-651) on synthetic boundary flags: lateral types 0..7 on every face,
+    all (z0, z1) type pairs with a running and an expired loading period, and the slant block
+    (types 1/3/11/13; ordinary nodes, intersections with type-0 and type-1 faces, the edge
+    projection, missing edge slots).  Assignments, multiply-adds and one correctly rounded
+    sqrt/divide: required to be BIT-EXACT."""
+    d = ref_branches("vbc")
+    mesh = refmodel.mesh_from_dump(d)
+    mesh["bcflag"] = d["vbc_bcflag"]
+    mesh["bnormals"] = d["vbc_bnormals"]
+    mesh["edge_slot"] = d["vbc_edge_slot"]
+    mesh["edge_vec"] = d["vbc_edge_vec"]
+    touched = 0
+    for i in range(int(d["vbc_n"])):
+        g = refmodel.model_from_dump(d, mesh=mesh, vbc_types=[int(x) for x in d["vbc%d_types" % i]],
+                                     vbc_values=[float(x) for x in d["vbc%d_values" % i]],
+                                     vbc_val_lateral=[float(x) for x in d["vbc%d_lateral" % i]],
+                                     vbc_val_z1_loading_period=float(d["vbc%d_period" % i]),
+                                     has_winkler_foundation=0, has_water_loading=0)
+        g.upload_state(vel=d["vbc%d_in" % i])
+        g.call("apply_vbcs", float(d["vbc%d_time" % i]))
+        got = g.download_state("vel")["vel"]
+        want = d["vbc%d_out" % i]
+        assert np.array_equal(got, want), (i, d["vbc%d_types" % i], np.abs(got - want).max())
+        touched += int((want != d["vbc%d_in" % i]).sum())
+        g.close()
+    assert touched > 1000
+
+
+def test_update_stress_ql_fallback():
+    """Stress states with degenerate principal values (diagonal tensors, two equal eigenvalues,
+    block-diagonal, near-isotropic tension): the reference's dsyevh3 leaves the Cardano /
+    cross-product path for the QL solver (3x3-C/dsyevh3.c:102,117; dsyevq3.c:49-135) on every
+    one of them (counted with a --wrap of dsyevq3 when the suite was written: 2400 of 2400),
+    and ~1600 of them yield, so the return mapping uses the QL eigenvectors."""
+    d = ref_branches("ql")
+    g = refmodel.model_from_dump(d)
+    up = {k: d["ql_in_" + k] for k in ("stress", "strain", "strain_rate", "plstrain", "edvoldt",
+                                       "volume", "volume_old", "temperature")}
+    g.upload_state(**up)
+    g.call("update_stress", float(d["s0_dt"]))
+    names = ["stress", "strain", "strain_rate", "plstrain", "delta_plstrain", "dpressure"]
+    got = g.download_state(*names)
+    kinds = d["ql_kinds"]
+    yl = d["ql_out_delta_plstrain"] > 0
+    assert (yl & (kinds <= 4)).sum() > 1000
+    assert np.array_equal(got["delta_plstrain"] > 0, yl)            # same yield decisions
+    compare(got, d, "ql_out_", names)
+    g.close()
+
+
+def test_residual_force():
+    """calculate_residual_force (fields.cxx:700-722) after update_force, three steps in: the
+    force of the LAST support element of each node (fields.cxx:673), squared and averaged.
+    The reference's sum is an OpenMP reduction, ours warp shuffles + atomics: 1e-12."""
+    d = ref_branches("residual")
+    g = refmodel.model_from_dump(d, prefix="res_")
+    g.call("update_force")
+    got = g.download_state("force")["force"]
+    assert refmodel.rel_err(got, d["res_force"]) < 1e-10
+    l2 = g.residual_force()
+    want = float(d["res_l2"])
+    assert want > 0 and abs(l2 - want) <= 1e-12 * want, (l2, want)
+    g.close()

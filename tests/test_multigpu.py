@@ -278,6 +278,10 @@ def test_parts_on_one_gpu_bit_identical(nparts, overlap):
             merged = _owned_merge(parts, outs, N, E)
             bad = [k for k in FIELDS if not np.array_equal(merged[k], refs[s][k])]
             assert not bad, "step %d: fields differ from the single-GPU run: %s" % (s, bad)
+            # ghost copies too: a rank-local download (or a host surface-marker pass on a
+            # partition) must see the owner's accumulated surface change
+            for p, o in zip(parts, outs):
+                assert np.array_equal(o["dhacc"], refs[s]["dhacc"][p["node_gid"]]), "ghost dhacc drifts"
     for g in gs:
         g.close()
 
