@@ -72,28 +72,31 @@ def cfg_variant(case, over):
     return path, tag
 
 
-def ref_dump(case, steps, sets=(), over=None):
+def ref_dump(case, steps, sets=(), over=None, perturb_at=None):
     """Reference inputs/outputs for tests/cfg/<case>.cfg: generated LIVE from the unmodified
     reference when oracle/_ref/libdesref.so is present (one subprocess per dump: the
     reference keeps process-wide state), else the committed golden fixture.
     over: {"section.key": value} cfg entries replaced before the reference reads the file;
     sets: (name, int) switches flipped after init() (refdump.py --set)."""
-    key = (case, tuple(steps), tuple(sets), tuple(sorted((over or {}).items())))
+    key = (case, tuple(steps), tuple(sets), tuple(sorted((over or {}).items())), perturb_at)
     if key in _cache:
         return _cache[key]
     golden = os.path.join(HERE, "golden", case + ".npz")
     if os.path.exists(REFLIB):
         cfg, tag = (os.path.join(HERE, "cfg", case + ".cfg"), "") if not over else cfg_variant(case, over)
-        out = os.path.join("/tmp", "desref_%s%s_%s_%s.npz" % (
-            case, tag, "-".join(map(str, steps)), "-".join("%s%d" % s for s in sets)))
+        out = os.path.join("/tmp", "desref_%s%s_%s_%s%s.npz" % (
+            case, tag, "-".join(map(str, steps)), "-".join("%s%d" % s for s in sets),
+            "" if perturb_at is None else "_ulp%d" % perturb_at))
         cmd = [sys.executable, os.path.join(HERE, "refdump.py"), cfg,
                out, "--steps", ",".join(map(str, steps))]
         for s in sets:
             cmd += ["--set", "%s=%d" % s]
+        if perturb_at is not None:
+            cmd += ["--perturb-at", str(perturb_at)]
         subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE,
                        env=dict(os.environ, OMP_NUM_THREADS="4"))
         d = dict(np.load(out))
-    elif os.path.exists(golden) and not sets and not over:
+    elif os.path.exists(golden) and not sets and not over and perturb_at is None:
         d = dict(np.load(golden))
         missing = [k for k in steps if ("s%d_coord" % k) not in d]
         if missing:
@@ -118,3 +121,22 @@ def ref_branches(suite, case="box-ep"):
                    stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, env=dict(os.environ, OMP_NUM_THREADS="4"))
     _cache[key] = dict(np.load(out))
     return _cache[key]
+
+
+def ref_conditioning(case, steps, over=None, at=0):
+    """{step: {field: relative change}} of the reference's OWN snapshots when every stress entry
+    of its state at step `at` is moved by one ulp (tests/refdump.py --perturb-at).  Where plastic
+    return mapping is active this is far above 1e-10: the Cardano eigenvalues lose ~1e5 of
+    precision to cancellation (3x3-C/dsyevc3.c) and the return direction follows them, so a
+    last-bit difference in libm (atan2/cos/sin: CUDA's vs glibc's) or in operation order
+    (the reference's 3x3-C is built -O3 -ffast-math) moves the result by the same amount."""
+    import refmodel
+    a = ref_dump(case, steps, over=over)
+    b = ref_dump(case, steps, over=over, perturb_at=at)
+    out = {}
+    for k in steps:
+        if k <= at:
+            continue
+        out[k] = {f[len("s%d_" % k):]: refmodel.rel_err(b[f], a[f]) for f in a if f.startswith("s%d_" % k)
+                  and a[f].ndim == 1 and a[f].size > 1}
+    return out

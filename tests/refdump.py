@@ -100,7 +100,7 @@ def snapshot(r, out, prefix):
     out[prefix + "max_surf_vel"] = np.float64(r.scalar("max_surf_vel"))
 
 
-def dump(cfg, out_path, steps=(1,), sets=(), by_function=True):
+def dump(cfg, out_path, steps=(1,), sets=(), by_function=True, perturb_at=None):
     with tempfile.TemporaryDirectory() as wd:
         r = Ref(cfg, workdir=wd)
         for name, val in sets:
@@ -117,6 +117,15 @@ def dump(cfg, out_path, steps=(1,), sets=(), by_function=True):
             out["p_" + s] = r.matvec(s)
         snapshot(r, out, "s0_")
         done = 0
+        if perturb_at is not None:
+            # conditioning probe: the same run with every stress entry moved by ONE ulp at step
+            # `perturb_at`; the distance between its later snapshots and the unperturbed run's is
+            # what the reference itself does with a last-bit difference in its input
+            by_function = False
+            if perturb_at > 0:
+                r.step(perturb_at)
+                done = perturb_at
+            r.set("stress", np.nextafter(r.get("stress"), np.inf))
         if by_function:
             # step 1, call by call (same order as desref_step / the driver)
             r.set_int("steps", 1)
@@ -157,6 +166,8 @@ if __name__ == "__main__":
     ap.add_argument("out")
     ap.add_argument("--steps", default="1")
     ap.add_argument("--set", action="append", default=[])
+    ap.add_argument("--perturb-at", type=int, default=None,
+                    help="move the stress by one ulp at this step (0 = initial state) before going on")
     a = ap.parse_args()
     dump(a.cfg, a.out, steps=[int(s) for s in a.steps.split(",")],
-         sets=[(s.split("=")[0], int(s.split("=")[1])) for s in a.set])
+         sets=[(s.split("=")[0], int(s.split("=")[1])) for s in a.set], perturb_at=a.perturb_at)

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 import refmodel
-from conftest import ref_dump, ref_branches
+from conftest import ref_dump, ref_branches, ref_conditioning
 from test_parity_gpu import FIELDS, compare
 
 pytestmark = pytest.mark.gpu
@@ -59,13 +59,19 @@ VARIANTS = {
 def test_cfg_variant(name):
     over = VARIANTS[name][0]
     d = ref_dump("box-ep", [1, 20], over=over)
+    # variants in which elements yield within the 20 steps (the top pushed down, ...): the
+    # return mapping makes the reference itself ill-conditioned -- measure by how much
+    floor = None
+    if (d["s20_plstrain"] != d["s0_plstrain"]).any():
+        floor = ref_conditioning("box-ep", [1, 20], over=over)
     g = refmodel.model_from_dump(d)
     dt = float(d["s0_dt"])
     g.step(dt, dt, 1)
-    compare(g.download_state(*FIELDS), d, "s1_", FIELDS)
+    compare(g.download_state(*FIELDS), d, "s1_", FIELDS, floor=floor and floor[1])
     dt2, time, steps = g.run(19, dt, dt, 1)
-    assert abs(dt2 - float(d["s20_dt"])) <= 1e-12 * abs(dt2), (dt2, float(d["s20_dt"]))
-    compare(g.download_state(*FIELDS), d, "s20_", FIELDS, tol=1e-9)
+    compare(g.download_state(*FIELDS), d, "s20_", FIELDS, tol=1e-9, floor=floor and floor[20])
+    dtol = 1e-12 if floor is None else max(1e-12, 8 * floor[20]["coord"])
+    assert abs(dt2 - float(d["s20_dt"])) <= dtol * abs(dt2), (dt2, float(d["s20_dt"]))
     g.close()
 
 
@@ -117,14 +123,36 @@ def test_yielding_variant(name):
     g.run(19, dt0, dt0, 1)
     compare(g.download_state(*FIELDS), d, "s20_", FIELDS, tol=1e-9)
     g.close()
-    # from the yielding state
+    # from the yielding state.  Elements in plastic return are where the reference is itself
+    # ill-conditioned (conftest.ref_conditioning): everything that does not yield must meet
+    # 1e-10 outright, the principal stresses of the yielding ones too, and whole fields may
+    # differ by no more than 8x what ONE ulp in the reference's own input does to it.
+    floor = ref_conditioning("box-ep", [250, 251, 270], over=YIELDING[name], at=250)
     g = refmodel.model_from_dump(d, prefix="s250_")
     dt, time = float(d["s250_dt"]), float(d["s250_time"])
     g.step(dt, time + dt, 251)
-    compare(g.download_state(*FIELDS), d, "s251_", FIELDS)
+    got = g.download_state(*FIELDS)
+    compare(got, d, "s251_", FIELDS, floor=floor[251])
+    E = int(d["p_nelem"])
+    a, b = got["stress"].reshape(6, E), d["s251_stress"].reshape(6, E)
+    yl = d["s251_delta_plstrain"] > 0
+    scale = np.abs(b).max()
+    assert np.abs(a - b)[:, ~yl].max() / scale < 1e-10
+    assert np.abs(principal(a) - principal(b)).max() / scale < 1e-10
     g.run(19, dt, time + dt, 251)
-    compare(g.download_state(*FIELDS), d, "s270_", FIELDS, tol=1e-9)
+    compare(g.download_state(*FIELDS), d, "s270_", FIELDS, tol=1e-9, floor=floor[270])
     g.close()
+
+
+def principal(s6):
+    """Principal values of [6, E] symmetric tensors (numpy, for invariants only)."""
+    n = s6.shape[1]
+    m = np.zeros((n, 3, 3))
+    m[:, 0, 0], m[:, 1, 1], m[:, 2, 2] = s6[0], s6[1], s6[2]
+    m[:, 0, 1] = m[:, 1, 0] = s6[3]
+    m[:, 0, 2] = m[:, 2, 0] = s6[4]
+    m[:, 1, 2] = m[:, 2, 1] = s6[5]
+    return np.linalg.eigvalsh(m)
 
 
 def test_apply_vbcs_every_branch():
@@ -174,7 +202,21 @@ def test_update_stress_ql_fallback():
     yl = d["ql_out_delta_plstrain"] > 0
     assert (yl & (kinds <= 4)).sum() > 1000
     assert np.array_equal(got["delta_plstrain"] > 0, yl)            # same yield decisions
-    compare(got, d, "ql_out_", names)
+    E = kinds.size
+    a, b = got["stress"].reshape(6, E), d["ql_out_stress"].reshape(6, E)
+    scale = np.abs(b).max()
+    # axis-aligned degenerate states (exactly diagonal / block-diagonal / isotropic): the QL
+    # iteration is deterministic arithmetic on exact zeros -- measured bit-exact, required 1e-12
+    well = kinds != 2
+    assert np.abs(a - b)[:, well].max() / scale < 1e-12
+    # kind 2: an EXACTLY repeated principal value in a rotated frame.  Its eigenvectors are any
+    # basis of a plane -- rounding noise picks one -- and the return mapping then separates the
+    # pair (rheology.cxx:402-404), so the tensor components inherit that arbitrary choice in the
+    # reference too.  The invariants do not: principal stresses and the plastic strain must agree.
+    assert np.abs(principal(a) - principal(b)).max() / scale < 1e-10
+    assert np.abs(a - b).max() / scale < 1e-5
+    for k in ("strain", "strain_rate", "plstrain", "delta_plstrain", "dpressure"):
+        assert refmodel.rel_err(got[k], d["ql_out_" + k]) < 1e-10, k
     g.close()
 
 
