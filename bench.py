@@ -147,8 +147,8 @@ def pin(a):
     return t.numpy(), t
 
 
-EVOLVING = ["coord", "vel", "temperature", "stress", "strain", "strain_rate", "plstrain",
-            "volume", "volume_old"]
+EVOLVING = ["coord", "vel", "temperature", "stress", "strain", "plstrain",
+            "volume", "volume_old"]      # SURVEY.md section 8b "evolving state" (strain_rate is derived: E-B writes it)
 OUTPUT = ["coord", "vel", "temperature", "stress", "strain", "strain_rate", "plstrain",
           "delta_plstrain", "force", "volume"]                        # what Output::_write reads
 
@@ -166,30 +166,43 @@ def read_traffic():
     return None
 
 
-def reference_cpu(steps, warmup, sample="100k", target_seconds=None):
-    """The unmodified reference on the host cores, same physics, on a box it can initialise.
-    Returns (element_steps_per_s, cores, description).  Runs in a subprocess (the reference
-    keeps process-wide state)."""
+def host_ram_gb():
+    try:
+        import psutil
+        return psutil.virtual_memory().total / 1e9
+    except Exception:
+        return 0.0
+
+
+def reference_cpu(steps, warmup, sample="1M", target_seconds=None):
+    """The unmodified reference on the host cores, same physics, same box generator.
+    Returns a dict (rate, cores, nelem, steps, seconds, init_seconds, desc).  Runs in a
+    subprocess (the reference keeps process-wide state).  The hot functions that are timed are
+    the reference's own object code; only init()'s O(nseg*nelem) boundary-facet search is
+    replaced by the support-based one of oracle/ref_harness.cxx (same arrays, tested), without
+    which the reference cannot initialise a box of more than ~1 M tets."""
     lib = os.path.join(ROOT, "oracle", "_ref", "libdesref.so")
     if not os.path.exists(lib):
-        return None, 0, "oracle/_ref/libdesref.so absent"
+        return {"rate": None, "cores": 0, "desc": "oracle/_ref/libdesref.so absent"}
     xl, yl, zl, res = SIZES[sample]
     cfg = CFG_TEMPLATE % dict(xl=xl, yl=yl, zl=zl, res=res)
     import tempfile
     wd = tempfile.mkdtemp(prefix="desref_")
     open(os.path.join(wd, "sample.cfg"), "w").write(cfg)
     code = (
-        "import sys, json; sys.path.insert(0, %r)\n"
+        "import sys, json, time; sys.path.insert(0, %r)\n"
         "from refharness import Ref\n"
-        "r = Ref(%r, workdir=%r)\n"
+        "t0 = time.time()\n"
+        "r = Ref(%r, workdir=%r, fast_init=True)\n"
+        "ti = time.time() - t0\n"
         "r.step(%d)\n"
         "n = %d\n"
         "t = r.step(n)\n"
         "target = %r\n"
-        "if target:\n"
+        "if target and t < target / 2:\n"
         "    n = max(n, min(20000, int(target / (t / n))))   # bounded sample: ~target seconds of CPU work\n"
         "    t = r.step(n)\n"
-        "print('RESULT', json.dumps({'t': t, 'n': n, 'nelem': r.int('nelem'), 'nnode': r.int('nnode')}))\n"
+        "print('RESULT', json.dumps({'t': t, 'n': n, 'ti': ti, 'nelem': r.int('nelem'), 'nnode': r.int('nnode')}))\n"
     ) % (os.path.join(ROOT, "tests"), os.path.join(wd, "sample.cfg"), wd, warmup, steps, target_seconds)
     cores = os.cpu_count() or 1
     env = dict(os.environ, OMP_NUM_THREADS=str(cores))
@@ -198,10 +211,18 @@ def reference_cpu(steps, warmup, sample="100k", target_seconds=None):
         if line.startswith("RESULT"):
             r = json.loads(line[7:])
             rate = r["nelem"] * r["n"] / r["t"]
-            return rate, cores, ("unmodified reference (g++ -O2 -fopenmp), %d-tet box, same physics, "
-                                 "%d steps (%.1f s) after %d warm-up, %d OpenMP threads"
-                                 % (r["nelem"], r["n"], r["t"], warmup, cores))
-    return None, cores, "reference run failed: " + out.stderr[-200:]
+            return {"rate": rate, "cores": cores, "nelem": r["nelem"], "nnode": r["nnode"], "steps": r["n"],
+                    "seconds": r["t"], "init_seconds": r["ti"],
+                    "desc": ("unmodified reference (g++ -O2 -fopenmp), %d-tet box (%s), same physics, "
+                             "%d steps in %.1f s after %d warm-up, %d OpenMP threads; init %.0f s"
+                             % (r["nelem"], sample, r["n"], r["t"], warmup, cores, r["ti"]))}
+    return {"rate": None, "cores": cores, "desc": "reference run failed: " + out.stderr[-300:]}
+
+
+def workload_name(size, cells, E, N):
+    return ("box %s (%dx%dx%d cells, %d tets, %d nodes): test-3d.cfg Mohr-Coulomb "
+            "elasto-plastic + thermal + mixed stress + surface diffusion, "
+            "compute_dt every 10 steps" % ((size,) + tuple(cells) + (E, N)))
 
 
 CFG_TEMPLATE = """[sim]
@@ -271,13 +292,18 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--size", default=None, help="box size key: " + ", ".join(SIZES))
     ap.add_argument("--order", default="reference", choices=["reference", "morton"])
-    ap.add_argument("--cpu-sample", default="100k")
+    ap.add_argument("--cpu-sample", default=None,
+                    help="box the CPU reference runs on (default: --impl reference: the named workload when "
+                         "the host has the RAM for it, else 6M; cpu_baseline leg: 1M)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--strong", action="store_true",
-                    help="N > 1: keep the --size mesh as it is and split it over the ranks (strong scaling), "
-                         "e.g. --size 200M --strong on 2/4/8 GPUs; default is weak scaling (size per GPU)")
+                    help="N > 1: keep the --size mesh as it is and split it over the ranks (strong scaling). "
+                         "This is the default for N > 1: the north star's 200M-tet box split over the N GPUs")
+    ap.add_argument("--weak", action="store_true",
+                    help="N > 1: weak scaling instead -- the box refined so that every GPU holds the --size mesh "
+                         "(default 50M per GPU)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -291,22 +317,28 @@ def main():
         if rank != 0:
             return
         size = a.size or "50M"
-        cpu_steps = max(1, min(K, 20))
-        rate, cores, desc = reference_cpu(cpu_steps, min(W, 3), a.cpu_sample, target_seconds=15.0)
+        # the named workload itself when the host can hold it (the reference needs ~65 GB for the
+        # 51.4M-tet box: 4 markers per element, vector<vector<int>> marker counts), else the
+        # largest box that fits; --cpu-sample overrides
+        sample = a.cpu_sample
+        if sample is None:
+            sample = size if host_ram_gb() >= 160 else ("6M" if host_ram_gb() >= 24 else "1M")
+        res_ = reference_cpu(K, min(W, 3), sample)
+        rate, cores, desc = res_["rate"], res_["cores"], res_["desc"]
         xl, yl, zl, res = SIZES[size]
         from dynearthsol_b200 import boxmesh as bm
         nx, ny, nz = bm.grid_dims(xl, yl, zl, res)
-        nelem_workload = (nx - 1) * (ny - 1) * (nz - 1) * 5
-        # one step of the named workload at the measured rate (the reference cannot initialise a
-        # mesh of that size, so its rate is measured on the bounded sample and is size-independent
-        # to first order: SURVEY.md section 8d)
-        ms_step = (nelem_workload / rate * 1e3) if rate else None
+        E_named, N_named = (nx - 1) * (ny - 1) * (nz - 1) * 5, nx * ny * nz
+        same = rate is not None and res_["nelem"] == E_named
+        # ms_per_step is MEASURED: wall time of the K timed steps of the box that was run
+        ms_step = (res_["seconds"] / res_["steps"] * 1e3) if rate else None
         line = {"impl": "reference", "metric": metric, "value": rate, "unit": unit, "n_gpus": a.gpus,
-                "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
+                "steps": res_.get("steps", K), "warmup": min(W, 3), "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": "box %s: test-3d.cfg Mohr-Coulomb + thermal + NMD + surface diffusion" % size,
-                           "sample": desc,
-                           "ms_per_step": "extrapolated: %d tets of the named workload / the measured rate" % nelem_workload},
+                "config": {"workload": workload_name(size, (nx - 1, ny - 1, nz - 1), E_named, N_named),
+                           "sample": desc, "same_config": same,
+                           "sample_nelem": res_.get("nelem"), "host_ram_gb": round(host_ram_gb(), 1),
+                           "element_order": "reference", "parallelism": "%d OpenMP threads" % cores},
                 "cpu_baseline": {"value": rate, "unit": unit, "cores": cores, "kind": "reference", "sample": desc},
                 "e2e": {"value": rate, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         if rate is None:
@@ -398,16 +430,14 @@ def main():
     # ---- CPU baseline: the unmodified reference on the host cores -----------------------
     cpu = None
     if not a.no_cpu:
-        rate, cores, desc = reference_cpu(10, 2, a.cpu_sample, target_seconds=10.0)
-        cpu = {"value": rate, "unit": unit, "cores": cores, "kind": "reference", "sample": desc}
+        res_ = reference_cpu(10, 2, a.cpu_sample or "1M", target_seconds=12.0)
+        cpu = {"value": res_["rate"], "unit": unit, "cores": res_["cores"], "kind": "reference", "sample": res_["desc"]}
 
     sampler.join(timeout=2)
     line = {"metric": metric, "value": value, "unit": unit, "n_gpus": 1, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "box %s (%dx%dx%d cells, %d tets, %d nodes): test-3d.cfg Mohr-Coulomb "
-                                   "elasto-plastic + thermal + mixed stress + surface diffusion, "
-                                   "compute_dt every 10 steps" % ((size,) + prob["cells"] + (E, N)),
+            "config": {"workload": workload_name(size, prob["cells"], E, N),
                        "element_order": a.order, "schedule": os.environ.get("DES_SCHEDULE", "2"), "l2": "working set (%.1f GB) >> 126 MB L2" % (E * 1160 / 1e9),
                        "parallelism": "1 GPU"},
             "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,

@@ -1,6 +1,8 @@
 // See des_bridge.hpp.  Compiled with the reference's flags (-DTHREED -DSOA) against its headers.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <iostream>
 #include <string>
 #include <vector>
@@ -161,8 +163,23 @@ int des_bridge_upload(DesBridge *b, const Param &param, const Variables &var)
     m.support_surf_arr = var.surfinfo.support_surf.arr_data.data();
     m.elem_and_nodes = var.surfinfo.elem_and_nodes->data();
     m.connectivity_surface = var.connectivity_surface->data();
+    m.coord = var.coord->data();        // a handle over several devices bisects the element centroids
     int rc = des_gpu_upload_mesh(b->h, &m);
     if (rc) return fail(b, rc, "upload_mesh");
+    {
+        int nparts = 1;
+        double ps = 0, us = 0;
+        std::vector<int> le(64), ln(64), gh(64);
+        des_gpu_partition_info(b->h, &nparts, &ps, &us, le.data(), ln.data(), gh.data());
+        if (nparts > 1) {
+            std::printf("  [B200] mesh partitioned over %d devices: partition %.3f s, upload %.3f s; elements per part",
+                        nparts, ps, us);
+            for (int r = 0; r < nparts; ++r) std::printf(" %d", le[r]);
+            std::printf(" (%d in the mesh), ghost nodes", var.nelem);
+            for (int r = 0; r < nparts; ++r) std::printf(" %d", gh[r]);
+            std::printf("\n");
+        }
+    }
     flatten_markers(b, param, var);
     if ((rc = des_gpu_upload_elemmarkers(b->h, b->flat_markers.data()))) return fail(b, rc, "upload_elemmarkers");
     des_gpu_set_compensation_pressure(b->h, var.compensation_pressure);
@@ -176,7 +193,18 @@ DesBridge *des_bridge_create(const Param &param, const Variables &var, int devic
 {
     DesBridge *b = new DesBridge;
     fill_param(b->p, param, var);
-    int rc = des_gpu_create(&b->p, device, &b->h);
+    // DES_BRIDGE_NDEV=n: one handle over n devices of the box (DES_BRIDGE_DEVICES=0,0,1: which ones;
+    // an index may repeat) -- partition, ghost exchange and gather/scatter happen inside the library
+    int ndev = 1;
+    std::vector<int> devs;
+    if (const char *s = std::getenv("DES_BRIDGE_NDEV")) ndev = std::max(1, std::atoi(s));
+    if (const char *s = std::getenv("DES_BRIDGE_DEVICES")) {
+        for (const char *q = s; *q; ) { devs.push_back(std::atoi(q)); while (*q && *q != ',') ++q; if (*q) ++q; }
+        ndev = int(devs.size());
+    }
+    int rc = (ndev > 1 || !devs.empty())
+        ? des_gpu_create_multi(&b->p, ndev, devs.empty() ? nullptr : devs.data(), &b->h)
+        : des_gpu_create(&b->p, device, &b->h);
     if (rc) {
         std::fprintf(stderr, "des_bridge: des_gpu_create failed (code %d): %s\n", rc,
                      b->h ? des_gpu_last_error(b->h) : "no CUDA device");

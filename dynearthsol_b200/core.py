@@ -79,7 +79,7 @@ class DesMesh(C.Structure):
         ("ntop_elems", C.c_int), ("top_elems", _IP),
         ("ntop", C.c_int), ("top_nodes", _IP), ("etop", C.c_int),
         ("support_surf_idx", _IP), ("support_surf_arr", _IP),
-        ("elem_and_nodes", _IP), ("connectivity_surface", _IP),
+        ("elem_and_nodes", _IP), ("connectivity_surface", _IP), ("coord", _DP),
     ]
 
 
@@ -116,7 +116,8 @@ class DesQuality(C.Structure):
 
 # every symbol include/des_gpu.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
-    "des_gpu_create", "des_gpu_destroy", "des_gpu_last_error", "des_gpu_upload_mesh",
+    "des_gpu_create", "des_gpu_create_multi", "des_gpu_partition_info",
+    "des_gpu_destroy", "des_gpu_last_error", "des_gpu_upload_mesh",
     "des_gpu_upload_state", "des_gpu_download_state", "des_gpu_upload_elemmarkers",
     "des_gpu_set_compensation_pressure", "des_gpu_step", "des_gpu_compute_dt",
     "des_dt_from_reductions", "des_gpu_sync",
@@ -151,6 +152,8 @@ def load_library():
     L = C.CDLL(LIB_PATH)
     H = C.c_void_p
     L.des_gpu_create.argtypes = [C.POINTER(DesParam), C.c_int, C.POINTER(H)]
+    L.des_gpu_create_multi.argtypes = [C.POINTER(DesParam), C.c_int, _IP, C.POINTER(H)]
+    L.des_gpu_partition_info.argtypes = [H, _IP, _DP, _DP, _IP, _IP, _IP]
     L.des_gpu_destroy.argtypes = [H]
     L.des_gpu_last_error.argtypes = [H]
     L.des_gpu_last_error.restype = C.c_char_p
@@ -369,11 +372,18 @@ class DesGpu:
     """One device-resident model.  Host arrays use the reference's SoA layout
     (Array2D a[d*n + i], array2d.hpp:410-425)."""
 
-    def __init__(self, param, device=0):
+    def __init__(self, param, device=0, devices=None):
+        """devices: a list of device indices -> one handle over several devices (or several parts
+        on one device when an index repeats): des_gpu_create_multi."""
         self.lib = load_library()
         self.param = param
         self.h = C.c_void_p()
-        rc = self.lib.des_gpu_create(C.byref(param), device, C.byref(self.h))
+        self.devices = list(devices) if devices is not None else None
+        if self.devices is not None:
+            arr = (C.c_int * len(self.devices))(*self.devices)
+            rc = self.lib.des_gpu_create_multi(C.byref(param), len(self.devices), arr, C.byref(self.h))
+        else:
+            rc = self.lib.des_gpu_create(C.byref(param), device, C.byref(self.h))
         if rc:
             msg = self.lib.des_gpu_last_error(self.h).decode() if self.h else "no handle"
             if self.h:
@@ -441,6 +451,7 @@ class DesGpu:
         dm.support_surf_arr = _ptr(arr("support_surf_arr", np.int32), C.c_int)
         dm.elem_and_nodes = _ptr(arr("elem_and_nodes", np.int32), C.c_int)
         dm.connectivity_surface = _ptr(arr("connectivity_surface", np.int32), C.c_int)
+        dm.coord = _ptr(arr("coord", np.float64), C.c_double)      # only a multi-device handle reads it
         self._ck(self.lib.des_gpu_upload_mesh(self.h, C.byref(dm)))
         self.nnode, self.nelem, self.etop = dm.nnode, dm.nelem, dm.etop
 
@@ -493,6 +504,14 @@ class DesGpu:
         if a.size != self.nelem * self.param.nmat:
             raise ValueError("elemmarkers: expected nelem*nmat ints")
         self._ck(self.lib.des_gpu_upload_elemmarkers(self.h, _ptr(a, C.c_int)))
+
+    def partition_info(self):
+        n = C.c_int(); ps = C.c_double(); us = C.c_double()
+        self._ck(self.lib.des_gpu_partition_info(self.h, C.byref(n), C.byref(ps), C.byref(us), None, None, None))
+        le = (C.c_int * n.value)(); ln = (C.c_int * n.value)(); gh = (C.c_int * n.value)()
+        self._ck(self.lib.des_gpu_partition_info(self.h, C.byref(n), C.byref(ps), C.byref(us), le, ln, gh))
+        return dict(nparts=n.value, partition_seconds=ps.value, upload_seconds=us.value,
+                    local_elems=list(le), local_nodes=list(ln), ghost_nodes=list(gh))
 
     def set_compensation_pressure(self, p):
         self._ck(self.lib.des_gpu_set_compensation_pressure(self.h, float(p)))

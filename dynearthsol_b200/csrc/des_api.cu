@@ -31,7 +31,11 @@ struct EvPair { cudaEvent_t a, b; int cls; };
 
 } // namespace
 
+struct DesMulti;
 struct DesGpu {
+    // a group handle (des_gpu_create_multi) owns one ordinary handle per part: des_multi.cuh
+    DesMulti *multi = nullptr;
+    std::vector<int> devices;
     int device = 0;
     cudaStream_t stream = nullptr;
     DesParam hp;
@@ -54,6 +58,8 @@ struct DesGpu {
     bool seg_tail_mass = false;         // volume/mass of the previous step pending for segment 0
     int n_interior = 0;                 // leading elements that touch no ghost node (des_gpu_set_interior)
     int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
+    // A/B switches of the three deferrals (all on by default; DES_DEFER=0 turns them off)
+    int defer_ddp = 1, defer_scale = 1, dt_rides = 1;
     // internal element order: DES_ELEM_ORDER=1 stores elements sorted by smallest node index.
     // Off by default: measured on B200 it cuts the lines a warp's gathers touch by 40 % but the
     // element kernels gain < 4 % and the node gathers lose 20-30 % (profiles/experiments/)
@@ -65,6 +71,11 @@ struct DesGpu {
     // staging
     void *stage = nullptr; size_t stage_bytes = 0;
     DtPartial *dt_partials = nullptr; int dt_blocks = 0;
+    size_t dt_cap = 0;                  // partials the buffer holds; slot [dt_cap] takes k_dt_final's result
+    // work of the step that ended which the next E-B applies first (resolve_pending otherwise):
+    bool nmd_pending = false;           // stress diagonal += ddp[e]       (E-C stored the scalar)
+    bool scale_pending = false;         // top elements: stress, strain, plstrain /= rdv (k_surf_correct_vol)
+    bool ea_prerun = false;             // des_gpu_compute_dt already ran the next step's E-A (with the dt reductions)
     QPartial *q_partials = nullptr; int *q_nodes = nullptr;     // des_gpu_mesh_quality
     // Output::average_fields accumulators (mesh-lifetime allocations, internal element order)
     double *avg_coord0 = nullptr;   // the element accumulators live in Dev (avg_stress, avg_strain0, avg_dpl)
@@ -191,6 +202,7 @@ void free_mesh(DesGpu *h)
     h->D.pf = h->pf_elems;
     h->have_mesh = h->have_state = false;
     h->tail_pending = false;
+    h->nmd_pending = h->scale_pending = h->ea_prerun = false;
     h->surf_ran = false;
 }
 
@@ -440,8 +452,22 @@ int average_now(DesGpu *h)
     return DES_OK;
 }
 
+// Applies what the fused schedule leaves for the next E-B to the stored fields, in the
+// reference's order: NMD_stress's diagonal correction (geometry.cxx:315-331), then
+// correct_surface_element's divisions (bc.cxx:1678-1685).
+int resolve_pending(DesGpu *h)
+{
+    if (h->nmd_pending) LAUNCH(KC_ELEM_C, k_apply_ddp, h->D.nelem, 256, h->D);
+    if (h->scale_pending) LAUNCH(KC_SURFACE, k_surf_apply_scale, h->D.ntop_elems, 128, h->D);
+    h->nmd_pending = h->scale_pending = false;
+    CK(cudaGetLastError());
+    return DES_OK;
+}
+
 int flush_tail(DesGpu *h)
 {
+    h->ea_prerun = false;       // whoever flushes may change what E-A read
+    { int rc = resolve_pending(h); if (rc) return rc; }
     if (!h->tail_pending) return average_now(h);
     const int mm = h->hp.has_moving_mesh;
     LAUNCH(KC_ELEM_A, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, h->dt_prev, tail_flags(h), 0);
@@ -469,8 +495,76 @@ int run_surface(DesGpu *h, double dt, bool with_volume_n)
 
 } // namespace
 
+// forward declarations the group layer calls back into
+extern "C" {
+int des_gpu_create(const DesParam *param, int device, DesGpu **out);
+int des_gpu_destroy(DesGpu *h);
+const char *des_gpu_last_error(const DesGpu *h);
+int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m);
+int des_gpu_upload_state(DesGpu *h, const DesState *s);
+int des_gpu_download_state(DesGpu *h, const DesState *s);
+int des_gpu_upload_elemmarkers(DesGpu *h, const int *elemmarkers);
+int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time);
+int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out);
+int des_gpu_mesh_quality(DesGpu *h, const DesQualityParam *qp, DesQuality *out);
+int des_gpu_download_averages(DesGpu *h, double *coord0, double *strain0, double *stress_avg, double *dpl_avg);
+int des_gpu_set_halo(DesGpu *h, int nsend, const int *send_nodes, int nrecv, const int *recv_nodes);
+int des_gpu_halo_pack(DesGpu *h, int phase);
+int des_gpu_halo_unpack(DesGpu *h, int phase);
+int des_host_build_support(int nnode, int nelem, const int *conn, int *idx, int *arr, int *lidx);
+}
+#include "des_multi.cuh"
+
 // =========================================================================================
 extern "C" {
+
+int des_gpu_create_multi(const DesParam *param, int ndev, const int *devices, DesGpu **out)
+{
+    if (!param || !out || ndev < 1 || ndev > 64) return DES_E_ARG;
+    *out = nullptr;
+    int have = 0;
+    if (cudaGetDeviceCount(&have) != cudaSuccess || have == 0) return DES_E_NODEVICE;
+    DesGpu *h = new DesGpu;
+    h->hp = *param;
+    h->own_stream = false;
+    memset(&h->D, 0, sizeof(h->D));
+    memset(h->kc_ms, 0, sizeof(h->kc_ms));
+    memset(h->kc_n, 0, sizeof(h->kc_n));
+    *out = h;
+    for (int i = 0; i < ndev; ++i) {
+        const int d = devices ? devices[i] : i;
+        if (d < 0 || d >= have) return fail(h, DES_E_NODEVICE, "device index out of range");
+        h->devices.push_back(d);
+    }
+    h->device = h->devices[0];
+    h->multi = new DesMulti;
+    return fill_dev_params(h);      // the same option checks as one device
+}
+
+int des_gpu_partition_info(DesGpu *h, int *nparts, double *partition_seconds, double *upload_seconds,
+                           int *local_elems, int *local_nodes, int *ghost_nodes)
+{
+    if (!h) return DES_E_ARG;
+    if (!h->multi) {
+        if (nparts) *nparts = 1;
+        if (partition_seconds) *partition_seconds = 0;
+        if (upload_seconds) *upload_seconds = 0;
+        if (local_elems) local_elems[0] = h->D.nelem;
+        if (local_nodes) local_nodes[0] = h->D.nnode;
+        if (ghost_nodes) ghost_nodes[0] = h->nrecv;
+        return DES_OK;
+    }
+    const DesMulti &M = *h->multi;
+    if (nparts) *nparts = int(M.parts.size());
+    if (partition_seconds) *partition_seconds = M.partition_seconds;
+    if (upload_seconds) *upload_seconds = M.upload_seconds;
+    for (size_t r = 0; r < M.parts.size(); ++r) {
+        if (local_elems) local_elems[r] = int(M.parts[r].elem_gid.size());
+        if (local_nodes) local_nodes[r] = int(M.parts[r].node_gid.size());
+        if (ghost_nodes) ghost_nodes[r] = int(M.parts[r].recv_nodes.size());
+    }
+    return DES_OK;
+}
 
 int des_gpu_create(const DesParam *param, int device, DesGpu **out)
 {
@@ -485,6 +579,10 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
     h->hp = *param;
     if (const char *sv = getenv("DES_SCHEDULE")) h->schedule = (atoi(sv) == 1) ? 1 : 2;
     if (const char *sv = getenv("DES_ELEM_ORDER")) h->reorder = atoi(sv) != 0;
+    if (const char *sv = getenv("DES_DEFER")) {     // bit 1 ddp, 2 surface scale, 4 compute_dt on E-A
+        const int v = atoi(sv);
+        h->defer_ddp = v & 1; h->defer_scale = (v >> 1) & 1; h->dt_rides = (v >> 2) & 1;
+    }
     if (const char *sv = getenv("DES_PF_ELEMS")) h->pf_elems = atoi(sv) > 0 ? atoi(sv) : 0;
     memset(&h->D, 0, sizeof(h->D));
     h->D.pf = h->pf_elems;
@@ -500,6 +598,7 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
 int des_gpu_destroy(DesGpu *h)
 {
     if (!h) return DES_OK;
+    if (h->multi) { multi_free_parts(h); delete h->multi; h->multi = nullptr; }
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_mesh(h);
@@ -521,6 +620,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     if (!h || !m) return DES_E_ARG;
     if (m->nnode <= 0 || m->nelem <= 0) return fail(h, DES_E_ARG, "empty mesh");
     if (size_t(m->nelem) * 4 >= (size_t(1) << 31)) return fail(h, DES_E_ARG, "nelem*4 overflows int32");
+    if (h->multi) return multi_upload_mesh(h, m, m->coord);
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     free_mesh(h);
@@ -621,6 +721,8 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     D.ca_hi = D.ca + size_t(E) * 4;
     if ((rc = dalloc(h, &D.etmp, E, "etmp"))) return rc;
     if ((rc = dalloc(h, &D.fc, size_t(E) * DES_FC_STRIDE, "fc"))) return rc;
+    if ((rc = dalloc(h, &D.ddp, E, "ddp"))) return rc;
+    if ((rc = dalloc(h, &D.escale, E, "escale"))) return rc;
     CK(cudaMemsetAsync(D.strain_rate, 0, sizeof(double) * 6 * E, h->stream));
     CK(cudaMemsetAsync(D.strain, 0, sizeof(double) * 6 * E, h->stream));
     CK(cudaMemsetAsync(D.stress, 0, sizeof(double) * 6 * E, h->stream));
@@ -651,6 +753,12 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
         if ((rc = upload_new(h, &D.top_elems, te.data(), te.size()))) return rc;
         CK(cudaStreamSynchronize(h->stream));
     }
+    {
+        unsigned char *ef; if ((rc = dalloc(h, &ef, size_t(E), "eflag"))) return rc;
+        CK(cudaMemsetAsync(ef, 0, size_t(E), h->stream));
+        LAUNCH(KC_PACK, k_set_eflag, m->ntop_elems, 256, m->ntop_elems, D.top_elems, ef);
+        D.eflag = ef;
+    }
     if (m->etop != m->nbfacets[5]) return fail(h, DES_E_ARG, "etop != nbfacets[z1]");
     {
         std::vector<int> fe(m->etop), ff(m->etop);
@@ -678,7 +786,16 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     if ((rc = build_stress_bcs(h, m))) return rc;
 
     h->dt_blocks = 148 * 32;     // ~40 elements per thread at 51 M tets: enough warps in flight for the gathers (592 blocks: 2.05 ms, measured)
-    if (!h->dt_partials) CK(cudaMalloc(&h->dt_partials, sizeof(DtPartial) * h->dt_blocks));
+    {
+        // one partial per block of k_dt or of E-A (when compute_dt rides on it) + the final result
+        const size_t cap = std::max(size_t(h->dt_blocks), size_t(DES_GRID(E, DES_EA_BLOCK)));
+        if (cap > h->dt_cap) {
+            if (h->dt_partials) cudaFree(h->dt_partials);
+            h->dt_partials = nullptr; h->dt_cap = 0;
+            CK(cudaMalloc(&h->dt_partials, sizeof(DtPartial) * (cap + 1)));
+            h->dt_cap = cap;
+        }
+    }
     CK(cudaStreamSynchronize(h->stream));
     h->have_mesh = true;
     return DES_OK;
@@ -688,6 +805,7 @@ int des_gpu_upload_elemmarkers(DesGpu *h, const int *elemmarkers)
 {
     if (!h || !elemmarkers) return DES_E_ARG;
     if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    if (h->multi) return multi_upload_elemmarkers(h, elemmarkers);
     CK(cudaSetDevice(h->device));
     int rc = flush_tail(h);     // the pending mass computation must see the OLD markers
     if (rc) return rc;
@@ -709,6 +827,7 @@ int des_gpu_set_compensation_pressure(DesGpu *h, double p)
 {
     if (!h) return DES_E_ARG;
     h->compensation_pressure = p;
+    if (h->multi) for (MultiPart &q : h->multi->parts) q.g->compensation_pressure = p;
     return DES_OK;
 }
 
@@ -716,39 +835,41 @@ int des_gpu_upload_state(DesGpu *h, const DesState *s)
 {
     if (!h || !s) return DES_E_ARG;
     if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    if (h->multi) return multi_move_state(h, s, true);
     CK(cudaSetDevice(h->device));
     int rc = flush_tail(h);
     if (rc) return rc;
     Dev &D = h->D;
     const size_t N = D.nnode, E = D.nelem;
-    if ((rc = ensure_stage(h, std::max(std::max(N * 3, h->eperm ? E * 6 : size_t(1)), size_t(1)) * sizeof(double)))) return rc;
-    double *st = static_cast<double *>(h->stage);
+    // every copy and pack kernel is queued on the stream back to back, each node field through
+    // its own slice of the staging buffer; ONE synchronisation at the end (the host arrays are
+    // borrowed until the call returns)
+    if ((rc = ensure_stage(h, (N * 10 + (h->eperm ? E * 6 : size_t(0)) + 1) * sizeof(double)))) return rc;
+    double *stn = static_cast<double *>(h->stage);
+    double *st = stn + N * 10;      // element rows (internal element order only)
     if (s->coord) {
-        if ((rc = h2d(h, st, s->coord, N * 3))) return rc;
-        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), st, D.xT);
-        CK(cudaStreamSynchronize(h->stream));
+        if ((rc = h2d(h, stn, s->coord, N * 3))) return rc;
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn, D.xT);
     }
     if (s->vel) {
-        if ((rc = h2d(h, st, s->vel, N * 3))) return rc;
-        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), st, D.vv);
-        CK(cudaStreamSynchronize(h->stream));
+        if ((rc = h2d(h, stn + N * 3, s->vel, N * 3))) return rc;
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn + N * 3, D.vv);
     }
     if (s->coord0 && h->hp.has_elastic_foundation) {
-        if ((rc = h2d(h, st, s->coord0, N * 3))) return rc;
-        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), st, D.coord0);
-        CK(cudaStreamSynchronize(h->stream));
+        if ((rc = h2d(h, stn + N * 6, s->coord0, N * 3))) return rc;
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn + N * 6, D.coord0);
     }
     if (s->temperature) {
-        if ((rc = h2d(h, st, s->temperature, N))) return rc;
-        LAUNCH(KC_PACK, k_pack_w, int(N), 256, int(N), st, D.xT);
-        CK(cudaStreamSynchronize(h->stream));
+        if ((rc = h2d(h, stn + N * 9, s->temperature, N))) return rc;
+        LAUNCH(KC_PACK, k_pack_w, int(N), 256, int(N), stn + N * 9, D.xT);
     }
 #define UP(field, dev, n) if (s->field) { if ((rc = h2d(h, dev, (const double *)s->field, n))) return rc; }
     // element fields arrive in the caller's element order and are stored in the internal one
 #define UPE(field, dev, rows) if (s->field) { \
         if (!h->eperm) { if ((rc = h2d(h, dev, (const double *)s->field, E * (rows)))) return rc; } \
         else { if ((rc = h2d(h, st, (const double *)s->field, E * (rows)))) return rc; \
-               LAUNCH(KC_PACK, k_rows_to_internal<double>, int(E), 256, int(E), rows, st, h->eperm, dev); } }
+               LAUNCH(KC_PACK, k_rows_to_internal<double>, int(E), 256, int(E), rows, st, h->eperm, dev); \
+               CK(cudaStreamSynchronize(h->stream)); } }
     UPE(stress, D.stress, 6) UPE(strain, D.strain, 6) UPE(strain_rate, D.strain_rate, 6)
     UPE(plstrain, D.plstrain, 1) UPE(delta_plstrain, D.delta_plstrain, 1)
     UPE(volume, D.volume, 1) UPE(volume_old, D.volume_old, 1)
@@ -768,32 +889,35 @@ int des_gpu_download_state(DesGpu *h, const DesState *s)
 {
     if (!h || !s) return DES_E_ARG;
     if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    if (h->multi) return multi_move_state(h, s, false);
     CK(cudaSetDevice(h->device));
     int rc = flush_tail(h);
     if (rc) return rc;
     Dev &D = h->D;
     const size_t N = D.nnode, E = D.nelem;
-    if ((rc = ensure_stage(h, std::max(std::max(N * 3, h->eperm ? E * 6 : size_t(1)), size_t(1)) * sizeof(double)))) return rc;
-    double *st = static_cast<double *>(h->stage);
+    if ((rc = ensure_stage(h, (N * 10 + (h->eperm ? E * 6 : size_t(0)) + 1) * sizeof(double)))) return rc;
+    double *stn = static_cast<double *>(h->stage);
+    double *st = stn + N * 10;
 #define DN(dst, src, n) CK(cudaMemcpyAsync(dst, src, (n) * sizeof(double), cudaMemcpyDeviceToHost, h->stream))
+    // unpack kernels and copies back to back, one synchronisation at the end
     if (s->coord) {
-        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, st);
-        DN(s->coord, st, N * 3); CK(cudaStreamSynchronize(h->stream));
+        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, stn);
+        DN(s->coord, stn, N * 3);
     }
     if (s->vel) {
-        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.vv, st);
-        DN(s->vel, st, N * 3); CK(cudaStreamSynchronize(h->stream));
+        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.vv, stn + N * 3);
+        DN(s->vel, stn + N * 3, N * 3);
     }
     if (s->temperature) {
-        LAUNCH(KC_PACK, k_unpack_w, int(N), 256, int(N), D.xT, st);
-        DN(s->temperature, st, N); CK(cudaStreamSynchronize(h->stream));
+        LAUNCH(KC_PACK, k_unpack_w, int(N), 256, int(N), D.xT, stn + N * 9);
+        DN(s->temperature, stn + N * 9, N);
     }
 #define DOWN(field, dev, n) if (s->field) { DN(s->field, dev, n); }
     // element fields leave in the caller's element order
 #define DOWNE(field, dev, rows) if (s->field) { \
         if (!h->eperm) { DN(s->field, dev, E * (rows)); } \
         else { LAUNCH(KC_PACK, k_rows_to_caller<double>, int(E), 256, int(E), rows, (const double *)dev, h->einv, st); \
-               DN(s->field, st, E * (rows)); } }
+               DN(s->field, st, E * (rows)); CK(cudaStreamSynchronize(h->stream)); } }
     DOWNE(stress, D.stress, 6) DOWNE(strain, D.strain, 6) DOWNE(strain_rate, D.strain_rate, 6)
     DOWNE(plstrain, D.plstrain, 1) DOWNE(delta_plstrain, D.delta_plstrain, 1)
     DOWNE(volume, D.volume, 1) DOWNE(volume_old, D.volume_old, 1)
@@ -811,6 +935,10 @@ int des_gpu_download_state(DesGpu *h, const DesState *s)
 int des_gpu_sync(DesGpu *h)
 {
     if (!h) return DES_E_ARG;
+    if (h->multi) {
+        for (MultiPart &p : h->multi->parts) { int rc = des_gpu_sync(p.g); if (rc) return fail(h, rc, des_gpu_last_error(p.g)); }
+        return DES_OK;
+    }
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());
@@ -848,17 +976,18 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
         h->seg_tail_mass = tail && mm;
         h->seg_rot = tail && (h->hp.rheol_type & DES_RH_ELASTIC);
     }
-    // E-A / N-A
+    // E-A / N-A (E-A already ran, with compute_dt's reductions on board, if ea_prerun)
+    const bool do_ea = do_elem && !h->ea_prerun;
     if (h->seg_tail_mass) {
-        if (do_elem) LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, DES_EA_BLOCK, h->P, D, 3, hf);
+        if (do_ea) LAUNCH_M(KC_ELEM_A, k2_elem_a, true, E, DES_EA_BLOCK, h->P, D, 3, hf, (DtPartial *)nullptr);
         if (do_node) LAUNCH(KC_NODE_A, (k3_node_a<true>), N, 256, h->P, D0, dt, hf);
         if (do_node) { int rc = ymass_update(h); if (rc) return rc; }
     }
     else {
-        if (do_elem) LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, DES_EA_BLOCK, h->P, D, 0, hf);
+        if (do_ea) LAUNCH_M(KC_ELEM_A, k2_elem_a, false, E, DES_EA_BLOCK, h->P, D, 0, hf, (DtPartial *)nullptr);
         if (do_node) LAUNCH(KC_NODE_A, (k3_node_a<false>), N, 256, h->P, D0, dt, hf);
     }
-    if (do_node) h->tail_pending = false;
+    if (do_node) { h->tail_pending = false; h->ea_prerun = false; }
     }
     else if (seg == 1) {
     const bool rot = h->seg_rot;
@@ -866,15 +995,16 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
     if (do_elem) {
         const double dtr = rot ? h->dt_prev : 0.0;
 #define EB_CASE(S, R, A) switch (h->hp.rheol_type) { \
-        case DES_RH_ELASTIC: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_ELASTIC, A>), E, 128, h->P, D, dt, dtr, afirst); break; \
-        case DES_RH_MAXWELL: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_MAXWELL, A>), E, 128, h->P, D, dt, dtr, afirst); break; \
-        case DES_RH_EP:      LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EP, A>), E, 128, h->P, D, dt, dtr, afirst); break; \
-        default:             LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EVP, A>), E, 128, h->P, D, dt, dtr, afirst); break; }
+        case DES_RH_ELASTIC: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_ELASTIC, A>), E, 128, h->P, D, dt, dtr, afirst, pre); break; \
+        case DES_RH_MAXWELL: LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_MAXWELL, A>), E, 128, h->P, D, dt, dtr, afirst, pre); break; \
+        case DES_RH_EP:      LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EP, A>), E, 128, h->P, D, dt, dtr, afirst, pre); break; \
+        default:             LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EVP, A>), E, 128, h->P, D, dt, dtr, afirst, pre); break; }
         const bool single = h->hp.nmat == 1;
         // a deferred Output::average_fields rides on the rotation (des_gpu_average_fields)
         if (!rot && h->avg_pending) { int rc = average_now(h); if (rc) return rc; }
         const bool avg = rot && h->avg_pending != 0;
         const int afirst = (h->avg_pending == 2) ? 1 : 0;
+        const int pre = (h->nmd_pending ? 1 : 0) | (h->scale_pending ? 2 : 0);
         if (single && avg) EB_CASE(true, true, true)
         else if (avg) EB_CASE(false, true, true)
         else if (single && rot) EB_CASE(true, true, false)
@@ -882,7 +1012,10 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
         else if (rot) EB_CASE(false, true, false)
         else EB_CASE(false, false, false)
 #undef EB_CASE
-        if (avg && (part == -1 || part == 1)) h->avg_pending = 0;      // both element parts have taken it
+        if (part == -1 || part == 1) {      // both element parts have taken it
+            if (avg) h->avg_pending = 0;
+            h->nmd_pending = h->scale_pending = false;
+        }
     }
     if (do_node && h->hp.is_using_mixed_stress) {
         LAUNCH(KC_NODE_B, k_node_b, N, 256, D0);
@@ -891,8 +1024,9 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
     else if (seg == 2) {
     // E-C / N-C
     if (do_elem) {
-    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
-    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
+    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D, h->defer_ddp);
+    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D, 0);
+    if (h->hp.is_using_mixed_stress && h->defer_ddp && (part == -1 || part == 1)) h->nmd_pending = true;
     }
     if (do_node) {
     LAUNCH(KC_SBC, k_sbc_facets, D0.nsbc_facets, 128, h->P, D0, h->compensation_pressure);
@@ -912,7 +1046,11 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
     else if (seg == 4) {
     if (mm) {
         if (h->hp.surface_process_option == 1 && D0.ntop > 0) LAUNCH(KC_SURFACE, k_surf_edvacc, D0.etop, 128, D0);
-        LAUNCH(KC_SURFACE, k_surf_correct_elems, D0.ntop_elems, 128, D0);
+        if (h->defer_scale) {
+            LAUNCH(KC_SURFACE, k_surf_correct_vol, D0.ntop_elems, 128, D0);
+            if (D0.ntop_elems > 0) h->scale_pending = true;
+        }
+        else LAUNCH(KC_SURFACE, k_surf_correct_elems, D0.ntop_elems, 128, D0);
     }
     }
     else {
@@ -932,6 +1070,8 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
     if (seg < 0 || seg > 5) return fail(h, DES_E_ARG, "segment must be 0..5");
     if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
+    if (h->multi) return multi_step_segment(h, seg, dt, time);
+    CK(cudaSetDevice(h->device));
     return segment_impl(h, seg, -1, dt, time);
 }
 
@@ -951,6 +1091,8 @@ int des_gpu_step_segment_part(DesGpu *h, int seg, int part, double dt, double ti
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
     if (seg < 0 || seg > 2 || part < 0 || part > 2) return fail(h, DES_E_ARG, "segment 0..2, part 0..2");
     if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
+    if (h->multi) return fail(h, DES_E_UNSUPPORTED, "segment parts are for hosts that run their own exchange");
+    CK(cudaSetDevice(h->device));
     cudaStream_t keep = h->stream;
     if (cuda_stream) h->stream = static_cast<cudaStream_t>(cuda_stream);
     const int rc = segment_impl(h, seg, part, dt, time);
@@ -964,6 +1106,7 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
+    if (h->multi && h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "several devices need schedule v2");
     if (h->schedule != 1) {
         for (int seg = 0; seg < 6; ++seg) {
             int rc = des_gpu_step_segment(h, seg, dt, time);
@@ -991,8 +1134,8 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
     LAUNCH(KC_ELEM_B, k_elem_b, E, 128, h->P, D, dt, 0);
     if (h->hp.is_using_mixed_stress) LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
     LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
-    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D);
-    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D);
+    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D, 0);
+    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D, 0);
     int bc_z1 = h->hp.vbc_types[5];
     if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
     LAUNCH(KC_NODE_C, k_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
@@ -1014,29 +1157,42 @@ int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out)
 {
     if (!h || !out) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
-    {
+    if (h->multi) return multi_compute_dt(h, out);
+    CK(cudaSetDevice(h->device));
+    int nparts;
+    if (h->schedule == 2 && h->dt_rides) {
+        // compute_dt reads the coordinates, velocities, volume and density the NEXT step's E-A
+        // gathers anyway, and E-A does not depend on dt: run that launch now with the reductions
+        // on board (k2_elem_a<.., DT>); segment 0 of the next step then skips its E-A.  Nothing
+        // is flushed: the deferred compute_volume is part of the same launch (TAIL).
+        const bool tail = h->tail_pending && h->hp.has_moving_mesh;
+        const int E = h->D.nelem, hf = head_flags(h);
+        nparts = DES_GRID(E, DES_EA_BLOCK);
+        const bool single = h->hp.nmat == 1;
+        if (tail && single)  LAUNCH(KC_ELEM_A, (k2_elem_a<true, true, true>), E, DES_EA_BLOCK, h->P, h->D, 3, hf, h->dt_partials);
+        else if (tail)       LAUNCH(KC_ELEM_A, (k2_elem_a<false, true, true>), E, DES_EA_BLOCK, h->P, h->D, 3, hf, h->dt_partials);
+        else if (single)     LAUNCH(KC_ELEM_A, (k2_elem_a<true, false, true>), E, DES_EA_BLOCK, h->P, h->D, 0, hf, h->dt_partials);
+        else                 LAUNCH(KC_ELEM_A, (k2_elem_a<false, false, true>), E, DES_EA_BLOCK, h->P, h->D, 0, hf, h->dt_partials);
+        h->ea_prerun = true;
+    }
+    else {
         // the deferred end-of-step work does not have to be flushed for this: the only
         // thing compute_dt reads from it is volume, which k_dt then evaluates itself
         // (tet_volume of the current coordinates == what compute_volume will store)
         const int fresh_volume = (h->tail_pending && h->hp.has_moving_mesh) ? 1 : 0;
+        nparts = h->dt_blocks;
         LaunchScope ls(h, KC_DT);
         if (h->hp.nmat == 1) k_dt<true><<<h->dt_blocks, 256, 0, h->stream>>>(h->P, h->D, h->dt_partials, fresh_volume);
         else k_dt<false><<<h->dt_blocks, 256, 0, h->stream>>>(h->P, h->D, h->dt_partials, fresh_volume);
     }
-    std::vector<DtPartial> part(h->dt_blocks);
+    // the reduction finishes on the device: 40 + 8 bytes cross PCIe
+    LAUNCH_G(KC_DT, k_dt_final, 1, 1024, 0, nparts, (const DtPartial *)h->dt_partials, h->dt_partials + h->dt_cap);
+    DtPartial r;
     unsigned long long bits = 0;
-    CK(cudaMemcpyAsync(part.data(), h->dt_partials, sizeof(DtPartial) * h->dt_blocks,
-                       cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&r, h->dt_partials + h->dt_cap, sizeof(DtPartial), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpyAsync(&bits, h->D.maxdh_bits, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    DtPartial r = part[0];
-    for (int i = 1; i < h->dt_blocks; ++i) {
-        r.minl = std::min(r.minl, part[i].minl);
-        r.dt_maxwell = std::min(r.dt_maxwell, part[i].dt_maxwell);
-        r.dt_diffusion = std::min(r.dt_diffusion, part[i].dt_diffusion);
-        r.global_dt_min = std::min(r.global_dt_min, part[i].global_dt_min);
-        r.max_vem = std::max(r.max_vem, part[i].max_vem);
-    }
+    CK(cudaGetLastError());
     out->minl = r.minl; out->dt_maxwell = r.dt_maxwell; out->dt_diffusion = r.dt_diffusion;
     out->global_dt_min = r.global_dt_min; out->global_max_vem = r.max_vem;
     double maxdh; memcpy(&maxdh, &bits, sizeof(double));
@@ -1073,6 +1229,7 @@ int des_gpu_mesh_quality(DesGpu *h, const DesQualityParam *qp, DesQuality *out)
 {
     if (!h || !qp || !out) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (h->multi) return multi_mesh_quality(h, qp, out);
     CK(cudaSetDevice(h->device));
     int rc = flush_tail(h);     // bad_mesh_quality reads the volume compute_volume stored
     if (rc) return rc;
@@ -1141,6 +1298,7 @@ int des_gpu_check_nan(DesGpu *h, int *count)
 {
     if (!h || !count) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (h->multi) return fail(h, DES_E_UNSUPPORTED, "check_nan on a group handle: download and scan on the host");
     CK(cudaSetDevice(h->device));
     int rc = flush_tail(h);
     if (rc) return rc;
@@ -1156,6 +1314,11 @@ int des_gpu_average_fields(DesGpu *h, int first)
 {
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (h->multi) {
+        for (MultiPart &p : h->multi->parts) { int rc = des_gpu_average_fields(p.g, first); if (rc) return fail(h, rc, des_gpu_last_error(p.g)); }
+        h->avg_valid = true;
+        return DES_OK;
+    }
     CK(cudaSetDevice(h->device));
     int rc;
     Dev &D = h->D;
@@ -1185,6 +1348,7 @@ int des_gpu_download_averages(DesGpu *h, double *coord0, double *strain0, double
 {
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->avg_valid) return fail(h, DES_E_STATE, "no averaged fields on the device");
+    if (h->multi) return multi_download_averages(h, coord0, strain0, stress_avg, dpl_avg);
     CK(cudaSetDevice(h->device));
     const size_t N = h->D.nnode, E = h->D.nelem;
     int rc;
@@ -1270,6 +1434,7 @@ int des_gpu_halo_width(int phase) { return (phase < 0 || phase > 3) ? -1 : halo_
 int des_gpu_halo_pack(DesGpu *h, int phase)
 {
     if (!h || phase < 0 || phase > 3) return DES_E_ARG;
+    CK(cudaSetDevice(h->device));
     LAUNCH(KC_PACK, k_halo_pack, h->nsend, 256, phase, h->nsend, h->send_idx, h->D, h->top_of_node, h->send_buf);
     CK(cudaGetLastError());
     return DES_OK;
@@ -1278,6 +1443,7 @@ int des_gpu_halo_pack(DesGpu *h, int phase)
 int des_gpu_halo_unpack(DesGpu *h, int phase)
 {
     if (!h || phase < 0 || phase > 3) return DES_E_ARG;
+    CK(cudaSetDevice(h->device));
     LAUNCH(KC_PACK, k_halo_unpack, h->nrecv, 256, phase, h->nrecv, h->recv_idx, h->D, h->top_of_node, h->recv_buf);
     CK(cudaGetLastError());
     return DES_OK;
@@ -1321,7 +1487,13 @@ int des_abi_sizeof(int which)
 }
 
 // ---- instrumentation --------------------------------------------------------------------
-long long des_gpu_launch_count(const DesGpu *h) { return h ? h->launches : 0; }
+long long des_gpu_launch_count(const DesGpu *h)
+{
+    if (!h) return 0;
+    long long n = h->launches;
+    if (h->multi) for (const MultiPart &p : h->multi->parts) n += p.g->launches;
+    return n;
+}
 
 int des_gpu_enable_kernel_timing(DesGpu *h, int on)
 {

@@ -69,6 +69,16 @@ struct Dev {
     // L2 prefetch distance of the element kernels, in elements (0 = off): thread e asks L2 for
     // the streamed rows of element e + pf, so that block finds them in L2 instead of HBM
     int pf;
+    // work of step n that the fused schedule leaves to the next E-B, which streams the stress
+    // rows anyway (des_api.cu: resolve_pending applies it on its own before anything else
+    // looks at the stress):
+    //  ddp[e]     NMD_stress's diagonal correction (geometry.cxx:315-331); E-C uses it for the
+    //             forces but stores the scalar instead of rewriting three stress rows
+    //  eflag[e]   1 = top element (var.top_elems); escale[e] = its rdv of correct_surface_element
+    //             (bc.cxx:1669-1686), whose division of stress / strain / plstrain waits for E-B
+    double *ddp;
+    const unsigned char *eflag;
+    double *escale;
 };
 
 #define DES_GRID(n, b) (((n) + (b) - 1) / (b))
@@ -377,9 +387,12 @@ k_node_b(const __grid_constant__ Dev D)
 // (fields.cxx:622-653)
 // ---------------------------------------------------------------------------------------
 // SINGLE: one material (nmat == 1) -- the marker counts live in registers, not local memory
+// defer (MIXED only): keep the corrected diagonal in registers for the forces and store the
+// scalar ddp[e] (8 B) instead of rewriting three stress rows (24 B); the next E-B, or
+// resolve_pending, adds it to the stored diagonal as its first operation -- the same sum
 template <bool SINGLE, bool MIXED>
 __global__ void __launch_bounds__(256)
-k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
+k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int defer)
 {
     const int e = D.e0 + blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= D.e1) return;
@@ -417,7 +430,12 @@ k_elem_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
         const double dp_el = dp / 4;
         const double ddp = (-dp_orig + dp_el) / 3;
         #pragma unroll
-        for (int i = 0; i < 3; ++i) { s[i] += ddp; D.stress[size_t(i) * E + e] = s[i]; }
+        for (int i = 0; i < 3; ++i) s[i] += ddp;
+        if (defer) D.ddp[e] = ddp;
+        else {
+            #pragma unroll
+            for (int i = 0; i < 3; ++i) D.stress[size_t(i) * E + e] = s[i];
+        }
     }
     double sx[4], sy[4], sz[4];
     shape_fn(a0, a1, a2, a3, vol, sx, sy, sz);
@@ -668,6 +686,65 @@ __global__ void k_surf_correct_elems(const __grid_constant__ Dev D)
     }
 }
 
+// The same loop as the fused step runs it: the new volume and rdv now, the divisions later --
+// stress / strain / plstrain in the next E-B (which streams those rows; here every top element
+// is alone in its 32-byte sector of each of the 19 rows: 2.8 kB of DRAM traffic per element,
+// profiles/r01_v8_ncu_surface_kernels_50M.csv), strain_rate only if something reads it before
+// E-B overwrites it (k_surf_apply_scale below).
+__global__ void k_surf_correct_vol(const __grid_constant__ Dev D)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= D.ntop_elems) return;
+    const int e = D.top_elems[i];
+    const int4 c = D.conn[e];
+    const double nv = tet_volume(D.xT[c.x], D.xT[c.y], D.xT[c.z], D.xT[c.w]);
+    const double rdv = nv / D.volume[e];
+    D.volume[e] = nv;
+    D.escale[e] = rdv;
+}
+
+// the deferred divisions of k_surf_correct_vol, on their own (flush path)
+__global__ void k_surf_apply_scale(const __grid_constant__ Dev D)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= D.ntop_elems) return;
+    const int e = D.top_elems[i];
+    const int E = D.nelem;
+    const double rdv = D.escale[e];
+    if (rdv < 1.0) return;
+    double pl = D.plstrain[e], s[6], es[6], er[6];
+    #pragma unroll
+    for (int j = 0; j < 6; j++) {
+        s[j] = D.stress[size_t(j) * E + e];
+        es[j] = D.strain[size_t(j) * E + e];
+        er[j] = D.strain_rate[size_t(j) * E + e];
+    }
+    D.plstrain[e] = pl / rdv;
+    #pragma unroll
+    for (int j = 0; j < 6; j++) {
+        D.stress[size_t(j) * E + e] = s[j] / rdv;
+        D.strain[size_t(j) * E + e] = es[j] / rdv;
+        D.strain_rate[size_t(j) * E + e] = er[j] / rdv;
+    }
+}
+
+// the deferred diagonal correction of E-C, on its own (flush path)
+__global__ void k_apply_ddp(const __grid_constant__ Dev D)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= D.nelem) return;
+    const size_t E = D.nelem;
+    const double ddp = D.ddp[e];
+    #pragma unroll
+    for (int i = 0; i < 3; ++i) D.stress[i * E + e] += ddp;
+}
+
+__global__ void k_set_eflag(int n, const int *top_elems, unsigned char *eflag)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) eflag[top_elems[i]] = 1;
+}
+
 // correct_surface_element node loop, bc.cxx:1692-1701
 __global__ void k_surf_correct_nodes(const __grid_constant__ Dev D)
 {
@@ -745,6 +822,34 @@ k_dt(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, DtParti
             r.max_vem = fmax(r.max_vem, sh[i].max_vem);
         }
         partials[blockIdx.x] = r;
+    }
+}
+
+// partials[0..n) -> out[0]: the reduction finishes on the device, 40 bytes cross PCIe
+__global__ void __launch_bounds__(1024)
+k_dt_final(int n, const DtPartial *__restrict__ partials, DtPartial *__restrict__ out)
+{
+    double minl = DBL_MAX, dtm = DBL_MAX, dtd = DBL_MAX, gmin = DBL_MAX, vem = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const DtPartial p = partials[i];
+        minl = fmin(minl, p.minl); dtm = fmin(dtm, p.dt_maxwell); dtd = fmin(dtd, p.dt_diffusion);
+        gmin = fmin(gmin, p.global_dt_min); vem = fmax(vem, p.max_vem);
+    }
+    __shared__ DtPartial sh[32];
+    minl = warp_min(minl); dtm = warp_min(dtm); dtd = warp_min(dtd); gmin = warp_min(gmin);
+    vem = warp_max(vem);
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) sh[w] = DtPartial{minl, dtm, dtd, gmin, vem};
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        DtPartial r = sh[0];
+        for (int i = 1; i < (blockDim.x >> 5); ++i) {
+            r.minl = fmin(r.minl, sh[i].minl); r.dt_maxwell = fmin(r.dt_maxwell, sh[i].dt_maxwell);
+            r.dt_diffusion = fmin(r.dt_diffusion, sh[i].dt_diffusion);
+            r.global_dt_min = fmin(r.global_dt_min, sh[i].global_dt_min);
+            r.max_vem = fmax(r.max_vem, sh[i].max_vem);
+        }
+        out[0] = r;
     }
 }
 

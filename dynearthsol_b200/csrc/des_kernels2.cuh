@@ -42,13 +42,43 @@
 #else
 #define DES_EA_BOUNDS __launch_bounds__(DES_EA_BLOCK)
 #endif
-template <bool SINGLE, bool TAIL>
-__global__ void DES_EA_BOUNDS
-k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int tail_flags, int head_flags)
+// DT: also the element loop and reductions of compute_dt (geometry.cxx:1511-1593), which reads
+// the very coordinates, velocities, volume and density this launch already holds -- on the
+// steps where the host asks for a new dt (every 10th) E-A of the NEXT step runs early with DT
+// set (des_gpu_compute_dt) and writes one DtPartial per block; k_dt_final reduces them.
+// block reduction of the five compute_dt quantities -> partials[blockIdx.x] (min and max are
+// exact in any order)
+__device__ __forceinline__ void k2_dt_reduce(double minl, double dtm, double dtd, double gmin, double vem,
+                                             DtPartial *__restrict__ partials)
+{
+    __shared__ DtPartial sh[DES_EA_BLOCK / 32];
+    minl = warp_min(minl); dtm = warp_min(dtm); dtd = warp_min(dtd); gmin = warp_min(gmin);
+    vem = warp_max(vem);
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) sh[w] = DtPartial{minl, dtm, dtd, gmin, vem};
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        DtPartial r = sh[0];
+        for (int i = 1; i < DES_EA_BLOCK / 32; ++i) {
+            r.minl = fmin(r.minl, sh[i].minl); r.dt_maxwell = fmin(r.dt_maxwell, sh[i].dt_maxwell);
+            r.dt_diffusion = fmin(r.dt_diffusion, sh[i].dt_diffusion);
+            r.global_dt_min = fmin(r.global_dt_min, sh[i].global_dt_min);
+            r.max_vem = fmax(r.max_vem, sh[i].max_vem);
+        }
+        partials[blockIdx.x] = r;
+    }
+}
+
+template <bool SINGLE, bool TAIL, bool DT = false>
+__global__ void __launch_bounds__(DES_EA_BLOCK, DT ? 4 : (DES_EA_MINB > 0 ? DES_EA_MINB : 1))
+k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int tail_flags, int head_flags,
+          DtPartial *__restrict__ dt_partials = nullptr)
 {
     // tail_flags: 1 volume, 2 mass contributions;  head_flags: 1 T-diffusion, 4 tr(edot)*vol
-    const int e = D.e0 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= D.e1) return;
+    int e = D.e0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (DT) e = min(e, D.e1 - 1);   // every thread reaches the block reduction at the end: the
+                                    // surplus threads of the last block redo its last element
+    else if (e >= D.e1) return;
     const int nmat = SINGLE ? 1 : P.nmat;
     // every load of the kernel is issued here, before the first use of any of them: the
     // mid-kernel store of volume[e] (which may alias, as far as the compiler knows) and the
@@ -132,6 +162,25 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
     if (head_flags & 1) st256(D.ca + size_t(e) * 4, make_double4(rec[0], rec[1], rec[2], rec[3]));
     if (TAIL) st256(D.ca_hi + size_t(e) * 4, make_double4(rec[4], rec[5], rec[6], rec[7]));
     else if (head_flags & 4) D.ca_hi[size_t(e) * 4] = rec[4];
+
+    if (DT) {
+        // compute_dt's element loop, statement for statement as k_dt (des_kernels.cuh)
+        const double weight = 1.0 / 4;
+        double vxe = 0.0, vye = 0.0, vze = 0.0;
+        vxe += v0.x * weight; vye += v0.y * weight; vze += v0.z * weight;
+        vxe += v1.x * weight; vye += v1.y * weight; vze += v1.z * weight;
+        vxe += v2.x * weight; vye += v2.y * weight; vze += v2.z * weight;
+        vxe += v3.x * weight; vye += v3.y * weight; vze += v3.z * weight;
+        const double vem = sqrt(vxe*vxe + vye*vye + vze*vze);
+        const double maxa = fmax(fmax(tri_area(a0, a1, a2), tri_area(a0, a1, a3)),
+                                 fmax(tri_area(a2, a3, a0), tri_area(a2, a3, a1)));
+        const double minh = 3 * vol / maxa;
+        const double shearm = harm_mean(P.shear_modulus, mk.cnt, nmat);
+        const double dtm = 0.5 * P.visc_min / (1e-40 + shearm);
+        const double dtd = P.has_thermal_diffusion ? 0.5 * minh * minh / P.therm_diff_max : DBL_MAX;
+        const double gmin = minh / sqrt(shearm / rho) / 5.0;
+        k2_dt_reduce(minh, dtm, dtd, gmin, vem, dt_partials);
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -161,8 +210,12 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
 template <bool SINGLE, bool ROT, int RHEOL, bool AVG = false>
 __global__ void DES_EB_BOUNDS
 k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot,
-          int avg_first = 0)
+          int avg_first = 0, int pre = 0)
 {
+    // pre: what the previous step left for this launch to apply to the stored stress first,
+    // in the reference's order -- 1: NMD_stress's diagonal correction ddp[e] (geometry.cxx:
+    // 315-331, computed by E-C), 2: correct_surface_element's divisions by rdv for the top
+    // elements (bc.cxx:1669-1686); then (ROT) rotate_stress
     const int e = D.e0 + blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= D.e1) return;
     const int nmat = SINGLE ? 1 : P.nmat;
@@ -210,6 +263,7 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
                 }
                 if (RHEOL == DES_RH_EP || RHEOL == DES_RH_EVP) pf_l2(D.plstrain + ep);
                 if (RHEOL == DES_RH_MAXWELL || RHEOL == DES_RH_EVP) pf_l2(D.volume_old + ep);
+                if (pre & 1) pf_l2(D.ddp + ep);
             }
         }
         T0 = a0.w; T1 = a1.w; T2 = a2.w; T3 = a3.w;
@@ -251,6 +305,21 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
         es[i] = ld64_v(D.strain + size_t(i) * E + e);
     }
 #endif
+    if (pre & 1) {
+        const double ddp = D.ddp[e];
+        #pragma unroll
+        for (int i = 0; i < 3; ++i) s[i] += ddp;
+    }
+    double rdv = 0;
+    if ((pre & 2) && D.eflag[e]) rdv = D.escale[e];
+    const bool scaled = rdv >= 1.0;
+    bool pls_stored = false;
+    if (scaled) {
+        if (!(RHEOL == DES_RH_EP || RHEOL == DES_RH_EVP)) pls = D.plstrain[e];
+        pls = pls / rdv;
+        #pragma unroll
+        for (int i = 0; i < 6; ++i) { s[i] = s[i] / rdv; es[i] = es[i] / rdv; }
+    }
     if (ROT) {
         jaumann3(s, dt_rot, w3, w4, w5);
         jaumann3(es, dt_rot, w3, w4, w5);
@@ -311,6 +380,7 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
         plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
         rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, s);
         D.plstrain[e] = pls + depls;
+        pls_stored = true;
         dpl = depls;
         break;
     }
@@ -336,12 +406,14 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
         else {
             for (int i = 0; i < 6; ++i) s[i] = sp[i];
             D.plstrain[e] = pls + depls;
+            pls_stored = true;
             dpl = depls;
         }
         break;
     }
     default: break;
     }
+    if (scaled && !pls_stored) D.plstrain[e] = pls;     // the division alone (top elements)
     D.delta_plstrain[e] = dpl;
     #pragma unroll
     for (int i = 0; i < 6; ++i) D.stress[size_t(i) * E + e] = s[i];

@@ -84,6 +84,8 @@ int twin_ready(DesGpu *h)
 {
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (h->multi) return fail(h, DES_E_UNSUPPORTED, "the fine-grained twins run on a single-device handle");
+    CK(cudaSetDevice(h->device));
     return flush_tail(h);
 }
 
@@ -147,7 +149,7 @@ int des_gpu_update_force(DesGpu *h)
 {
     int rc = twin_ready(h); if (rc) return rc;
     LAUNCH(KC_TWIN, k_sbc_facets, h->D.nsbc_facets, 128, h->P, h->D, h->compensation_pressure);
-    LAUNCH_M(KC_TWIN, k_elem_c, false, h->D.nelem, 256, h->P, h->D);
+    LAUNCH_M(KC_TWIN, k_elem_c, false, h->D.nelem, 256, h->P, h->D, 0);
     LAUNCH(KC_TWIN, k_node_c, h->D.nnode, 256, h->P, h->D, 0.0, 0, 1);
     CK(cudaGetLastError());
     return DES_OK;

@@ -211,17 +211,20 @@ def build_box_rank(dims, rank, world, phys_overrides=None):
 
 
 def bench_main(a, rank, world, local_rank, W, K):
-    """bench.py under torchrun: weak scaling, the 150x100x100 km box refined so that every
-    GPU holds about as many tets as the 1-GPU configuration (50M): resolution / world^(1/3)."""
+    """bench.py under torchrun.  Default: the north star's multi-GPU configuration, the 200M-tet
+    box (450x300x300 cells, BASELINE.json configs[2]) split over the N GPUs (strong scaling;
+    the 1-GPU line is the 50M box, the largest single-GPU configuration).  --weak: the
+    150x100x100 km box refined so that every GPU holds about as many tets as --size (50M):
+    resolution / world^(1/3)."""
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from bench import SIZES, ClockSampler, alg_bytes_step, read_peaks      # bench.py is the main module's file
-    size = a.size or "50M"
+    strong = not bool(getattr(a, "weak", False))
+    size = a.size or ("200M" if strong else "50M")
     xl, yl, zl, res = SIZES[size]
-    strong = bool(getattr(a, "strong", False))
     if not strong:
         res = res / world ** (1.0 / 3.0)
     t0 = time.time()

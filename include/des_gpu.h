@@ -119,6 +119,8 @@ typedef struct DesMesh {
     const int *support_surf_arr;    /* surfinfo.support_surf.arr_data */
     const int *elem_and_nodes;      /* segment_t [3*etop] SoA: top-node LOCAL index per facet node */
     const int *connectivity_surface;/* conn_t(etop): [4*etop] SoA, first 3 columns used */
+    const double *coord;            /* var.coord [3*nnode] SoA: read only by a handle that spans several
+                                     * devices (recursive coordinate bisection of the element centroids) */
 } DesMesh;
 
 /* Field arrays.  NULL members are skipped, so the same struct serves as an upload list,
@@ -148,6 +150,21 @@ typedef struct DesDtReductions {
 /* ---- lifetime ------------------------------------------------------------------------ */
 /* after init()/restart() (dynearthsol.cxx:634-650); replaces init_offload_device() */
 int des_gpu_create(const DesParam *param, int device, DesGpu **out);
+/* The same handle over `ndev` devices of one box (devices == NULL: 0..ndev-1; a device may be
+ * listed more than once).  des_gpu_upload_mesh then partitions the mesh (RCB of the element
+ * centroids, node owner = lowest part, one redundant element layer), des_gpu_step exchanges the
+ * ghost-node values between the parts after each nodal barrier (peer copies, no reduction), and
+ * des_gpu_upload_state / _download_state / _upload_elemmarkers scatter and gather the host's
+ * global arrays, so the driver's call sites do not change and results are bit-identical to one
+ * device.  After every remesh the next des_gpu_upload_mesh repartitions; des_gpu_partition_info
+ * reports what that cost.  Not available on a group handle: the fine-grained twins, segment parts,
+ * des_gpu_check_nan, des_gpu_device_ptr, kernel timing (DES_E_UNSUPPORTED). */
+int des_gpu_create_multi(const DesParam *param, int ndev, const int *devices, DesGpu **out);
+/* the last des_gpu_upload_mesh: number of parts, host seconds spent partitioning (RCB, owners,
+ * local meshes, exchange plans) and uploading; per part (arrays of nparts ints, may be NULL) the
+ * local element / node counts including the redundant layer, and the ghost nodes it receives */
+int des_gpu_partition_info(DesGpu *h, int *nparts, double *partition_seconds, double *upload_seconds,
+                           int *local_elems, int *local_nodes, int *ghost_nodes);
 /* end() (dynearthsol.cxx:440-445) */
 int des_gpu_destroy(DesGpu *h);
 const char *des_gpu_last_error(const DesGpu *h);

@@ -18,6 +18,7 @@
 #include <string>
 #include <vector>
 #include <chrono>
+#include <algorithm>
 
 #include "constants.hpp"
 #include "parameters.hpp"
@@ -38,6 +39,83 @@
 void init_var(const Param& param, Variables& var);
 void init(const Param& param, Variables& var);
 void update_mesh(const Param& param, Variables& var);
+
+// ---- large-mesh initialisation of the CPU baseline ----------------------------------------
+// create_boundary_facets (mesh.cxx:3161-3283) scans ALL elements for every boundary segment:
+// O(nseg * nelem), 59 s at 1 M tets and days at the 51.4 M tets of the benchmark.  The library
+// is linked with --wrap on that one symbol (oracle/Makefile): calls from the reference's init()
+// arrive here and go on to the reference's own function (__real_) unless desref_fast_init(1)
+// was called, in which case the SAME candidates are tested in the SAME order, but only the
+// elements around the segment's first node (found through create_support's lists) instead
+// of all of them.  Only bench.py's CPU arm switches it on; every parity fixture comes from the
+// stock path, and tests/test_abi.py checks that both paths fill identical arrays.  The TIMED
+// functions (one_step below) are the reference's own either way.
+extern "C" void __real__Z22create_boundary_facetsR9Variables(Variables &var);
+static int g_fast_init = 0;
+
+static void fast_boundary_facets(Variables &var)
+{
+    create_support(var);    // init() calls it again right after; same result
+    const int nseg = var.nseg;
+    std::vector<int> se(nseg, -1), sf(nseg, -1);
+    int bad = -1;
+    #pragma omp parallel for
+    for (int i = 0; i < nseg; ++i) {
+        const uint flag = static_cast<uint>((*var.segflag)[i][0]);
+        if ((flag & BOUND_ANY) == 0) continue;
+        int k = -1;
+        for (int b = 0; b < nbdrytypes; ++b) if (flag == (1U << b)) k = b;
+        int a[3] = {(*var.segment)[i][0], (*var.segment)[i][1], (*var.segment)[i][2]};
+        std::sort(a, a + 3);
+        // the elements that contain node a[0], ascending: the reference's scan order restricted
+        // to the only elements that can match
+        const int *patch = var.support.patch(a[0]);
+        const int np = var.support.size(a[0]);
+        bool found = false;
+        for (int q = 0; q < np && !found; ++q) {
+            const int e = patch[q];
+            ConstConnAccessor conn = (*var.connectivity)[e];
+            for (int f = 0; f < FACETS_PER_ELEM && !found; ++f) {
+                const uint facet_flag = (*var.bcflag)[conn[NODE_OF_FACET[f][0]]] &
+                                        (*var.bcflag)[conn[NODE_OF_FACET[f][1]]] &
+                                        (*var.bcflag)[conn[NODE_OF_FACET[f][2]]];
+                if ((flag & facet_flag) == 0U) continue;
+                int b3[3] = {conn[NODE_OF_FACET[f][0]], conn[NODE_OF_FACET[f][1]], conn[NODE_OF_FACET[f][2]]};
+                std::sort(b3, b3 + 3);
+                if (a[0] == b3[0] && a[1] == b3[1] && a[2] == b3[2] && k >= 0) {
+                    se[i] = e; sf[i] = f; found = true;
+                }
+            }
+        }
+        if (!found) {
+            #pragma omp critical
+            bad = i;
+        }
+    }
+    if (bad >= 0) { std::fprintf(stderr, "Error: %d-th segment is not on any element\n", bad); std::abort(); }
+    for (int i = 0; i < nseg; ++i) {
+        if (se[i] < 0) continue;
+        const uint flag = static_cast<uint>((*var.segflag)[i][0]);
+        for (int b = 0; b < nbdrytypes; ++b)
+            if (flag == (1U << b)) var.bfacets[b]->emplace_back(se[i], sf[i]);
+    }
+    for (int n = 0; n < nbdrytypes; ++n)
+        std::sort(var.bfacets[n]->begin(), var.bfacets[n]->end(),
+                  [](const int_pair &a, const int_pair &b) { return a.first < b.first; });
+    const int etop = var.bfacets[iboundz1]->size();
+    var.connectivity_surface = new conn_t(etop);
+    for (int i = 0; i < etop; ++i) {
+        const int e = (*var.bfacets[iboundz1])[i].first, f = (*var.bfacets[iboundz1])[i].second;
+        for (int j = 0; j < NODES_PER_FACET; ++j)
+            (*var.connectivity_surface)[i][j] = (*var.connectivity)[e][NODE_OF_FACET[f][j]];
+    }
+}
+
+extern "C" void __wrap__Z22create_boundary_facetsR9Variables(Variables &var)
+{
+    if (g_fast_init) fast_boundary_facets(var);
+    else __real__Z22create_boundary_facetsR9Variables(var);
+}
 
 namespace {
 Param *g_param = nullptr;
@@ -260,6 +338,9 @@ int desref_init(const char *cfg_path)
     g_var->dt = compute_dt(*g_param, *g_var);
     return 0;
 }
+
+// 1: the next desref_init takes the support-based boundary-facet search (see the top of the file)
+int desref_fast_init(int on) { g_fast_init = on; return 0; }
 
 long desref_nbytes(const char *name) { View w = lookup(name); return w.found ? long(w.nbytes) : -1; }
 

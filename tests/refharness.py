@@ -14,9 +14,13 @@ def available():
 class Ref:
     """One reference model per process (the reference keeps static state)."""
 
-    def __init__(self, cfg_path, workdir=None):
+    def __init__(self, cfg_path, workdir=None, fast_init=False):
+        # fast_init: bench.py's CPU arm on meshes the reference's O(nseg * nelem) boundary-facet
+        # search cannot initialise (oracle/ref_harness.cxx: desref_fast_init); never for fixtures
         self.lib = C.CDLL(LIB)
         L = self.lib
+        if fast_init:
+            L.desref_fast_init(1)
         L.desref_init.argtypes = [C.c_char_p]
         L.desref_nbytes.argtypes = [C.c_char_p]; L.desref_nbytes.restype = C.c_long
         L.desref_get.argtypes = [C.c_char_p, C.c_void_p, C.c_long]

@@ -242,3 +242,37 @@ def test_new_entry_points_reject_bad_arguments_and_have_no_cpu_path():
         rc = L.des_gpu_build_support(0, 4, 1, core._ptr(conn, C.c_int), core._ptr(idx, C.c_int),
                                      core._ptr(arr, C.c_int), core._ptr(lidx, C.c_int))
         assert rc == 1
+
+
+def test_reference_fast_init_equals_stock_init(tmp_path):
+    """bench.py's CPU arm initialises large boxes with desref_fast_init(1): the boundary-facet
+    search walks the support of the segment's first node instead of all elements
+    (oracle/ref_harness.cxx).  Same arrays as the reference's own init(), bit for bit."""
+    import subprocess
+    import sys
+    from refharness import available
+    if not available():
+        pytest.skip("oracle/_ref/libdesref.so not built")
+    names = ["connectivity", "coord", "bcflag", "support_arr", "support_idx", "support_lidx", "top_elems",
+             "top_nodes", "elem_and_nodes", "connectivity_surface", "support_surf_arr", "support_surf_idx",
+             "stress", "plstrain", "temperature", "volume", "mass", "tmass", "volume_n", "vel"] \
+        + ["bfacets%d" % i for i in range(10)] + ["bnodes%d" % i for i in range(10)]
+    code = ("import sys; sys.path.insert(0, %r); import numpy as np\n"
+            "from refharness import Ref\n"
+            "r = Ref(%r, workdir=%r, fast_init=bool(int(sys.argv[1])))\n"
+            "r.step(2)\n"
+            "np.savez(sys.argv[2], dt=r.scalar('dt'), **{k: r.get(k) for k in %r})\n"
+            % (HERE, os.path.join(HERE, "cfg", "box-ep.cfg"), str(tmp_path), names))
+    out = []
+    for fast in (0, 1):
+        fn = str(tmp_path / ("init%d.npz" % fast))
+        env = dict(os.environ, OMP_NUM_THREADS="1")     # the stock bucket order is thread-dependent
+        subprocess.run([sys.executable, "-c", code, str(fast), fn], check=True, env=env,
+                       capture_output=True, cwd=str(tmp_path))
+        out.append(np.load(fn))
+    a, b = out
+    for k in names + ["dt"]:
+        x, y = a[k], b[k]
+        if k == "connectivity_surface":     # conn_t with 4 columns, the 4th is never written
+            x, y = x[:3 * x.size // 4], y[:3 * y.size // 4]
+        assert np.array_equal(x, y), k

@@ -206,9 +206,11 @@ def test_update_stress_ql_fallback():
     a, b = got["stress"].reshape(6, E), d["ql_out_stress"].reshape(6, E)
     scale = np.abs(b).max()
     # axis-aligned degenerate states (exactly diagonal / block-diagonal / isotropic): the QL
-    # iteration is deterministic arithmetic on exact zeros -- measured bit-exact, required 1e-12
+    # iteration runs the same recurrences, but the reference's 3x3-C is built -O3 -ffast-math
+    # (its own Makefile), so its rounding is not ours: measured 5.9e-12 on B200, required 1e-10
+    # (the north star's tolerance)
     well = kinds != 2
-    assert np.abs(a - b)[:, well].max() / scale < 1e-12
+    assert np.abs(a - b)[:, well].max() / scale < 1e-10
     # kind 2: an EXACTLY repeated principal value in a rotated frame.  Its eigenvectors are any
     # basis of a plane -- rounding noise picks one -- and the return mapping then separates the
     # pair (rheology.cxx:402-404), so the tensor components inherit that arbitrary choice in the

@@ -17,9 +17,9 @@ REF = os.path.join(ROOT, "oracle", "_ref", "dynearthsol3d.ref")
 B200 = os.path.join(ROOT, "bridge", "_build", "dynearthsol3d.b200")
 
 
-def run(binary, cfg, wd):
+def run(binary, cfg, wd, **extra_env):
     os.makedirs(wd, exist_ok=True)
-    env = dict(os.environ, OMP_NUM_THREADS=str(min(16, os.cpu_count() or 1)))
+    env = dict(os.environ, OMP_NUM_THREADS=str(min(16, os.cpu_count() or 1)), **extra_env)
     r = subprocess.run([binary, os.path.join(HERE, "cfg", cfg)], cwd=wd, env=env, capture_output=True,
                        text=True, timeout=1500)
     assert r.returncode == 0, (binary, r.stdout[-1500:], r.stderr[-1500:])
@@ -31,6 +31,7 @@ def run(binary, cfg, wd):
     ("t3d-remesh.cfg", "t3dr", 5),          # test-3d-remesh.cfg: host remesh at step 300 + re-upload
     ("t3d-iso.cfg", "t3di", 2),             # + isostasy spin-up before the step loop (51 twin-call iterations)
     ("orift.cfg", "orift", 4),              # oblique-rift-3d.cfg (300 steps): EVP, 2 materials, PREM, averaged fields
+    ("orift-full.cfg", "oriftfull", 3),     # oblique-rift-3d.cfg at its configured length (0.1 Myr, ~38 000 steps)
 ])
 def test_driver_matches_reference_frames(cfg, model, frames, tmp_path):
     if not (os.path.exists(REF) and os.path.exists(B200)):
@@ -48,3 +49,28 @@ def test_driver_matches_reference_frames(cfg, model, frames, tmp_path):
         assert not bad, "frame %d: %s   [all: %s]" % (k, bad, " ".join(report))
         worst_all = max(worst_all, worst)
     print("%s: %d frames, worst relative difference %.2e" % (cfg, frames, worst_all))
+
+
+@pytest.mark.parametrize("cfg,model,frames,nparts", [
+    ("t3d-remesh.cfg", "t3dr", 5, 2),       # download (gather by owner) -> host remesh -> re-upload + REPARTITION
+    ("orift.cfg", "orift", 4, 3),           # averaged output fields gathered from three parts
+])
+def test_driver_over_several_devices_matches_reference_frames(cfg, model, frames, nparts, tmp_path):
+    """The same binary with DES_BRIDGE_DEVICES: one handle over several devices (parts share
+    device 0 on a one-GPU box).  Frames must equal the reference's as the one-device run's do."""
+    import torch
+    if not (os.path.exists(REF) and os.path.exists(B200)):
+        pytest.skip("reference / bridge binaries not built (need /root/reference at build time)")
+    ndev = max(1, torch.cuda.device_count())
+    devices = ",".join(str(i % ndev) for i in range(nparts))
+    run(REF, cfg, str(tmp_path / "ref"))
+    out = run(B200, cfg, str(tmp_path / "gpu"), DES_BRIDGE_DEVICES=devices)
+    assert "mesh partitioned over %d devices" % nparts in out
+    if cfg == "t3d-remesh.cfg":
+        assert out.count("mesh partitioned over") == 2 and "host remesh" in out     # initial + after the remesh
+    for k in range(frames):
+        fn = "%s.save.%06d" % (model, k)
+        a = desframe.read_frame(str(tmp_path / "ref" / fn))
+        b = desframe.read_frame(str(tmp_path / "gpu" / fn))
+        worst, report, bad = desframe.compare_frames(a, b)
+        assert not bad, "frame %d: %s   [all: %s]" % (k, bad, " ".join(report))
