@@ -12,6 +12,7 @@
 #include "matprops.hpp"
 #include "markerset.hpp"
 #include "output.hpp"
+#include "utils.hpp"
 #include "des_bridge.hpp"
 
 #ifndef THREED
@@ -164,8 +165,10 @@ int des_bridge_upload(DesBridge *b, const Param &param, const Variables &var)
     m.elem_and_nodes = var.surfinfo.elem_and_nodes->data();
     m.connectivity_surface = var.connectivity_surface->data();
     m.coord = var.coord->data();        // a handle over several devices bisects the element centroids
+    const int64_t t0 = get_nanoseconds();
     int rc = des_gpu_upload_mesh(b->h, &m);
     if (rc) return fail(b, rc, "upload_mesh");
+    const int64_t t1 = get_nanoseconds();
     {
         int nparts = 1;
         double ps = 0, us = 0;
@@ -183,9 +186,12 @@ int des_bridge_upload(DesBridge *b, const Param &param, const Variables &var)
     flatten_markers(b, param, var);
     if ((rc = des_gpu_upload_elemmarkers(b->h, b->flat_markers.data()))) return fail(b, rc, "upload_elemmarkers");
     des_gpu_set_compensation_pressure(b->h, var.compensation_pressure);
+    const int64_t t2 = get_nanoseconds();
     DesState s;
     state_pointers(s, var, true);
     if ((rc = des_gpu_upload_state(b->h, &s))) return fail(b, rc, "upload_state");
+    std::printf("  [B200] upload of %d elements: mesh %.4f s, markers %.4f s, state %.4f s\n", var.nelem,
+                (t1 - t0) * 1e-9, (t2 - t1) * 1e-9, (get_nanoseconds() - t2) * 1e-9);
     return 0;
 }
 

@@ -64,15 +64,21 @@ extern "C" void __wrap__Z14create_supportR9Variables(Variables &var)
 extern "C" void __wrap__Z22create_boundary_facetsR9Variables(Variables &var)
 {
     if (use_reference()) { __real__Z22create_boundary_facetsR9Variables(var); return; }
-    // the search walks the support lists; init() builds them only after this call
-    // (dynearthsol.cxx:169-170) and builds them again then -- the same arrays
-    build_support(var);
+    // the search walks the support lists of the NEW mesh; var.support cannot be used or touched
+    // here: init() builds it only after this call (dynearthsol.cxx:169-170), and inside remesh()
+    // it still holds the OLD mesh's lists, which barycentric_node_interpolation reads after this
+    // call (remeshing.cxx:3020-3037, brc-interpolation.cxx:357)
+    std::vector<int> sidx(size_t(var.nnode) + 1), sarr(size_t(var.nelem) * NODES_PER_ELEM), slidx(sarr.size());
+    {
+        const int rc0 = des_gpu_build_support(topo_device(), var.nnode, var.nelem, var.connectivity->data(),
+                                              sidx.data(), sarr.data(), slidx.data());
+        if (rc0) topo_die("des_gpu_build_support", rc0);
+    }
     const int nseg = var.nseg;
     std::vector<int> se(nseg), sf(nseg);
     int rc = des_gpu_find_boundary_facets(topo_device(), var.nnode, var.nelem, nseg, var.connectivity->data(),
                                           var.segment->data(), var.segflag->data(), var.bcflag->data(),
-                                          var.support.idx_data.data(), var.support.arr_data.data(),
-                                          se.data(), sf.data());
+                                          sidx.data(), sarr.data(), se.data(), sf.data());
     if (rc) topo_die("des_gpu_find_boundary_facets", rc);
     for (int i = 0; i < nseg; ++i)
         if (se[i] == -2) {

@@ -58,7 +58,12 @@ struct DesGpu {
     bool seg_tail_mass = false;         // volume/mass of the previous step pending for segment 0
     int n_interior = 0;                 // leading elements that touch no ghost node (des_gpu_set_interior)
     int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
-    // A/B switches of the three deferrals (all on by default; DES_DEFER=0 turns them off)
+    // A/B switches of the three deferrals (DES_DEFER bits 1, 2, 4; all on).  Measured on the
+    // 51.4M-tet box, same board, back to back (profiles/r02_defer_ab_50M.json): E-C 1.75 -> 1.64 ms
+    // (it no longer rewrites three stress rows), the 0.30 ms correct_surface_element kernel and the
+    // 1.4 ms compute_dt kernel disappear, E-B 3.77 -> 4.01 ms and E-A on dt steps 1.5 -> 2.8 ms pay
+    // for it; the step as a whole moves by less than the run-to-run spread of a power-capped board
+    // (10.35-10.52 ms over the four combinations).
     int defer_ddp = 1, defer_scale = 1, dt_rides = 1;
     // internal element order: DES_ELEM_ORDER=1 stores elements sorted by smallest node index.
     // Off by default: measured on B200 it cuts the lines a warp's gathers touch by 40 % but the
@@ -721,6 +726,8 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     D.ca_hi = D.ca + size_t(E) * 4;
     if ((rc = dalloc(h, &D.etmp, E, "etmp"))) return rc;
     if ((rc = dalloc(h, &D.fc, size_t(E) * DES_FC_STRIDE, "fc"))) return rc;
+    if ((rc = dalloc(h, &D.status, 1, "status"))) return rc;
+    CK(cudaMemsetAsync(D.status, 0, sizeof(int), h->stream));
     if ((rc = dalloc(h, &D.ddp, E, "ddp"))) return rc;
     if ((rc = dalloc(h, &D.escale, E, "escale"))) return rc;
     CK(cudaMemsetAsync(D.strain_rate, 0, sizeof(double) * 6 * E, h->stream));
@@ -1189,10 +1196,13 @@ int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out)
     LAUNCH_G(KC_DT, k_dt_final, 1, 1024, 0, nparts, (const DtPartial *)h->dt_partials, h->dt_partials + h->dt_cap);
     DtPartial r;
     unsigned long long bits = 0;
+    int status = 0;
     CK(cudaMemcpyAsync(&r, h->dt_partials + h->dt_cap, sizeof(DtPartial), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpyAsync(&bits, h->D.maxdh_bits, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&status, h->D.status, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());
+    if (status & 1) return fail(h, DES_E_NAN, "an element volume became non-positive or NaN (compute_volume)");
     out->minl = r.minl; out->dt_maxwell = r.dt_maxwell; out->dt_diffusion = r.dt_diffusion;
     out->global_dt_min = r.global_dt_min; out->global_max_vem = r.max_vem;
     double maxdh; memcpy(&maxdh, &bits, sizeof(double));

@@ -64,6 +64,12 @@ __device__ __forceinline__ double ld64_v(const double *p)       // ordered among
     asm volatile("ld.global.f64 %0, [%1];" : "=d"(r) : "l"(p));
     return r;
 }
+__device__ __forceinline__ unsigned ld8_v(const unsigned char *p)
+{
+    unsigned r;
+    asm volatile("ld.global.u8 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
 // L2 prefetch hint (no register, no scoreboard entry): used for the rows a later block streams
 __device__ __forceinline__ void pf_l2(const void *p)
 {
@@ -362,9 +368,23 @@ __device__ __forceinline__ double ref_pressure(const DevParams &P, double z)
 }
 
 // ---------------------------------------------------------------------------------------
-// 3x3 symmetric eigen-solvers: a restatement of J. Kopp's algorithms (arXiv physics/0610206)
-// as the reference vendors them in 3x3-C/.  A is the upper triangle
-// a00 a01 a02 / a11 a12 / a22.
+// 3x3 symmetric eigen-solvers: a device restatement of J. Kopp's algorithms (arXiv
+// physics/0610206) as the reference vendors them in 3x3-C/ (dsyevc3.c, dsytrd3.c, dsyevq3.c,
+// dsyevh3.c).  The branch decisions and the operation order must match that library for the
+// yield decisions to match the reference, so eig3_cardano / eig3_tridiag / eig3_ql /
+// eig3_hybrid below follow it statement by statement; they are a derived work of it:
+//
+//   Numerical diagonalization of 3x3 matrcies
+//   Copyright (C) 2006  Joachim Kopp
+//
+//   This library is free software; you can redistribute it and/or modify it under the terms
+//   of the GNU Lesser General Public License as published by the Free Software Foundation;
+//   either version 2.1 of the License, or (at your option) any later version.
+//   This library is distributed in the hope that it will be useful, but WITHOUT ANY WARRANTY;
+//   without even the implied warranty of MERCHANTABILITY or FITNESS FOR A PARTICULAR PURPOSE.
+//   See the GNU Lesser General Public License for more details.
+//
+// A is the upper triangle a00 a01 a02 / a11 a12 / a22.
 // ---------------------------------------------------------------------------------------
 struct Sym3 { double a00, a11, a22, a01, a02, a12; };
 

@@ -79,6 +79,9 @@ struct Dev {
     double *ddp;
     const unsigned char *eflag;
     double *escale;
+    // bit 0: compute_volume produced a non-positive or NaN volume (reported by the next
+    // des_gpu_compute_dt / des_gpu_download_state as DES_E_NAN)
+    int *status;
 };
 
 #define DES_GRID(n, b) (((n) + (b) - 1) / (b))
@@ -118,6 +121,7 @@ k_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
     if (TAIL && (tail_flags & 1)) {
         vol = tet_volume(a0, a1, a2, a3);
         D.volume[e] = vol;
+        if (!(vol > 0.0)) atomicOr(D.status, 1);
     }
     else
         vol = D.volume[e];

@@ -70,7 +70,7 @@ __device__ __forceinline__ void k2_dt_reduce(double minl, double dtm, double dtd
 }
 
 template <bool SINGLE, bool TAIL, bool DT = false>
-__global__ void __launch_bounds__(DES_EA_BLOCK, DT ? 4 : (DES_EA_MINB > 0 ? DES_EA_MINB : 1))
+__global__ void __launch_bounds__(DES_EA_BLOCK, DT ? 5 : (DES_EA_MINB > 0 ? DES_EA_MINB : 1))
 k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, int tail_flags, int head_flags,
           DtPartial *__restrict__ dt_partials = nullptr)
 {
@@ -110,6 +110,7 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
     if (TAIL && (tail_flags & 1)) {
         vol = tet_volume(a0, a1, a2, a3);       // compute_volume, geometry.cxx:180-197
         D.volume[e] = vol;
+        if (!(vol > 0.0)) atomicOr(D.status, 1);    // inverted / NaN element: DES_E_NAN at the next sync point
     }
 
     double sx[4], sy[4], sz[4];
@@ -264,6 +265,7 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
                 if (RHEOL == DES_RH_EP || RHEOL == DES_RH_EVP) pf_l2(D.plstrain + ep);
                 if (RHEOL == DES_RH_MAXWELL || RHEOL == DES_RH_EVP) pf_l2(D.volume_old + ep);
                 if (pre & 1) pf_l2(D.ddp + ep);
+                if (pre & 2) pf_l2(D.eflag + ep);
             }
         }
         T0 = a0.w; T1 = a1.w; T2 = a2.w; T3 = a3.w;
@@ -296,6 +298,12 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
         for (int i = 0; i < 4; ++i) edot[5] += 0.5 * (vy[i] * sz[i] + vz[i] * sy[i]);
     }
 
+    // what the previous step left for this launch: requested in the same batch as the stress
+    // rows (one more dependent round trip otherwise: measured +0.45 ms at 51 M tets)
+    double ddp = 0;
+    unsigned ef = 0;
+    if (pre & 1) ddp = ld64_v(D.ddp + e);
+    if (pre & 2) ef = ld8_v(D.eflag + e);
 #if DES_EB_LATE
     // stress and strain are requested only now (volatile: the order is kept), when the 64
     // registers of the node records are free again; the rows were prefetched into L2
@@ -306,12 +314,11 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     }
 #endif
     if (pre & 1) {
-        const double ddp = D.ddp[e];
         #pragma unroll
         for (int i = 0; i < 3; ++i) s[i] += ddp;
     }
     double rdv = 0;
-    if ((pre & 2) && D.eflag[e]) rdv = D.escale[e];
+    if (ef) rdv = D.escale[e];          // top elements only
     const bool scaled = rdv >= 1.0;
     bool pls_stored = false;
     if (scaled) {

