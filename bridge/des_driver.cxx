@@ -4,7 +4,7 @@
 // parsing, init(), mesh generation, markers, phase changes, remeshing, output.
 //
 // main() below follows dynearthsol.cxx:593-1030 for the configurations in scope (isostasy
-// spin-up included; no restart, GoSPL, PT loop, hydraulics, rate-and-state/ATS, monitor): the statements that remain are
+// spin-up and restart included; no GoSPL, PT loop, hydraulics, rate-and-state/ATS, monitor): the statements that remain are
 // the reference's own calls; the lines marked [B200] are the swaps INTEGRATION.md lists.
 #include <cstdio>
 #include <iostream>
@@ -25,6 +25,7 @@
 
 void init_var(const Param& param, Variables& var);      // dynearthsol.cxx:36
 void init(const Param& param, Variables& var);          // dynearthsol.cxx:159
+void restart(const Param& param, Variables& var);       // dynearthsol.cxx:231
 void end(Variables& var);                               // dynearthsol.cxx:440
 
 static int unsupported(const char *what)
@@ -42,7 +43,6 @@ int main(int argc, const char* argv[])
     }
     Param param;
     get_input_parameters(argv[1], param);
-    if (param.sim.is_restarting) return unsupported("sim.is_restarting");
     if (param.control.has_PT) return unsupported("control.has_PT");
     if (param.control.has_hydraulic_diffusion) return unsupported("control.has_hydraulic_diffusion");
     if (param.control.use_global_velocity_scaling) return unsupported("control.use_global_velocity_scaling");
@@ -50,25 +50,36 @@ int main(int argc, const char* argv[])
 
     static Variables var;
     init_var(param, var);
-    var.output = new Output(param, var.func_time.start_time, 0);
-    init(param, var);
-    var.info_display_next_step = param.sim.info_display_step_interval;
+    var.output = new Output(param, var.func_time.start_time,
+                            (param.sim.is_restarting) ? param.sim.restarting_from_frame : 0);
+    DesBridge *gpu = nullptr;
+    if (! param.sim.is_restarting) {
+        init(param, var);
+        var.info_display_next_step = param.sim.info_display_step_interval;
 
-    // [B200] device model: after init() (dynearthsol.cxx:634), replaces init_offload_device()
-    DesBridge *gpu = des_bridge_create(param, var, 0);
-    if (!gpu) return 1;
-    if (param.ic.isostasy_adjustment_time_in_yr > 0) {
-        // [B200] isostasy_adjustment(param, var);   (dynearthsol.cxx:638-641) through the twins,
-        // then the adjusted state back into Variables for the first frame
-        if (des_bridge_isostasy_adjustment(gpu, param, var)) return 1;
-        if (des_bridge_download(gpu, var, DES_DL_ALL)) return 1;
+        // [B200] device model: after init() (dynearthsol.cxx:634), replaces init_offload_device()
+        gpu = des_bridge_create(param, var, 0);
+        if (!gpu) return 1;
+        if (param.ic.isostasy_adjustment_time_in_yr > 0) {
+            // [B200] isostasy_adjustment(param, var);   (dynearthsol.cxx:638-641) through the twins,
+            // then the adjusted state back into Variables for the first frame
+            if (des_bridge_isostasy_adjustment(gpu, param, var)) return 1;
+            if (des_bridge_download(gpu, var, DES_DL_ALL)) return 1;
+        }
+        // [B200] var.dt = compute_dt(param, var);   (dynearthsol.cxx:643)
+        var.dt = des_bridge_compute_dt(gpu, param, var);
+        if (!(var.dt > 0)) { std::cerr << "dt <= 0\n"; return 11; }
+
+        if (param.sim.has_initial_checkpoint)
+            var.output->write_checkpoint(param, var);
     }
-    // [B200] var.dt = compute_dt(param, var);   (dynearthsol.cxx:643)
-    var.dt = des_bridge_compute_dt(gpu, param, var);
-    if (!(var.dt > 0)) { std::cerr << "dt <= 0\n"; return 11; }
-
-    if (param.sim.has_initial_checkpoint)
-        var.output->write_checkpoint(param, var);
+    else {
+        // restart() (dynearthsol.cxx:231-437) rebuilds mesh, topology, fields, mass and dt on the
+        // host from the checkpoint; the device needs nothing extra: the normal upload
+        restart(param, var);
+        gpu = des_bridge_create(param, var, 0);
+        if (!gpu) return 1;
+    }
 
     int64_t init_time = get_nanoseconds() - var.func_time.start_time;
     var.output->write_exact(var);

@@ -115,3 +115,26 @@ def test_driver_over_several_devices_matches_reference_frames(cfg, model, frames
         b = desframe.read_frame(str(tmp_path / "gpu" / fn))
         worst, report, bad = desframe.compare_frames(a, b)
         assert not bad, "frame %d: %s   [all: %s]" % (k, bad, " ".join(report))
+
+
+def test_driver_restart_matches_reference_frames(tmp_path):
+    """sim.is_restarting: restart() (dynearthsol.cxx:231-437) rebuilds the host state from a
+    checkpoint; the bridge uploads it like any other state.  The reference writes the
+    checkpoints (t3d-ckpt.cfg), then both binaries restart from its frame 2 (t3d-restart.cfg)."""
+    import shutil
+    if not (os.path.exists(REF) and os.path.exists(B200)):
+        pytest.skip("reference / bridge binaries not built (need /root/reference at build time)")
+    run(REF, "t3d-ckpt.cfg", str(tmp_path / "ref"))
+    os.makedirs(str(tmp_path / "gpu"))
+    for f in os.listdir(str(tmp_path / "ref")):
+        if f.startswith("t3dck."):
+            shutil.copy(str(tmp_path / "ref" / f), str(tmp_path / "gpu"))
+    run(REF, "t3d-restart.cfg", str(tmp_path / "ref"))
+    out = run(B200, "t3d-restart.cfg", str(tmp_path / "gpu"))
+    assert "Initializing mesh and field data from checkpoints" in out
+    for k in (2, 3, 4, 5):
+        fn = "t3drs.save.%06d" % k
+        a = desframe.read_frame(str(tmp_path / "ref" / fn))
+        b = desframe.read_frame(str(tmp_path / "gpu" / fn))
+        worst, report, bad = desframe.compare_frames(a, b)
+        assert not bad, "frame %d: %s   [all: %s]" % (k, bad, " ".join(report))
