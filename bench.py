@@ -159,8 +159,8 @@ def run_steps(g, n, dt, t, s):
 
 def read_traffic():
     """DRAM bytes per element and launch of each kernel, from the committed ncu --set full
-    capture (profiles/r01_v8_traffic.json); None if absent."""
-    p = os.path.join(ROOT, "profiles", "r01_v8_traffic.json")
+    capture at 51.4M tets (profiles/r02_traffic_50M.json); None if absent."""
+    p = os.path.join(ROOT, "profiles", "r02_traffic_50M.json")
     if os.path.exists(p):
         return json.load(open(p))
     return None
@@ -284,6 +284,47 @@ min_viscosity = 1e24
 """
 
 
+def driver_bench(a, K, W, metric, unit):
+    """dynearthsol3d.b200 (the reference's object code + the bridge) on a generated box .cfg."""
+    import re
+    import tempfile
+    size = a.size or "6M"
+    xl, yl, zl, res = SIZES[size]
+    exe = os.path.join(ROOT, "bridge", "_build", "dynearthsol3d.b200")
+    if not os.path.exists(exe):
+        print(json.dumps({"impl": "driver", "unavailable": "bridge/_build/dynearthsol3d.b200 not built"}))
+        return
+    wd = tempfile.mkdtemp(prefix="desdrv_")
+    # the reference's "Compute" bucket also holds the final download and end() (freeing the host
+    # arrays): a few hundred steps make that a small share
+    nsteps = max(K + W, 300)
+    cfg = (CFG_TEMPLATE % dict(xl=xl, yl=yl, zl=zl, res=res)).replace("max_steps = 10", "max_steps = %d" % nsteps)
+    open(os.path.join(wd, "drv.cfg"), "w").write(cfg)
+    env = dict(os.environ, OMP_NUM_THREADS=str(os.cpu_count() or 1), DES_BRIDGE_NO_INITIAL_FRAME="1")
+    t0 = time.time()
+    r = subprocess.run([exe, "drv.cfg"], cwd=wd, env=env, capture_output=True, text=True)
+    wall = time.time() - t0
+    m = re.search(r"Compute\s*:\s*\S+.*?/\s*(\d+)\s*=\s*([0-9.eE+-]+)\s*s/step", r.stdout)
+    mm = re.search(r"nodes=(\d+), elements=(\d+)", r.stdout)
+    im = re.search(r"Initiate:\s*(\d+):(\d+):([0-9.]+)", r.stdout)
+    if r.returncode != 0 or not m or not mm:
+        print(json.dumps({"impl": "driver", "unavailable": "driver run failed: " + (r.stderr or r.stdout)[-300:]}))
+        return
+    N, E = int(mm.group(1)), int(mm.group(2))
+    s_step = float(m.group(2))
+    init_s = (int(im.group(1)) * 3600 + int(im.group(2)) * 60 + float(im.group(3))) if im else None
+    print(json.dumps({"impl": "driver", "metric": metric, "value": E / s_step, "unit": unit, "n_gpus": 1,
+                      "steps": int(m.group(1)), "warmup": 0, "ms_per_step": s_step * 1e3, "higher_is_better": True,
+                      "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": "box %s (%d tets, %d nodes) from a .cfg through dynearthsol3d.b200: the reference's "
+                                             "init() (markers, initial fields) with create_boundary_facets / create_support "
+                                             "swapped for the library's builders, step loop on the GPU, compute_dt every 10 steps; "
+                                             "Compute = run time - init - output, over ALL steps (no warm-up excluded)" % (size, E, N),
+                                 "init_seconds": init_s, "wall_seconds": wall}}))
+    import shutil
+    shutil.rmtree(wd, ignore_errors=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -296,6 +337,11 @@ def main():
                     help="box the CPU reference runs on (default: --impl reference: the named workload when "
                          "the host has the RAM for it, else 6M; cpu_baseline leg: 1M)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--driver", action="store_true",
+                    help="measure the path through the reference's own driver instead of the ctypes mirror: "
+                         "bridge/_build/dynearthsol3d.b200 reads a .cfg (meshing_option = 1 box of --size, default 6M), "
+                         "init() runs on the host with the library's topology builders, the step loop on the GPU; "
+                         "the value is the reference's own \"Compute ... s/step\" line")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--strong", action="store_true",
@@ -350,6 +396,9 @@ def main():
         from dynearthsol_b200 import multigpu
         return multigpu.bench_main(a, rank, world, local_rank, W, K)
 
+    if a.driver:
+        return driver_bench(a, K, W, metric, unit)
+
     size = a.size or "50M"
     prob = build_problem(size, a.order, a.verbose)
     E, N = prob["nelem"], prob["nnode"]
@@ -396,7 +445,7 @@ def main():
             if key in per_kernel:
                 per_kernel[key]["dram_bytes_per_elem_ncu"] = v
         if dom in tr["dram_bytes_per_elem"]:
-            traffic = tr["dram_bytes_per_elem"][dom] * E      # bytes per launch, scaled from the 6M capture
+            traffic = tr["dram_bytes_per_elem"][dom] * E      # bytes per launch (the capture is at 51.4M tets)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["achieved_gbs"], "peak": peak,
                 "unit": "GB/s", "frac": per_kernel[dom]["achieved_gbs"] / peak, "traffic": traffic,
                 "traffic_source": tr["source"] if tr else None,
@@ -438,7 +487,7 @@ def main():
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(size, prob["cells"], E, N),
-                       "element_order": a.order, "schedule": os.environ.get("DES_SCHEDULE", "2"), "l2": "working set (%.1f GB) >> 126 MB L2" % (E * 1160 / 1e9),
+                       "element_order": a.order, "l2": "working set (%.1f GB) >> 126 MB L2" % (E * 1160 / 1e9),
                        "parallelism": "1 GPU"},
             "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu}

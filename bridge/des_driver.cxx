@@ -7,6 +7,7 @@
 // spin-up and restart included; no GoSPL, PT loop, hydraulics, rate-and-state/ATS, monitor): the statements that remain are
 // the reference's own calls; the lines marked [B200] are the swaps INTEGRATION.md lists.
 #include <cstdio>
+#include <cstdlib>
 #include <iostream>
 #include <iomanip>
 #include <limits>
@@ -82,7 +83,9 @@ int main(int argc, const char* argv[])
     }
 
     int64_t init_time = get_nanoseconds() - var.func_time.start_time;
-    var.output->write_exact(var);
+    // (benchmark runs of multi-million-element boxes skip the initial frame: tens of GB with markers)
+    if (!std::getenv("DES_BRIDGE_NO_INITIAL_FRAME"))
+        var.output->write_exact(var);
 
     const double starting_time = var.reference_frame_time;
     var.reference_frame_time = starting_time + param.sim.output_time_interval_in_yr * YEAR2SEC;

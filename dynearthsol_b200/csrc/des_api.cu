@@ -57,7 +57,6 @@ struct DesGpu {
     bool seg_rot = false;               // rotation pending for segment 1 of the current step
     bool seg_tail_mass = false;         // volume/mass of the previous step pending for segment 0
     int n_interior = 0;                 // leading elements that touch no ghost node (des_gpu_set_interior)
-    int schedule = 2;                   // DES_SCHEDULE=1 selects the v1 kernels (A/B measurements)
     // A/B switches of the three deferrals (DES_DEFER bits 1, 2, 4; all on).  Measured on the
     // 51.4M-tet box, same board, back to back (profiles/r02_defer_ab_50M.json): E-C 1.75 -> 1.64 ms
     // (it no longer rewrites three stress rows), the 0.30 ms correct_surface_element kernel and the
@@ -582,7 +581,6 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
     DesGpu *h = new DesGpu;
     h->device = device;
     h->hp = *param;
-    if (const char *sv = getenv("DES_SCHEDULE")) h->schedule = (atoi(sv) == 1) ? 1 : 2;
     if (const char *sv = getenv("DES_ELEM_ORDER")) h->reorder = atoi(sv) != 0;
     if (const char *sv = getenv("DES_DEFER")) {     // bit 1 ddp, 2 surface scale, 4 compute_dt on E-A
         const int v = atoi(sv);
@@ -1076,7 +1074,6 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
     if (seg < 0 || seg > 5) return fail(h, DES_E_ARG, "segment must be 0..5");
-    if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
     if (h->multi) return multi_step_segment(h, seg, dt, time);
     CK(cudaSetDevice(h->device));
     return segment_impl(h, seg, -1, dt, time);
@@ -1097,7 +1094,6 @@ int des_gpu_step_segment_part(DesGpu *h, int seg, int part, double dt, double ti
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
     if (seg < 0 || seg > 2 || part < 0 || part > 2) return fail(h, DES_E_ARG, "segment 0..2, part 0..2");
-    if (h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "segments need schedule v2");
     if (h->multi) return fail(h, DES_E_UNSUPPORTED, "segment parts are for hosts that run their own exchange");
     CK(cudaSetDevice(h->device));
     cudaStream_t keep = h->stream;
@@ -1113,50 +1109,10 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps)
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
-    if (h->multi && h->schedule == 1) return fail(h, DES_E_UNSUPPORTED, "several devices need schedule v2");
-    if (h->schedule != 1) {
-        for (int seg = 0; seg < 6; ++seg) {
-            int rc = des_gpu_step_segment(h, seg, dt, time);
-            if (rc) return rc;
-        }
-        return DES_OK;
-    }
-    Dev &D = h->D;
-    const int N = D.nnode, E = D.nelem;
-    const int mm = h->hp.has_moving_mesh;
-    const int hf = head_flags(h);
-    {
-    // ---- schedule v1 (des_kernels.cuh): rotation in E-A, strain rate stored by E-A ----
-    if (h->tail_pending) {
-        LAUNCH(KC_ELEM_A, (k_elem_a<true, true>), E, 256, h->P, D, h->dt_prev, tail_flags(h), hf);
-        if (mm) LAUNCH(KC_NODE_A, (k_node_a<true, true>), N, 256, h->P, D, dt, hf);
-        else    LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
-        if (mm) { int rc = ymass_update(h); if (rc) return rc; }
-        h->tail_pending = false;
-    }
-    else {
-        LAUNCH(KC_ELEM_A, (k_elem_a<false, true>), E, 256, h->P, D, 0.0, 0, hf);
-        LAUNCH(KC_NODE_A, (k_node_a<false, true>), N, 256, h->P, D, dt, hf);
-    }
-    LAUNCH(KC_ELEM_B, k_elem_b, E, 128, h->P, D, dt, 0);
-    if (h->hp.is_using_mixed_stress) LAUNCH(KC_NODE_B, k_node_b, N, 256, D);
-    LAUNCH(KC_SBC, k_sbc_facets, D.nsbc_facets, 128, h->P, D, h->compensation_pressure);
-    if (h->hp.is_using_mixed_stress) LAUNCH_M(KC_ELEM_C, k_elem_c, true, E, 256, h->P, D, 0);
-    else                             LAUNCH_M(KC_ELEM_C, k_elem_c, false, E, 256, h->P, D, 0);
-    int bc_z1 = h->hp.vbc_types[5];
-    if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
-    LAUNCH(KC_NODE_C, k_node_c, N, 256, h->P, D, dt, bc_z1, mm ? 15 : 7);
-    }
-    // update_mesh remainder
-    if (mm) {
-        int rc = run_surface(h, dt, false);
+    for (int seg = 0; seg < 6; ++seg) {
+        int rc = des_gpu_step_segment(h, seg, dt, time);
         if (rc) return rc;
-        std::swap(D.volume, D.volume_old);      // dynearthsol.cxx:466-470
     }
-    h->tail_pending = true;
-    h->dt_prev = dt;
-    h->last_dt = dt;
-    CK(cudaGetLastError());
     return DES_OK;
 }
 
@@ -1167,7 +1123,7 @@ int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out)
     if (h->multi) return multi_compute_dt(h, out);
     CK(cudaSetDevice(h->device));
     int nparts;
-    if (h->schedule == 2 && h->dt_rides) {
+    if (h->dt_rides) {
         // compute_dt reads the coordinates, velocities, volume and density the NEXT step's E-A
         // gathers anyway, and E-A does not depend on dt: run that launch now with the reductions
         // on board (k2_elem_a<.., DT>); segment 0 of the next step then skips its E-A.  Nothing
@@ -1348,7 +1304,7 @@ int des_gpu_average_fields(DesGpu *h, int first)
     // deferred, the rotation happens inside the next step's E-B, and the sums ride on it there
     // (k2_elem_b<.., AVG>): no flush, +112 B/element in that launch.  Otherwise: now.
     h->avg_pending = first ? 2 : 1;
-    const bool rides = h->tail_pending && h->schedule != 1 && (h->hp.rheol_type & DES_RH_ELASTIC);
+    const bool rides = h->tail_pending && (h->hp.rheol_type & DES_RH_ELASTIC);
     if (!rides && (rc = flush_tail(h))) return rc;
     CK(cudaGetLastError());
     return DES_OK;

@@ -3,7 +3,7 @@
 //   E-A  k_elem_a<TAIL,HEAD>   tail(n-1): volume, mass contributions, Jaumann rotation
 //                              head(n)  : T-diffusion contributions, strain rate, tr(edot)*vol
 //   N-A  k_node_a<MASS,HEAD>   CSR gather: volume_n/mass/tmass, T update, dvoldt
-//   E-B  k_elem_b              edvoldt, anti-locking, strain, rheology, plstrain, dpressure*vol
+//   E-B  (des_kernels2.cuh: k2_elem_b, also the update_stress twin)
 //   N-B  k_node_b              CSR gather: dp_nd
 //   E-C  k_elem_c<MIXED>       NMD correction of the stress diagonal, element forces
 //   N-C  k_node_c              CSR gather of forces, stress bcs, damping, v, vbc, x
@@ -247,118 +247,6 @@ k_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
             D.xT[n].w = T;
         }
         if (head_flags & 4) D.ntmp[n] = dvol / vn;
-    }
-}
-
-// ---------------------------------------------------------------------------------------
-// E-B
-// ---------------------------------------------------------------------------------------
-// compute_edvoldt (geometry.cxx:263-272) + update_stress (rheology.cxx:727-1026) + the
-// first loop of NMD_stress (geometry.cxx:293-295).
-__global__ void __launch_bounds__(128)
-k_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int edv_mode)
-{
-    // edv_mode: 0 = edvoldt from ntmp (fused), 1 = same and store it, 2 = load D.edvoldt (twin)
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= D.nelem) return;
-    const int nmat = P.nmat;
-    const int E = D.nelem;
-    const int4 c = D.conn[e];
-
-    double edvoldt;
-    if (edv_mode == 2) edvoldt = D.edvoldt[e];
-    else {
-        double dj = 0;
-        dj += D.ntmp[c.x]; dj += D.ntmp[c.y]; dj += D.ntmp[c.z]; dj += D.ntmp[c.w];
-        edvoldt = dj / 4;
-        if (edv_mode == 1) D.edvoldt[e] = edvoldt;
-    }
-
-    double s[6], es[6], edot[6];
-    #pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        s[i] = D.stress[size_t(i) * E + e];
-        es[i] = D.strain[size_t(i) * E + e];
-        edot[i] = D.strain_rate[size_t(i) * E + e];
-    }
-    const double old_s = trace3(s);
-
-    // anti-mesh-locking correction, rheology.cxx:786-793
-    {
-        const double div = trace3(edot);
-        for (int i = 0; i < 3; ++i) edot[i] += (edvoldt - div) / 3;
-    }
-    double de[6];
-    for (int i = 0; i < 6; ++i) es[i] += edot[i] * dt;
-    for (int i = 0; i < 6; ++i) de[i] = edot[i] * dt;
-    #pragma unroll
-    for (int i = 0; i < 3; ++i) D.strain_rate[size_t(i) * E + e] = edot[i];
-    #pragma unroll
-    for (int i = 0; i < 6; ++i) D.strain[size_t(i) * E + e] = es[i];
-
-    Markers mk;
-    load_markers(D.elemmarkers, e, nmat, mk);
-    const double bulkm = harm_mean(P.bulk_modulus, mk.cnt, nmat);
-    const double shearm = harm_mean(P.shear_modulus, mk.cnt, nmat);
-    const double vol = D.volume[e];
-    double dpl = 0.;
-
-    switch (P.rheol_type) {
-    case DES_RH_ELASTIC:
-        rh_elastic(bulkm, shearm, de, s);
-        break;
-    case DES_RH_MAXWELL: {
-        const double visc = mat_visc(P, nmat, mk, D.xT[c.x].w, D.xT[c.y].w, D.xT[c.z].w, D.xT[c.w].w, s, edot);
-        D.viscosity[e] = visc;
-        const double dv = vol / D.volume_old[e] - 1;
-        rh_maxwell(bulkm, shearm, visc, dt, dv, de, s);
-        break;
-    }
-    case DES_RH_EP: {
-        double depls = 0, amc, anphi, anpsi, hardn, ten_max;
-        const double pls = D.plstrain[e];
-        plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
-        rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, s);
-        D.plstrain[e] = pls + depls;
-        dpl = depls;
-        break;
-    }
-    case DES_RH_EVP: {
-        double depls = 0;
-        const double visc = mat_visc(P, nmat, mk, D.xT[c.x].w, D.xT[c.y].w, D.xT[c.z].w, D.xT[c.w].w, s, edot);
-        D.viscosity[e] = visc;
-        const double dv = vol / D.volume_old[e] - 1;
-        double sv[6];
-        for (int i = 0; i < 6; ++i) sv[i] = s[i];
-        rh_maxwell(bulkm, shearm, visc, dt, dv, de, sv);
-        const double svII = second_invariant2(sv);
-
-        double amc, anphi, anpsi, hardn, ten_max;
-        const double pls = D.plstrain[e];
-        plastic_props(P, nmat, mk, pls, amc, anphi, anpsi, hardn, ten_max);
-        double sp[6];
-        for (int i = 0; i < 6; ++i) sp[i] = s[i];
-        rh_elasto_plastic(bulkm, shearm, amc, anphi, anpsi, hardn, ten_max, de, depls, sp);
-        const double spII = second_invariant2(sp);
-        if (svII < spII) {
-            for (int i = 0; i < 6; ++i) s[i] = sv[i];
-        }
-        else {
-            for (int i = 0; i < 6; ++i) s[i] = sp[i];
-            D.plstrain[e] = pls + depls;
-            dpl = depls;
-        }
-        break;
-    }
-    default: break;
-    }
-    D.delta_plstrain[e] = dpl;
-    #pragma unroll
-    for (int i = 0; i < 6; ++i) D.stress[size_t(i) * E + e] = s[i];
-    if (P.is_using_mixed_stress) {
-        const double dp = trace3(s) - old_s;
-        D.dpressure[e] = dp;
-        D.etmp[e] = dp * vol;
     }
 }
 

@@ -208,7 +208,10 @@ k2_elem_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, in
 // AVG (only with ROT): Output::average_fields (output.cxx:312-352) of the step that just ended,
 // whose call the host deferred to this launch -- the rotated stress it must see is in
 // registers here.  avg_first: the interval's first step (snapshot) instead of a running sum.
-template <bool SINGLE, bool ROT, int RHEOL, bool AVG = false>
+// TWIN (never with ROT / AVG): the un-fused reference call update_stress (rheology.cxx:703) --
+// the strain rate and edvoldt are the STORED ones (update_strain_rate and compute_edvoldt ran
+// as their own calls), everything after that is the same code as the fused step.
+template <bool SINGLE, bool ROT, int RHEOL, bool AVG = false, bool TWIN = false>
 __global__ void DES_EB_BOUNDS
 k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot,
           int avg_first = 0, int pre = 0)
@@ -243,7 +246,13 @@ k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     double edot[6], w3 = 0, w4 = 0, w5 = 0;
     double T0, T1, T2, T3;
     double edvoldt;
-    {
+    if (TWIN) {
+        edvoldt = D.edvoldt[e];
+        #pragma unroll
+        for (int i = 0; i < 6; ++i) edot[i] = D.strain_rate[size_t(i) * E + e];
+        T0 = D.xT[c.x].w; T1 = D.xT[c.y].w; T2 = D.xT[c.z].w; T3 = D.xT[c.w].w;
+    }
+    else {
         const double4 a0 = ld256_nc(D.xT + c.x), a1 = ld256_nc(D.xT + c.y), a2 = ld256_nc(D.xT + c.z), a3 = ld256_nc(D.xT + c.w);
         const double4 v0 = ld256_nc(D.vv + c.x), v1 = ld256_nc(D.vv + c.y), v2 = ld256_nc(D.vv + c.z), v3 = ld256_nc(D.vv + c.w);
         {

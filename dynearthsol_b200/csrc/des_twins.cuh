@@ -130,7 +130,12 @@ int des_gpu_compute_edvoldt(DesGpu *h)
 int des_gpu_update_stress(DesGpu *h, double dt)
 {
     int rc = twin_ready(h); if (rc) return rc;
-    LAUNCH(KC_TWIN, k_elem_b, h->D.nelem, 128, h->P, h->D, dt, 2);
+    switch (h->hp.rheol_type) {     // E-B itself on the stored strain rate and edvoldt
+    case DES_RH_ELASTIC: LAUNCH(KC_TWIN, (k2_elem_b<false, false, DES_RH_ELASTIC, false, true>), h->D.nelem, 128, h->P, h->D, dt, 0.0, 0, 0); break;
+    case DES_RH_MAXWELL: LAUNCH(KC_TWIN, (k2_elem_b<false, false, DES_RH_MAXWELL, false, true>), h->D.nelem, 128, h->P, h->D, dt, 0.0, 0, 0); break;
+    case DES_RH_EP:      LAUNCH(KC_TWIN, (k2_elem_b<false, false, DES_RH_EP, false, true>), h->D.nelem, 128, h->P, h->D, dt, 0.0, 0, 0); break;
+    default:             LAUNCH(KC_TWIN, (k2_elem_b<false, false, DES_RH_EVP, false, true>), h->D.nelem, 128, h->P, h->D, dt, 0.0, 0, 0); break;
+    }
     CK(cudaGetLastError());
     return DES_OK;
 }
