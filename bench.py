@@ -113,6 +113,7 @@ def build_problem(size, order="reference", verbose=False):
     coord, conn, bcflag = bm.regular_box(xl, yl, zl, nx, ny, nz, order=order)
     sup = core.host_build_support(coord.shape[1], conn)
     mesh = bm.boundary_topology(coord, conn, bcflag, support=sup)
+    mesh["coord"] = coord
     phys = dict(bm.TEST3D_PHYSICS)
     phys["zlength"] = zl
     state, comp_p = bm.initial_fields(coord, conn, rho0=phys["rho0"][0], bulk_modulus=phys["bulk_modulus"][0],

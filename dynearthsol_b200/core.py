@@ -116,7 +116,7 @@ class DesQuality(C.Structure):
 
 # every symbol include/des_gpu.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
-    "des_gpu_create", "des_gpu_create_multi", "des_gpu_partition_info",
+    "des_gpu_create", "des_gpu_create_multi", "des_gpu_partition_info", "des_gpu_set_reorder",
     "des_gpu_destroy", "des_gpu_last_error", "des_gpu_upload_mesh",
     "des_gpu_upload_state", "des_gpu_download_state", "des_gpu_upload_elemmarkers",
     "des_gpu_set_compensation_pressure", "des_gpu_step", "des_gpu_compute_dt",
@@ -154,6 +154,7 @@ def load_library():
     L.des_gpu_create.argtypes = [C.POINTER(DesParam), C.c_int, C.POINTER(H)]
     L.des_gpu_create_multi.argtypes = [C.POINTER(DesParam), C.c_int, _IP, C.POINTER(H)]
     L.des_gpu_partition_info.argtypes = [H, _IP, _DP, _DP, _IP, _IP, _IP]
+    L.des_gpu_set_reorder.argtypes = [H, C.c_int]
     L.des_gpu_destroy.argtypes = [H]
     L.des_gpu_last_error.argtypes = [H]
     L.des_gpu_last_error.restype = C.c_char_p
@@ -504,6 +505,11 @@ class DesGpu:
         if a.size != self.nelem * self.param.nmat:
             raise ValueError("elemmarkers: expected nelem*nmat ints")
         self._ck(self.lib.des_gpu_upload_elemmarkers(self.h, _ptr(a, C.c_int)))
+
+    def set_reorder(self, mode):
+        """0 caller's order, 1 elements by smallest node, 2 Morton (nodes + elements; the mesh
+        dict then needs "coord"); effective at the next upload_mesh."""
+        self._ck(self.lib.des_gpu_set_reorder(self.h, int(mode)))
 
     def partition_info(self):
         n = C.c_int(); ps = C.c_double(); us = C.c_double()

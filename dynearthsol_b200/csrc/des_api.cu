@@ -68,8 +68,16 @@ struct DesGpu {
     // Off by default: measured on B200 it cuts the lines a warp's gathers touch by 40 % but the
     // element kernels gain < 4 % and the node gathers lose 20-30 % (profiles/experiments/)
     bool reorder = false;
+    // DES_REORDER=morton / des_gpu_set_reorder(h, 2): nodes stored in the Morton order of their
+    // coordinates, elements in the Morton order of their centroids (needs DesMesh.coord).  On a
+    // 1.07M-tet tetgen mesh the step is 11 % faster than in the order the reference delivers
+    // (profiles/r02_order_ab_tetgen_1M.json); every array crosses the C-ABI in the caller's order
+    // and each node's support keeps the caller's element order, so no result changes.
+    int reorder_mode = 0;                           // 0 caller's order, 1 elements by smallest node, 2 Morton
     const int *eperm = nullptr, *einv = nullptr;    // device: internal -> caller, caller -> internal
     std::vector<int> h_einv;                        // host copy of einv (empty = identity)
+    const int *nperm = nullptr, *ninv = nullptr;    // the same for nodes
+    std::vector<int> h_ninv;
     int pf_elems = DES_PF_DEFAULT;      // L2 prefetch distance of the element kernels (DES_PF_ELEMS overrides)
     long long launches = 0;
     // staging
@@ -202,6 +210,8 @@ void free_mesh(DesGpu *h)
     h->avg_pending = 0;
     h->eperm = h->einv = nullptr;
     h->h_einv.clear();
+    h->nperm = h->ninv = nullptr;
+    h->h_ninv.clear();
     memset(&h->D, 0, sizeof(h->D));
     h->D.pf = h->pf_elems;
     h->have_mesh = h->have_state = false;
@@ -347,7 +357,7 @@ int build_stress_bcs(DesGpu *h, const DesMesh *m)
         row.assign(m->nnode, -1);
         int r = 0;
         for (auto &kv : rows) {
-            row[kv.first] = r++;
+            row[h->h_ninv.empty() ? kv.first : h->h_ninv[kv.first]] = r++;
             ent.insert(ent.end(), kv.second.begin(), kv.second.end());
             idx.push_back(int(ent.size()));
         }
@@ -581,7 +591,8 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
     DesGpu *h = new DesGpu;
     h->device = device;
     h->hp = *param;
-    if (const char *sv = getenv("DES_ELEM_ORDER")) h->reorder = atoi(sv) != 0;
+    if (const char *sv = getenv("DES_ELEM_ORDER")) h->reorder_mode = atoi(sv) != 0 ? 1 : 0;
+    if (const char *sv = getenv("DES_REORDER")) h->reorder_mode = (!strcmp(sv, "morton") || atoi(sv) == 2) ? 2 : (atoi(sv) == 1 ? 1 : 0);
     if (const char *sv = getenv("DES_DEFER")) {     // bit 1 ddp, 2 surface scale, 4 compute_dt on E-A
         const int v = atoi(sv);
         h->defer_ddp = v & 1; h->defer_scale = (v >> 1) & 1; h->dt_rides = (v >> 2) & 1;
@@ -637,7 +648,66 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     // internal element order: stable counting sort by smallest node index -- consecutive
     // elements then share nodes, so a warp's gathers touch ~40 % fewer 128-byte lines than in
     // the mesh generators' orders (measured: profiles/)
-    if (h->reorder) {
+    h->reorder = h->reorder_mode != 0;
+    if (h->reorder_mode == 2 && !m->coord)
+        return fail(h, DES_E_ARG, "Morton order needs DesMesh.coord");
+    if (h->reorder_mode == 2) {
+        // 21 bits per axis of the bounding box; ties by the caller's id (std::sort on pairs)
+        const double *x = m->coord;
+        double lo[3], hi[3];
+        for (int d = 0; d < 3; ++d) {
+            lo[d] = hi[d] = x[size_t(d) * N];
+            for (int n = 1; n < N; ++n) { lo[d] = std::min(lo[d], x[size_t(d) * N + n]); hi[d] = std::max(hi[d], x[size_t(d) * N + n]); }
+        }
+        auto spread = [](unsigned long long v) {
+            v &= 0x1fffffull;
+            v = (v | (v << 32)) & 0x1f00000000ffffull;
+            v = (v | (v << 16)) & 0x1f0000ff0000ffull;
+            v = (v | (v << 8)) & 0x100f00f00f00f00full;
+            v = (v | (v << 4)) & 0x10c30c30c30c30c3ull;
+            v = (v | (v << 2)) & 0x1249249249249249ull;
+            return v;
+        };
+        auto code = [&](const double p[3]) {
+            unsigned long long q[3];
+            for (int d = 0; d < 3; ++d) {
+                const double w = hi[d] - lo[d];
+                double t = w > 0 ? (p[d] - lo[d]) / w : 0.0;
+                t = std::min(std::max(t, 0.0), 1.0);
+                q[d] = (unsigned long long)(t * 2097151.0);
+            }
+            return spread(q[0]) | (spread(q[1]) << 1) | (spread(q[2]) << 2);
+        };
+        std::vector<std::pair<unsigned long long, int> > kn(N), ke(E);
+        #pragma omp parallel for
+        for (int n = 0; n < N; ++n) {
+            const double p[3] = {x[n], x[size_t(N) + n], x[size_t(2) * N + n]};
+            kn[n] = std::make_pair(code(p), n);
+        }
+        const int *c = m->connectivity;
+        #pragma omp parallel for
+        for (int e = 0; e < E; ++e) {
+            double p[3] = {0, 0, 0};
+            for (int j = 0; j < 4; ++j) {
+                const int n = c[size_t(j) * E + e];
+                for (int d = 0; d < 3; ++d) p[d] += x[size_t(d) * N + n];
+            }
+            for (int d = 0; d < 3; ++d) p[d] /= 4;
+            ke[e] = std::make_pair(code(p), e);
+        }
+        std::sort(kn.begin(), kn.end());
+        std::sort(ke.begin(), ke.end());
+        std::vector<int> nperm(N), eperm(E);
+        h->h_ninv.resize(N); h->h_einv.resize(E);
+        for (int i = 0; i < N; ++i) { nperm[i] = kn[i].second; h->h_ninv[kn[i].second] = i; }
+        for (int i = 0; i < E; ++i) { eperm[i] = ke[i].second; h->h_einv[ke[i].second] = i; }
+        if ((rc = upload_new(h, &h->nperm, nperm.data(), size_t(N), "nperm"))) return rc;
+        if ((rc = upload_new(h, &h->ninv, h->h_ninv.data(), size_t(N), "ninv"))) return rc;
+        if ((rc = upload_new(h, &h->eperm, eperm.data(), size_t(E), "eperm"))) return rc;
+        if ((rc = upload_new(h, &h->einv, h->h_einv.data(), size_t(E), "einv"))) return rc;
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    else if (h->reorder) {
         const int *c = m->connectivity;
         std::vector<int> key(E), start(size_t(N) + 1, 0), perm(E);
         for (int e = 0; e < E; ++e) {
@@ -659,7 +729,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
         int *st = static_cast<int *>(h->stage);
         int4 *conn; if ((rc = dalloc(h, &conn, E, "conn"))) return rc;
         if ((rc = h2d(h, st, m->connectivity, size_t(E) * 4))) return rc;
-        LAUNCH(KC_PACK, k_pack_conn, E, 256, E, st, h->eperm, conn);
+        LAUNCH(KC_PACK, k_pack_conn, E, 256, E, st, h->eperm, h->ninv, conn);
         D.conn = conn;
         CK(cudaStreamSynchronize(h->stream));
     }
@@ -668,9 +738,12 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     {
         std::vector<int> pidx(size_t(N) + 1);
         long long tot = 0;
+        std::vector<int> hn;        // internal -> caller node (host copy of nperm)
+        if (!h->h_ninv.empty()) { hn.resize(N); for (int c = 0; c < N; ++c) hn[h->h_ninv[c]] = c; }
         for (int n = 0; n < N; ++n) {
             pidx[n] = int(tot);
-            tot += (m->support_idx[n + 1] - m->support_idx[n] + 3) & ~3;
+            const int cn = hn.empty() ? n : hn[n];
+            tot += (m->support_idx[cn + 1] - m->support_idx[cn] + 3) & ~3;
             if (tot >= (1ll << 31)) return fail(h, DES_E_ARG, "padded support list overflows int32");
         }
         pidx[N] = int(tot);
@@ -682,11 +755,17 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
         if ((rc = h2d(h, st, m->support_arr, size_t(E) * 4))) return rc;
         if ((rc = h2d(h, st + size_t(E) * 4, m->support_lidx, size_t(E) * 4))) return rc;
         if ((rc = h2d(h, st + size_t(E) * 8, m->support_idx, size_t(N) + 1))) return rc;
-        LAUNCH(KC_PACK, k_pack_support, N, 256, N, st + size_t(E) * 8, D.sup_idx, st, st + size_t(E) * 4, h->einv, ent);
+        LAUNCH(KC_PACK, k_pack_support, N, 256, N, st + size_t(E) * 8, D.sup_idx, st, st + size_t(E) * 4, h->einv, h->nperm, ent);
         D.sup_ent = ent;
         CK(cudaStreamSynchronize(h->stream));
     }
-    if ((rc = upload_new(h, &D.bcflag, m->bcflag, size_t(N), "bcflag"))) return rc;
+    if (h->h_ninv.empty()) { if ((rc = upload_new(h, &D.bcflag, m->bcflag, size_t(N), "bcflag"))) return rc; }
+    else {
+        std::vector<unsigned> bc(N);
+        for (int c = 0; c < N; ++c) bc[h->h_ninv[c]] = m->bcflag[c];
+        if ((rc = upload_new(h, &D.bcflag, bc.data(), size_t(N), "bcflag"))) return rc;
+        CK(cudaStreamSynchronize(h->stream));
+    }
     {
         int *mk; if ((rc = dalloc(h, &mk, size_t(E) * h->hp.nmat, "elemmarkers"))) return rc;
         D.elemmarkers = mk;
@@ -751,7 +830,13 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     }
     // surface
     D.ntop = m->ntop; D.etop = m->etop; D.ntop_elems = m->ntop_elems;
-    if ((rc = upload_new(h, &D.top_nodes, m->top_nodes, size_t(m->ntop)))) return rc;
+    if (h->h_ninv.empty()) { if ((rc = upload_new(h, &D.top_nodes, m->top_nodes, size_t(m->ntop)))) return rc; }
+    else {
+        std::vector<int> tn(m->top_nodes, m->top_nodes + m->ntop);
+        for (int &n : tn) n = h->h_ninv[n];
+        if ((rc = upload_new(h, &D.top_nodes, tn.data(), tn.size()))) return rc;
+        CK(cudaStreamSynchronize(h->stream));
+    }
     {
         std::vector<int> te(m->top_elems, m->top_elems + m->ntop_elems);
         if (!h->h_einv.empty()) for (int &e : te) e = h->h_einv[e];
@@ -778,7 +863,13 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
         if ((rc = upload_new(h, &D.ssup_arr, m->support_surf_arr, size_t(m->support_surf_idx[m->ntop])))) return rc;
     }
     if ((rc = upload_new(h, &D.elem_and_nodes, m->elem_and_nodes, size_t(m->etop) * 3))) return rc;
-    if ((rc = upload_new(h, &D.conn_surf, m->connectivity_surface, size_t(m->etop) * 4))) return rc;
+    if (h->h_ninv.empty()) { if ((rc = upload_new(h, &D.conn_surf, m->connectivity_surface, size_t(m->etop) * 4))) return rc; }
+    else {
+        std::vector<int> cs(size_t(m->etop) * 4, 0);        // conn_t(etop): 3 of 4 columns are written
+        for (size_t k = 0; k < size_t(m->etop) * 3; ++k) cs[k] = h->h_ninv[m->connectivity_surface[k]];
+        if ((rc = upload_new(h, &D.conn_surf, cs.data(), cs.size()))) return rc;
+        CK(cudaStreamSynchronize(h->stream));
+    }
     if ((rc = dalloc(h, &D.dh, m->ntop))) return rc;
     if ((rc = dalloc(h, &D.edvacc_surf, m->etop, "edvacc_surf"))) return rc;
     if ((rc = dalloc(h, &D.s_area, m->etop))) return rc;
@@ -849,24 +940,24 @@ int des_gpu_upload_state(DesGpu *h, const DesState *s)
     // every copy and pack kernel is queued on the stream back to back, each node field through
     // its own slice of the staging buffer; ONE synchronisation at the end (the host arrays are
     // borrowed until the call returns)
-    if ((rc = ensure_stage(h, (N * 10 + (h->eperm ? E * 6 : size_t(0)) + 1) * sizeof(double)))) return rc;
+    if ((rc = ensure_stage(h, (N * 10 + (h->eperm ? std::max(E * 6, N * 3) : size_t(0)) + 1) * sizeof(double)))) return rc;
     double *stn = static_cast<double *>(h->stage);
     double *st = stn + N * 10;      // element rows (internal element order only)
     if (s->coord) {
         if ((rc = h2d(h, stn, s->coord, N * 3))) return rc;
-        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn, D.xT);
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn, h->nperm, D.xT);
     }
     if (s->vel) {
         if ((rc = h2d(h, stn + N * 3, s->vel, N * 3))) return rc;
-        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn + N * 3, D.vv);
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn + N * 3, h->nperm, D.vv);
     }
     if (s->coord0 && h->hp.has_elastic_foundation) {
         if ((rc = h2d(h, stn + N * 6, s->coord0, N * 3))) return rc;
-        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn + N * 6, D.coord0);
+        LAUNCH(KC_PACK, k_pack_vec3, int(N), 256, int(N), stn + N * 6, h->nperm, D.coord0);
     }
     if (s->temperature) {
         if ((rc = h2d(h, stn + N * 9, s->temperature, N))) return rc;
-        LAUNCH(KC_PACK, k_pack_w, int(N), 256, int(N), stn + N * 9, D.xT);
+        LAUNCH(KC_PACK, k_pack_w, int(N), 256, int(N), stn + N * 9, h->nperm, D.xT);
     }
 #define UP(field, dev, n) if (s->field) { if ((rc = h2d(h, dev, (const double *)s->field, n))) return rc; }
     // element fields arrive in the caller's element order and are stored in the internal one
@@ -881,9 +972,16 @@ int des_gpu_upload_state(DesGpu *h, const DesState *s)
     UPE(viscosity, D.viscosity, 1) UPE(dpressure, D.dpressure, 1) UPE(edvoldt, D.edvoldt, 1)
     UPE(radiogenic_source, const_cast<double *>(D.radiogenic), 1)
 #undef UPE
-    UP(force, D.force, N * 3) UP(volume_n, D.volume_n, N) UP(mass, D.mass, N) UP(tmass, D.tmass, N)
+    // node rows: straight copies, or through the staging slice when the nodes are stored in another order
+#define UPN(field, dev, rows) if (s->field) { \
+        if (!h->nperm) { if ((rc = h2d(h, dev, (const double *)s->field, N * (rows)))) return rc; } \
+        else { if ((rc = h2d(h, st, (const double *)s->field, N * (rows)))) return rc; \
+               LAUNCH(KC_PACK, k_rows_to_internal<double>, int(N), 256, int(N), rows, st, h->nperm, dev); \
+               CK(cudaStreamSynchronize(h->stream)); } }
+    UPN(force, D.force, 3) UPN(volume_n, D.volume_n, 1) UPN(mass, D.mass, 1) UPN(tmass, D.tmass, 1)
     if (s->mass && (rc = ymass_update(h))) return rc;       // ymass is not part of DesState: rebuilt with the mass
-    UP(ntmp, D.ntmp, N) UP(dhacc, D.dhacc, N) UP(edvacc_surf, D.edvacc_surf, size_t(D.etop))
+    UPN(ntmp, D.ntmp, 1) UPN(dhacc, D.dhacc, 1) UP(edvacc_surf, D.edvacc_surf, size_t(D.etop))
+#undef UPN
 #undef UP
     CK(cudaStreamSynchronize(h->stream));
     h->have_state = true;
@@ -900,21 +998,21 @@ int des_gpu_download_state(DesGpu *h, const DesState *s)
     if (rc) return rc;
     Dev &D = h->D;
     const size_t N = D.nnode, E = D.nelem;
-    if ((rc = ensure_stage(h, (N * 10 + (h->eperm ? E * 6 : size_t(0)) + 1) * sizeof(double)))) return rc;
+    if ((rc = ensure_stage(h, (N * 10 + (h->eperm ? std::max(E * 6, N * 3) : size_t(0)) + 1) * sizeof(double)))) return rc;
     double *stn = static_cast<double *>(h->stage);
     double *st = stn + N * 10;
 #define DN(dst, src, n) CK(cudaMemcpyAsync(dst, src, (n) * sizeof(double), cudaMemcpyDeviceToHost, h->stream))
     // unpack kernels and copies back to back, one synchronisation at the end
     if (s->coord) {
-        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, stn);
+        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, h->nperm, stn);
         DN(s->coord, stn, N * 3);
     }
     if (s->vel) {
-        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.vv, stn + N * 3);
+        LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.vv, h->nperm, stn + N * 3);
         DN(s->vel, stn + N * 3, N * 3);
     }
     if (s->temperature) {
-        LAUNCH(KC_PACK, k_unpack_w, int(N), 256, int(N), D.xT, stn + N * 9);
+        LAUNCH(KC_PACK, k_unpack_w, int(N), 256, int(N), D.xT, h->nperm, stn + N * 9);
         DN(s->temperature, stn + N * 9, N);
     }
 #define DOWN(field, dev, n) if (s->field) { DN(s->field, dev, n); }
@@ -929,8 +1027,13 @@ int des_gpu_download_state(DesGpu *h, const DesState *s)
     DOWNE(viscosity, D.viscosity, 1) DOWNE(dpressure, D.dpressure, 1) DOWNE(edvoldt, D.edvoldt, 1)
     DOWNE(radiogenic_source, D.radiogenic, 1)
 #undef DOWNE
-    DOWN(force, D.force, N * 3) DOWN(volume_n, D.volume_n, N) DOWN(mass, D.mass, N) DOWN(tmass, D.tmass, N)
-    DOWN(ntmp, D.ntmp, N) DOWN(dhacc, D.dhacc, N) DOWN(edvacc_surf, D.edvacc_surf, size_t(D.etop))
+#define DOWNN(field, dev, rows) if (s->field) { \
+        if (!h->nperm) { DN(s->field, dev, N * (rows)); } \
+        else { LAUNCH(KC_PACK, k_rows_to_caller<double>, int(N), 256, int(N), rows, (const double *)dev, h->ninv, st); \
+               DN(s->field, st, N * (rows)); CK(cudaStreamSynchronize(h->stream)); } }
+    DOWNN(force, D.force, 3) DOWNN(volume_n, D.volume_n, 1) DOWNN(mass, D.mass, 1) DOWNN(tmass, D.tmass, 1)
+    DOWNN(ntmp, D.ntmp, 1) DOWNN(dhacc, D.dhacc, 1) DOWN(edvacc_surf, D.edvacc_surf, size_t(D.etop))
+#undef DOWNN
 #undef DOWN
 #undef DN
     CK(cudaStreamSynchronize(h->stream));
@@ -1079,10 +1182,19 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
     return segment_impl(h, seg, -1, dt, time);
 }
 
+int des_gpu_set_reorder(DesGpu *h, int mode)
+{
+    if (!h || mode < 0 || mode > 2) return DES_E_ARG;
+    h->reorder_mode = mode;     // takes effect at the next des_gpu_upload_mesh
+    return DES_OK;
+}
+
 int des_gpu_set_interior(DesGpu *h, int n_interior)
 {
     if (!h) return DES_E_ARG;
     if (!h->have_mesh) return fail(h, DES_E_STATE, "upload_mesh first");
+    if (h->eperm && n_interior != h->D.nelem)
+        return fail(h, DES_E_UNSUPPORTED, "interior-first element ranges need the caller's element order (reorder off)");
     if (n_interior < 0 || n_interior > h->D.nelem) return fail(h, DES_E_ARG, "n_interior out of range");
     h->n_interior = n_interior;
     return DES_OK;
@@ -1213,7 +1325,7 @@ int des_gpu_mesh_quality(DesGpu *h, const DesQualityParam *qp, DesQuality *out)
     LAUNCH_G(KC_DT, k_quality_elems, nb, 256, 0, h->D, h->eperm, smallest_vol, normf, h->q_partials);
     if (check_bottom || check_sides)
         LAUNCH(KC_DT, k_quality_nodes, h->D.nnode, 256, h->D, -qp->zlength, dist, qp->xlength, qp->ylength,
-               check_bottom, check_sides, h->q_nodes);
+               check_bottom, check_sides, h->nperm, h->q_nodes);
     std::vector<QPartial> part(nb);
     int nodes[2];
     CK(cudaMemcpyAsync(part.data(), h->q_partials, sizeof(QPartial) * nb, cudaMemcpyDeviceToHost, h->stream));
@@ -1231,14 +1343,15 @@ int des_gpu_mesh_quality(DesGpu *h, const DesQualityParam *qp, DesQuality *out)
     out->first_side_node = (nodes[1] >= h->D.nnode) ? -1 : nodes[1];
     out->bottom_value = out->side_value = 0;
     double4 x;
+    auto internal = [&](int cn) { return h->h_ninv.empty() ? cn : h->h_ninv[cn]; };
     if (out->first_bottom_node >= 0) {
-        CK(cudaMemcpy(&x, h->D.xT + out->first_bottom_node, sizeof(x), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&x, h->D.xT + internal(out->first_bottom_node), sizeof(x), cudaMemcpyDeviceToHost));
         out->bottom_value = x.z;
     }
     if (out->first_side_node >= 0) {
         unsigned flag;
-        CK(cudaMemcpy(&x, h->D.xT + out->first_side_node, sizeof(x), cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(&flag, h->D.bcflag + out->first_side_node, sizeof(flag), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&x, h->D.xT + internal(out->first_side_node), sizeof(x), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&flag, h->D.bcflag + internal(out->first_side_node), sizeof(flag), cudaMemcpyDeviceToHost));
         out->side_value = (flag & (BOUNDX0 | BOUNDX1)) ? x.x : x.y;
     }
     return DES_OK;
@@ -1298,7 +1411,7 @@ int des_gpu_average_fields(DesGpu *h, int first)
     }
     if (!first && !h->avg_valid) return fail(h, DES_E_STATE, "average_fields: no snapshot in this interval");
     // coordinates are final for the step (nothing moves them before the next N-C)
-    if (first) LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, h->avg_coord0);
+    if (first) LAUNCH(KC_PACK, k_unpack_vec3, int(N), 256, int(N), D.xT, h->nperm, h->avg_coord0);   // caller's node order
     h->avg_valid = true;
     // average_fields must see the stress AFTER rotate_stress.  With the end-of-step work still
     // deferred, the rotation happens inside the next step's E-B, and the sums ride on it there
@@ -1368,15 +1481,18 @@ int des_gpu_set_halo(DesGpu *h, int nsend, const int *send_nodes, int nrecv, con
         if (recv_nodes[i] < 0 || recv_nodes[i] >= h->D.nnode) return fail(h, DES_E_ARG, "recv node out of range");
     int rc;
     const int *p;
-    if ((rc = upload_new(h, &p, send_nodes, size_t(nsend)))) return rc;
+    std::vector<int> sn(send_nodes, send_nodes + nsend), rn(recv_nodes, recv_nodes + nrecv);
+    if (!h->h_ninv.empty()) { for (int &n : sn) n = h->h_ninv[n]; for (int &n : rn) n = h->h_ninv[n]; }
+    if ((rc = upload_new(h, &p, sn.data(), size_t(nsend)))) return rc;
     h->send_idx = const_cast<int *>(p);
-    if ((rc = upload_new(h, &p, recv_nodes, size_t(nrecv)))) return rc;
+    if ((rc = upload_new(h, &p, rn.data(), size_t(nrecv)))) return rc;
     h->recv_idx = const_cast<int *>(p);
+    CK(cudaStreamSynchronize(h->stream));
     if ((rc = dalloc(h, &h->send_buf, size_t(nsend) * 7, "halo_send"))) return rc;
     if ((rc = dalloc(h, &h->recv_buf, size_t(nrecv) * 7, "halo_recv"))) return rc;
     {
         std::vector<unsigned char> gh(size_t(h->D.nnode), 0);
-        for (int i = 0; i < nrecv; ++i) gh[recv_nodes[i]] = 1;
+        for (int i = 0; i < nrecv; ++i) gh[rn[i]] = 1;
         if ((rc = upload_new(h, &h->D.ghost, gh.data(), gh.size()))) return rc;
         CK(cudaStreamSynchronize(h->stream));
     }

@@ -59,22 +59,24 @@ k_quality_elems(const __grid_constant__ Dev D, const int *perm, double smallest_
 // Boundary-node distortion checks, remeshing.cxx:2778-2838: out[0] = lowest bottom node with
 // |z - bottom| > dist, out[1] = lowest side node (remeshing_option 13; the reference's
 // x0 / x1 / y0 / y1 else-if chain) off its plane by more than dist.  out[] preset to INT_MAX.
+// (ids reported are the caller's: nperm[internal] when the nodes are stored in another order)
 __global__ void k_quality_nodes(const __grid_constant__ Dev D, double bottom, double dist, double xlength,
-                                double ylength, int check_bottom, int check_sides, int *out)
+                                double ylength, int check_bottom, int check_sides, const int *nperm, int *out)
 {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= D.nnode) return;
+    const int cn = nperm ? nperm[n] : n;
     const unsigned flag = D.bcflag[n];
     if (!(flag & (BOUNDX0 | BOUNDX1 | BOUNDY0 | BOUNDY1 | BOUNDZ0))) return;
     const double4 x = D.xT[n];
-    if (check_bottom && (flag & BOUNDZ0) && fabs(x.z - bottom) > dist) atomicMin(out, n);
+    if (check_bottom && (flag & BOUNDZ0) && fabs(x.z - bottom) > dist) atomicMin(out, cn);
     if (check_sides) {
         bool bad = false;
         if (flag & BOUNDX0) bad = fabs(x.x) > dist;
         else if (flag & BOUNDX1) bad = fabs(x.x - xlength) > dist;
         else if (flag & BOUNDY0) bad = fabs(x.y) > dist;
         else if (flag & BOUNDY1) bad = fabs(x.y - ylength) > dist;
-        if (bad) atomicMin(out + 1, n);
+        if (bad) atomicMin(out + 1, cn);
     }
 }
 

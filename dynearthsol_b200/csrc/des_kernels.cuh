@@ -751,20 +751,26 @@ k_dt_final(int n, const DtPartial *__restrict__ partials, DtPartial *__restrict_
 // Internal element order: elements are stored sorted by their smallest
 // node index, perm[internal] = caller's element id, einv = its inverse (both NULL when the
 // caller's order is kept).  Everything element-indexed crosses the C-ABI in the caller's order.
-__global__ void k_pack_conn(int n, const int *soa, const int *perm, int4 *out)
+// ninv (caller's node id -> internal) is NULL when the caller's node order is kept
+__global__ void k_pack_conn(int n, const int *soa, const int *perm, const int *ninv, int4 *out)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
     const size_t o = perm ? perm[e] : e;
-    out[e] = make_int4(soa[o], soa[size_t(n) + o], soa[size_t(2) * n + o], soa[size_t(3) * n + o]);
+    int4 c = make_int4(soa[o], soa[size_t(n) + o], soa[size_t(2) * n + o], soa[size_t(3) * n + o]);
+    if (ninv) c = make_int4(ninv[c.x], ninv[c.y], ninv[c.z], ninv[c.w]);
+    out[e] = c;
 }
 // one thread per node: its support entries -> packed, into the padded list (out pre-filled with -1)
+// (internal node n holds the list of the caller's node nperm[n], entries in the caller's order:
+// the summation order never changes)
 __global__ void k_pack_support(int nnode, const int *idx, const int *pidx, const int *arr, const int *lidx,
-                               const int *einv, int *out)
+                               const int *einv, const int *nperm, int *out)
 {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= nnode) return;
-    const int beg = idx[n], end = idx[n + 1], o = pidx[n] - beg;
+    const int cn = nperm ? nperm[n] : n;
+    const int beg = idx[cn], end = idx[cn + 1], o = pidx[n] - beg;
     for (int k = beg; k < end; ++k) {
         const int e = einv ? einv[arr[k]] : arr[k];
         out[o + k] = (e << 2) | lidx[k];
@@ -796,31 +802,34 @@ __global__ void k_markers_to_internal(int n, int nmat, const int *in, const int 
     const size_t o = perm[i];
     for (int m = 0; m < nmat; ++m) out[size_t(i) * nmat + m] = in[o * nmat + m];
 }
-// which: 0 = xyz from soa, 1 = w from soa[n]
-__global__ void k_pack_vec3(int n, const double *soa, double4 *out)
+// node fields between the caller's SoA and the device records; perm[internal] = caller's node
+// id (NULL: same order)
+__global__ void k_pack_vec3(int n, const double *soa, const int *perm, double4 *out)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const size_t c = perm ? perm[i] : i;
     double4 r = out[i];
-    r.x = soa[i]; r.y = soa[size_t(n) + i]; r.z = soa[size_t(2) * n + i];
+    r.x = soa[c]; r.y = soa[size_t(n) + c]; r.z = soa[size_t(2) * n + c];
     out[i] = r;
 }
-__global__ void k_pack_w(int n, const double *src, double4 *out)
+__global__ void k_pack_w(int n, const double *src, const int *perm, double4 *out)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i].w = src[i];
+    out[i].w = src[perm ? perm[i] : i];
 }
-__global__ void k_unpack_vec3(int n, const double4 *in, double *soa)
+__global__ void k_unpack_vec3(int n, const double4 *in, const int *perm, double *soa)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const size_t c = perm ? perm[i] : i;
     const double4 r = in[i];
-    soa[i] = r.x; soa[size_t(n) + i] = r.y; soa[size_t(2) * n + i] = r.z;
+    soa[c] = r.x; soa[size_t(n) + c] = r.y; soa[size_t(2) * n + c] = r.z;
 }
-__global__ void k_unpack_w(int n, const double4 *in, double *dst)
+__global__ void k_unpack_w(int n, const double4 *in, const int *perm, double *dst)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    dst[i] = in[i].w;
+    dst[perm ? perm[i] : i] = in[i].w;
 }

@@ -169,6 +169,7 @@ int multi_upload_mesh(DesGpu *h, const DesMesh *m, const double *coord)
     std::vector<std::vector<std::vector<int> > > recv_gid(P, std::vector<std::vector<int> >(P));
     struct Local {
         std::vector<int> conn, sidx, sarr, slidx, te, tn, ssidx, ssarr, ean, cs;
+        std::vector<double> coord;
         std::vector<unsigned> bc;
         std::vector<int> bf[DES_NBDRY], bn[DES_NBDRY];
     };
@@ -203,9 +204,11 @@ int multi_upload_mesh(DesGpu *h, const DesMesh *m, const double *coord)
             if (mo == r) p.owned_elems.push_back(le);       // each element reported by exactly one part
         }
         L.bc.resize(Nl);
+        L.coord.resize(size_t(Nl) * 3);
         for (int ln = 0; ln < Nl; ++ln) {
             const int n = p.node_gid[ln];
             L.bc[ln] = m->bcflag[n];
+            for (int d = 0; d < 3; ++d) L.coord[size_t(d) * Nl + ln] = coord[size_t(d) * N + n];
             if (owner[n] == r) p.owned_nodes.push_back(ln);
             else recv_gid[r][owner[n]].push_back(n);
         }
@@ -297,6 +300,8 @@ int multi_upload_mesh(DesGpu *h, const DesMesh *m, const double *coord)
         lm.etop = int(p.facet_gid.size());
         lm.support_surf_idx = L.ssidx.data(); lm.support_surf_arr = L.ssarr.data();
         lm.elem_and_nodes = L.ean.data(); lm.connectivity_surface = L.cs.data();
+        lm.coord = L.coord.data();
+        p.g->reorder_mode = h->reorder_mode;    // each part orders its own nodes and elements
         MCK(p, des_gpu_upload_mesh(p.g, &lm));
         MCK(p, des_gpu_set_halo(p.g, int(p.send_nodes.size()), p.send_nodes.data(),
                                 int(p.recv_nodes.size()), p.recv_nodes.data()));

@@ -48,7 +48,7 @@ def renumber(coord, conn, segment, nperm, eperm):
             np.ascontiguousarray(inv[segment]))
 
 
-def run(coord, conn, segment, segflag, steps):
+def run(coord, conn, segment, segflag, steps, reorder=0):
     N, E = coord.shape[1], conn.shape[1]
     mesh = core.build_topology(coord, conn, segment, segflag)
     xl, yl, zl = [float(coord[d].max() - coord[d].min()) for d in range(3)]
@@ -57,6 +57,8 @@ def run(coord, conn, segment, segflag, steps):
                                       gravity=phys["gravity"], xlength=xl, ylength=yl, zlength=zl,
                                       resolution=(xl * yl * zl / E * 6) ** (1 / 3.0), weakzone=None)
     g = core.DesGpu(core.make_param(**phys), 0)
+    g.set_reorder(reorder)
+    mesh["coord"] = coord
     mesh["bnormals"] = np.zeros(30); mesh["edge_slot"] = np.full(100, -1, dtype=np.int32)
     g.upload_mesh(mesh)
     g.upload_elemmarkers(np.full(E, 4, dtype=np.int32))
@@ -100,6 +102,9 @@ def main():
         c, cn, sg = renumber(coord, conn, segment, npm, epm)
         res["orders"][name] = run(c, cn, sg, segflag, steps)
         print(name, json.dumps(res["orders"][name]), flush=True)
+    # the same, done by the library: the caller keeps the delivered order, des_gpu_set_reorder(h, 2)
+    res["orders"]["delivered, stored in Morton order by the library"] = run(coord, conn, segment, segflag, steps, reorder=2)
+    print("library", json.dumps(res["orders"]["delivered, stored in Morton order by the library"]), flush=True)
     json.dump(res, open(out, "w"), indent=1)
 
 

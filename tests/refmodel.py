@@ -39,12 +39,16 @@ def mesh_from_dump(d):
     m = {"nnode": int(d["p_nnode"]), "nelem": int(d["p_nelem"])}
     for k in MESH_KEYS:
         m[k] = d["mesh_" + k]
+    if "s0_coord" in d:
+        m["coord"] = d["s0_coord"]      # read by a multi-device handle (RCB) and by the Morton storage order
     return m
 
 
-def model_from_dump(d, prefix="s0_", device=0, mesh=None, **override):
+def model_from_dump(d, prefix="s0_", device=0, mesh=None, reorder=None, **override):
     """Create the device model and upload mesh + the state snapshot `prefix`."""
     g = core.DesGpu(param_from_dump(d, **override), device)
+    if reorder is not None:
+        g.set_reorder(reorder)
     g.upload_mesh(mesh if mesh is not None else mesh_from_dump(d))
     g.upload_elemmarkers(d["elemmarkers"])
     g.set_compensation_pressure(float(d["p_compensation_pressure"]))

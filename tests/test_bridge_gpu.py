@@ -95,6 +95,7 @@ def _beyond_conditioning(a, b, frame):
 @pytest.mark.parametrize("cfg,model,frames,nparts", [
     ("t3d-remesh.cfg", "t3dr", 5, 2),       # download (gather by owner) -> host remesh -> re-upload + REPARTITION
     ("orift.cfg", "orift", 4, 3),           # averaged output fields gathered from three parts
+    ("t3d-remesh.cfg", "t3dr", 5, -2),      # the same two parts, each storing its sub-mesh in Morton order
 ])
 def test_driver_over_several_devices_matches_reference_frames(cfg, model, frames, nparts, tmp_path):
     """The same binary with DES_BRIDGE_DEVICES: one handle over several devices (parts share
@@ -103,9 +104,11 @@ def test_driver_over_several_devices_matches_reference_frames(cfg, model, frames
     if not (os.path.exists(REF) and os.path.exists(B200)):
         pytest.skip("reference / bridge binaries not built (need /root/reference at build time)")
     ndev = max(1, torch.cuda.device_count())
+    extra = {"DES_REORDER": "morton"} if nparts < 0 else {}
+    nparts = abs(nparts)
     devices = ",".join(str(i % ndev) for i in range(nparts))
     run(REF, cfg, str(tmp_path / "ref"))
-    out = run(B200, cfg, str(tmp_path / "gpu"), DES_BRIDGE_DEVICES=devices)
+    out = run(B200, cfg, str(tmp_path / "gpu"), DES_BRIDGE_DEVICES=devices, **extra)
     assert "mesh partitioned over %d devices" % nparts in out
     if cfg == "t3d-remesh.cfg":
         assert out.count("mesh partitioned over") == 2 and "host remesh" in out     # initial + after the remesh

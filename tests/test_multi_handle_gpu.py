@@ -17,10 +17,11 @@ FIELDS = ["coord", "vel", "temperature", "stress", "strain", "strain_rate", "pls
           "volume", "volume_old", "force", "mass", "tmass", "volume_n", "dhacc", "edvacc_surf", "viscosity"]
 
 
-def run(d, devices, nsteps=23, device=0, quality=False):
+def run(d, devices, nsteps=23, device=0, quality=False, reorder=0):
     mesh = refmodel.mesh_from_dump(d)
     mesh["coord"] = d["s0_coord"]
     g = core.DesGpu(refmodel.param_from_dump(d), device, devices=devices)
+    g.set_reorder(reorder)
     g.upload_mesh(mesh)
     g.upload_elemmarkers(d["elemmarkers"])
     g.set_compensation_pressure(float(d["p_compensation_pressure"]))
@@ -76,6 +77,23 @@ def test_group_handle_equals_single_device(case, nparts):
     for k in again:
         for f in again[k]:
             assert np.array_equal(again[k][f], many[k][f]), ("run to run", k, f)
+
+
+@pytest.mark.parametrize("case", ["box-ep", "box-evp"])
+def test_morton_storage_order_changes_no_bit(case):
+    """des_gpu_set_reorder(h, 2): nodes and elements stored in Morton order inside the library.
+    Every array crosses the C-ABI in the caller's order and every node's support keeps the
+    caller's element order, so all fields, dt, the marker-step download in the middle of a step
+    and the mesh-quality ids must equal the default order's bit for bit -- on one device, with the
+    elements-by-smallest-node order, and with three parts that each reorder their own sub-mesh."""
+    d = ref_dump(case, [1])
+    one, _, q1 = run(d, None, quality=True)
+    for reorder, devices in ((2, None), (1, None), (2, [0, 0, 0])):
+        got, _, q = run(d, devices, quality=True, reorder=reorder)
+        for k in one:
+            for f in one[k]:
+                assert np.array_equal(one[k][f], got[k][f]), (reorder, devices, k, f)
+        assert q1 == q, (reorder, devices, q1, q)
 
 
 def test_group_handle_refuses_what_it_cannot_do():
