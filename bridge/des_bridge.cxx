@@ -211,6 +211,12 @@ DesBridge *des_bridge_create(const Param &param, const Variables &var, int devic
     int rc = (ndev > 1 || !devs.empty())
         ? des_gpu_create_multi(&b->p, ndev, devs.empty() ? nullptr : devs.data(), &b->h)
         : des_gpu_create(&b->p, device, &b->h);
+    // storage order inside the library: unstructured (tetgen) meshes step ~9 % faster with nodes
+    // and elements in Morton order (profiles/r02_order_ab_tetgen_1M.json); the regular box
+    // generator's own order is better left alone (measured 3 % slower in Morton order at 51M tets).
+    // DES_REORDER in the environment overrides.
+    if (!rc && !std::getenv("DES_REORDER"))
+        des_gpu_set_reorder(b->h, param.mesh.meshing_option == 1 ? 0 : 2);
     if (rc) {
         std::fprintf(stderr, "des_bridge: des_gpu_create failed (code %d): %s\n", rc,
                      b->h ? des_gpu_last_error(b->h) : "no CUDA device");

@@ -31,6 +31,22 @@ struct EvPair { cudaEvent_t a, b; int cls; };
 
 } // namespace
 
+// One captured step (des_gpu_step on small meshes): the host state that selects the launches
+// and their baked-in arguments, the executable graph, and the host state the step leaves.
+struct StepGraph {
+    // key
+    bool tail_pending, nmd_pending, scale_pending, ea_prerun, z1_expired;
+    int avg_pending;
+    const void *volume;         // which of the two volume buffers is current
+    double compensation_pressure;
+    // value
+    cudaGraphExec_t exec;
+    bool seg_tail_mass, seg_rot, post_tail_pending, post_nmd, post_scale, post_surf_ran;
+    int post_avg;
+    long long launches;
+    unsigned long long used;
+};
+
 struct DesMulti;
 struct DesGpu {
     // a group handle (des_gpu_create_multi) owns one ordinary handle per part: des_multi.cuh
@@ -74,6 +90,15 @@ struct DesGpu {
     // (profiles/r02_order_ab_tetgen_1M.json); every array crosses the C-ABI in the caller's order
     // and each node's support keeps the caller's element order, so no result changes.
     int reorder_mode = 0;                           // 0 caller's order, 1 elements by smallest node, 2 Morton
+    // Meshes of up to graph_max_elems elements run des_gpu_step as ONE CUDA Graph launch: at 14 k
+    // tets the 11-16 kernels of a step take ~35 us on the device and ~100 us to launch one by one
+    // (DES_GRAPH=0 turns it off, DES_GRAPH=n sets the element limit).
+    long long graph_max_elems = 2000000;
+    std::vector<StepGraph> graphs;
+    unsigned long long graph_clock = 0;
+    double *sc_dev = nullptr;                       // {dt, dt_rot} read by the captured kernels
+    double sc_host[2] = {0, 0};
+    bool sc_valid = false;
     const int *eperm = nullptr, *einv = nullptr;    // device: internal -> caller, caller -> internal
     std::vector<int> h_einv;                        // host copy of einv (empty = identity)
     const int *nperm = nullptr, *ninv = nullptr;    // the same for nodes
@@ -197,8 +222,17 @@ int upload_new(DesGpu *h, const T **devp, const T *src, size_t n, const char *na
     return rc;
 }
 
+void free_graphs(DesGpu *h)
+{
+    for (StepGraph &g : h->graphs) cudaGraphExecDestroy(g.exec);
+    h->graphs.clear();
+    h->sc_valid = false;
+}
+
 void free_mesh(DesGpu *h)
 {
+    free_graphs(h);
+    h->sc_dev = nullptr;
     for (void *p : h->mesh_allocs) cudaFree(p);
     h->mesh_allocs.clear();
     h->named.clear();
@@ -598,6 +632,7 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
         h->defer_ddp = v & 1; h->defer_scale = (v >> 1) & 1; h->dt_rides = (v >> 2) & 1;
     }
     if (const char *sv = getenv("DES_PF_ELEMS")) h->pf_elems = atoi(sv) > 0 ? atoi(sv) : 0;
+    if (const char *sv = getenv("DES_GRAPH")) h->graph_max_elems = atoll(sv);
     memset(&h->D, 0, sizeof(h->D));
     h->D.pf = h->pf_elems;
     memset(h->kc_ms, 0, sizeof(h->kc_ms));
@@ -803,6 +838,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     D.ca_hi = D.ca + size_t(E) * 4;
     if ((rc = dalloc(h, &D.etmp, E, "etmp"))) return rc;
     if ((rc = dalloc(h, &D.fc, size_t(E) * DES_FC_STRIDE, "fc"))) return rc;
+    if ((rc = dalloc(h, &h->sc_dev, 2, "step_scalars"))) return rc;
     if ((rc = dalloc(h, &D.status, 1, "status"))) return rc;
     CK(cudaMemsetAsync(D.status, 0, sizeof(int), h->stream));
     if ((rc = dalloc(h, &D.ddp, E, "ddp"))) return rc;
@@ -1215,12 +1251,81 @@ int des_gpu_step_segment_part(DesGpu *h, int seg, int part, double dt, double ti
     return rc;
 }
 
+// des_gpu_step as one graph launch.  The six segments are captured once per combination of the
+// host flags that select kernels and baked-in arguments (a handful: steady state x 2 volume
+// buffers, the step after a compute_dt, the first step, averaging on/off); dt and the pending
+// rotation's dt reach the kernels through Dev::sc, refreshed by an 16-byte copy when they change.
+static int step_graphed(DesGpu *h, double dt, double time)
+{
+    CK(cudaSetDevice(h->device));
+    const bool rot = h->tail_pending && (h->hp.rheol_type & DES_RH_ELASTIC);
+    const double sc[2] = {dt, rot ? h->dt_prev : 0.0};
+    if (!h->sc_valid || sc[0] != h->sc_host[0] || sc[1] != h->sc_host[1]) {
+        h->sc_host[0] = sc[0]; h->sc_host[1] = sc[1];
+        // pageable source: the runtime stages it before returning, sc_host may change afterwards
+        CK(cudaMemcpyAsync(h->sc_dev, h->sc_host, sizeof(sc), cudaMemcpyHostToDevice, h->stream));
+        h->sc_valid = true;
+    }
+    const bool z1_expired = time > h->hp.vbc_val_z1_loading_period;
+    StepGraph *g = nullptr;
+    for (StepGraph &c : h->graphs)
+        if (c.tail_pending == h->tail_pending && c.nmd_pending == h->nmd_pending && c.scale_pending == h->scale_pending &&
+            c.ea_prerun == h->ea_prerun && c.z1_expired == z1_expired && c.avg_pending == h->avg_pending &&
+            c.volume == h->D.volume && c.compensation_pressure == h->compensation_pressure) { g = &c; break; }
+    if (!g) {
+        StepGraph n;
+        n.tail_pending = h->tail_pending; n.nmd_pending = h->nmd_pending; n.scale_pending = h->scale_pending;
+        n.ea_prerun = h->ea_prerun; n.z1_expired = z1_expired; n.avg_pending = h->avg_pending;
+        n.volume = h->D.volume; n.compensation_pressure = h->compensation_pressure;
+        const long long l0 = h->launches;
+        h->D.sc = h->sc_dev;
+        CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeRelaxed));
+        int rc = DES_OK;
+        for (int seg = 0; seg < 6 && rc == DES_OK; ++seg) rc = segment_impl(h, seg, -1, dt, time);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+        h->D.sc = nullptr;
+        if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess) return fail(h, DES_E_CUDA, std::string("stream capture: ") + cudaGetErrorString(e));
+        const cudaError_t ei = cudaGraphInstantiate(&n.exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess) return fail(h, DES_E_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ei));
+        n.seg_tail_mass = h->seg_tail_mass; n.seg_rot = h->seg_rot;
+        n.post_tail_pending = h->tail_pending; n.post_nmd = h->nmd_pending; n.post_scale = h->scale_pending;
+        n.post_surf_ran = h->surf_ran; n.post_avg = h->avg_pending;
+        n.launches = h->launches - l0;
+        if (h->graphs.size() >= 16) {       // drop the least recently used
+            size_t lru = 0;
+            for (size_t i = 1; i < h->graphs.size(); ++i) if (h->graphs[i].used < h->graphs[lru].used) lru = i;
+            cudaGraphExecDestroy(h->graphs[lru].exec);
+            h->graphs.erase(h->graphs.begin() + lru);
+        }
+        h->graphs.push_back(n);
+        g = &h->graphs.back();
+        // the capture has already moved the host state to where the step leaves it
+    }
+    else {
+        // what the six segments do to the host state (segment_impl), without enqueuing anything
+        h->seg_tail_mass = g->seg_tail_mass; h->seg_rot = g->seg_rot;
+        h->tail_pending = g->post_tail_pending; h->nmd_pending = g->post_nmd; h->scale_pending = g->post_scale;
+        h->surf_ran = h->surf_ran || g->post_surf_ran; h->avg_pending = g->post_avg;
+        h->ea_prerun = false;
+        if (h->hp.has_moving_mesh) std::swap(h->D.volume, h->D.volume_old);
+        h->dt_prev = dt; h->last_dt = dt;
+        h->launches += g->launches;
+    }
+    g->used = ++h->graph_clock;
+    CK(cudaGraphLaunch(g->exec, h->stream));
+    return DES_OK;
+}
+
 int des_gpu_step(DesGpu *h, double dt, double time, int steps)
 {
     (void)steps;
     if (!h) return DES_E_ARG;
     if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
     if (!(dt > 0)) return fail(h, DES_E_NAN, "dt <= 0");
+    if (!h->multi && !h->timing && h->D.nelem <= h->graph_max_elems) return step_graphed(h, dt, time);
     for (int seg = 0; seg < 6; ++seg) {
         int rc = des_gpu_step_segment(h, seg, dt, time);
         if (rc) return rc;
@@ -1458,6 +1563,7 @@ int des_gpu_set_stream(DesGpu *h, void *stream, int own)
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     drain_events(h);
+    free_graphs(h);     // captured on the old stream
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     if (!own) { h->stream = static_cast<cudaStream_t>(stream); h->own_stream = false; }   // 0 = legacy default stream
     else {
@@ -1475,6 +1581,7 @@ int des_gpu_set_halo(DesGpu *h, int nsend, const int *send_nodes, int nrecv, con
     // des_gpu_halo_buffers must stay valid): one plan per uploaded mesh
     if (h->send_idx || h->recv_idx) return fail(h, DES_E_STATE, "halo already set for this mesh (upload_mesh resets it)");
     CK(cudaSetDevice(h->device));
+    free_graphs(h);     // Dev changes below
     for (int i = 0; i < nsend; ++i)
         if (send_nodes[i] < 0 || send_nodes[i] >= h->D.nnode) return fail(h, DES_E_ARG, "send node out of range");
     for (int i = 0; i < nrecv; ++i)

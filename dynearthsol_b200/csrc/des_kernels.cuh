@@ -82,6 +82,10 @@ struct Dev {
     // bit 0: compute_volume produced a non-positive or NaN volume (reported by the next
     // des_gpu_compute_dt / des_gpu_download_state as DES_E_NAN)
     int *status;
+    // When the step runs as a CUDA Graph (small meshes, des_api.cu: step_graphed) the scalars
+    // that change from step to step are read from here instead of from the baked-in launch
+    // arguments: sc[0] = dt, sc[1] = dt of the step whose rotation is pending.  NULL otherwise.
+    const double *sc;
 };
 
 #define DES_GRID(n, b) (((n) + (b) - 1) / (b))
@@ -503,6 +507,7 @@ __global__ void k_surf_facets(const __grid_constant__ Dev D)
 // (bc.cxx:1772-1781) + max|dh| (bc.cxx:1811-1821)
 __global__ void k_surf_nodes(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt)
 {
+    if (D.sc) dt = D.sc[0];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= D.ntop) return;
     const int n = D.top_nodes[i];

@@ -216,6 +216,7 @@ __global__ void DES_EB_BOUNDS
 k2_elem_b(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, double dt_rot,
           int avg_first = 0, int pre = 0)
 {
+    if (D.sc) { dt = D.sc[0]; dt_rot = D.sc[1]; }
     // pre: what the previous step left for this launch to apply to the stored stress first,
     // in the reference's order -- 1: NMD_stress's diagonal correction ddp[e] (geometry.cxx:
     // 315-331, computed by E-C), 2: correct_surface_element's divisions by rdv for the top
@@ -453,6 +454,7 @@ template <bool MASS>
 __global__ void __launch_bounds__(256)
 k3_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int head_flags)
 {
+    if (D.sc) dt = D.sc[0];
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= D.nnode) return;
     const int beg = D.sup_idx[n], end = D.sup_idx[n + 1];
@@ -501,6 +503,7 @@ k3_node_a(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
 __global__ void __launch_bounds__(256)
 k3_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int bc_z1, int mode)
 {
+    if (D.sc) dt = D.sc[0];
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= D.nnode) return;
     const int N = D.nnode;

@@ -96,9 +96,23 @@ def test_morton_storage_order_changes_no_bit(case):
         assert q1 == q, (reorder, devices, q1, q)
 
 
+def test_graph_launch_equals_kernel_by_kernel_launches(monkeypatch):
+    """Meshes below DES_GRAPH elements (default 2M) run des_gpu_step as one CUDA Graph launch,
+    dt reaching the kernels through device memory.  Same bits as launching kernel by kernel,
+    through the marker step, the compute_dt steps and the steps right after them."""
+    d = ref_dump("box-evp", [1])
+    graphed, _, _ = run(d, None, nsteps=33)
+    monkeypatch.setenv("DES_GRAPH", "0")
+    plain, _, _ = run(d, None, nsteps=33)
+    for k in plain:
+        for f in plain[k]:
+            assert np.array_equal(plain[k][f], graphed[k][f]), (k, f)
+
+
 def test_group_handle_refuses_what_it_cannot_do():
     d = ref_dump("box-ep", [1])
     mesh = refmodel.mesh_from_dump(d)
+    mesh.pop("coord", None)
     g = core.DesGpu(refmodel.param_from_dump(d), devices=[0, 0])
     with pytest.raises(core.DesError) as e:
         g.upload_mesh(mesh)             # no coordinates: nothing to bisect
