@@ -231,6 +231,14 @@ def test_new_entry_points_reject_bad_arguments_and_have_no_cpu_path():
     assert L.des_gpu_step_segment_part(None, 1, 0, 1.0, 0.0, None) == 3
     assert L.des_gpu_isostasy_constrain_velocity(None) == 3
     assert L.des_gpu_check_nan(None, None) == 3
+    assert L.des_gpu_set_reorder(None, 2) == 3
+    assert L.des_gpu_partition_info(None, None, None, None, None, None, None) == 3
+    assert L.des_gpu_create_multi(None, 2, None, None) == 3
+    p = core.make_param()
+    hh = C.c_void_p()
+    assert L.des_gpu_create_multi(C.byref(p), 0, None, C.byref(hh)) == 3          # no devices asked for
+    if not have_gpu():
+        assert L.des_gpu_create_multi(C.byref(p), 2, None, C.byref(hh)) == 1      # no CPU stand-in for a device group
     assert L.des_gpu_build_support(0, 4, 1, None, None, None, None) == 3
     assert L.des_host_boundary_flags(4, 1, None, None, None) == 3
     # out-of-range segment node

@@ -127,3 +127,26 @@ def test_group_handle_refuses_what_it_cannot_do():
     g.close()
     with pytest.raises(core.DesError):
         core.DesGpu(refmodel.param_from_dump(d), devices=[0, 99])
+
+
+def test_non_positive_volume_is_reported():
+    """the step reports NaN / negative volume through its status.  A node
+    pushed through the opposite facet inverts its elements; the next sync point of the
+    asynchronous step loop (des_gpu_compute_dt) returns DES_E_NAN instead of a dt."""
+    d = ref_dump("box-ep", [1])
+    g = refmodel.model_from_dump(d)
+    dt = g.compute_dt()[0]
+    g.step(dt, dt, 1)
+    assert g.compute_dt()[0] > 0
+    N = int(d["p_nnode"])
+    coord = g.download_state("coord")["coord"].reshape(3, N).copy()
+    inner = int(np.argmin(np.abs(coord[0] - coord[0].mean()) + np.abs(coord[1] - coord[1].mean())
+                          + np.abs(coord[2] - coord[2].mean())))
+    coord[2, inner] += 10 * (coord[2].max() - coord[2].min())      # far through its neighbours
+    g.upload_state(coord=coord)
+    g.step(dt, 2 * dt, 2)
+    g.step(dt, 3 * dt, 3)       # the inverted volume is computed by this step's E-A (deferred compute_volume)
+    with pytest.raises(core.DesError) as e:
+        g.compute_dt()
+    assert e.value.code == 11
+    g.close()
