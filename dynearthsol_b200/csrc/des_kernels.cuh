@@ -79,8 +79,9 @@ struct Dev {
     double *ddp;
     const unsigned char *eflag;
     double *escale;
-    // bit 0: compute_volume produced a non-positive or NaN volume (reported by the next
-    // des_gpu_compute_dt / des_gpu_download_state as DES_E_NAN)
+    // bit 0: compute_volume produced a non-positive or NaN volume (the next des_gpu_compute_dt,
+    // the step loop's sync point, returns DES_E_NAN; downloads still work so that the host can
+    // write its error frame)
     int *status;
     // When the step runs as a CUDA Graph (small meshes, des_api.cu: step_graphed) the scalars
     // that change from step to step are read from here instead of from the baked-in launch

@@ -215,7 +215,11 @@ int des_gpu_step(DesGpu *h, double dt, double time, int steps);
  * volume swap (dynearthsol.cxx:466-470), no kernel.
  * des_gpu_step(h, dt, time, steps) == segments 0..5 in order. */
 int des_gpu_step_segment(DesGpu *h, int segment, double dt, double time);
-/* compute_dt (dynearthsol.cxx:643,893; geometry.cxx:1480): device reductions only */
+/* compute_dt (dynearthsol.cxx:643,893; geometry.cxx:1480): device reductions only.  This is the
+ * step loop's sync point (des_gpu_step is asynchronous): it returns DES_E_NAN when a step since
+ * the last upload computed a non-positive or NaN element volume (an inverted or degenerate
+ * tetrahedron: the host then writes its error frame -- downloads still work -- and dies).
+ * The element loop rides on the next step's first kernel, so the call costs no extra pass. */
 int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out);
 /* host scalar algebra of geometry.cxx:1597-1630 (no GPU work); returns dt, <=0 on error */
 double des_dt_from_reductions(const DesParam *param, const DesDtReductions *r,
