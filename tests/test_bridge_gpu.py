@@ -141,3 +141,20 @@ def test_driver_restart_matches_reference_frames(tmp_path):
         b = desframe.read_frame(str(tmp_path / "gpu" / fn))
         worst, report, bad = desframe.compare_frames(a, b)
         assert not bad, "frame %d: %s   [all: %s]" % (k, bad, " ".join(report))
+
+
+def test_bench_driver_mode(tmp_path):
+    """bench.py --driver: the metric through the reference's own driver -- a generated
+    meshing_option = 1 box .cfg, init() on the host with the wrapped topology builders
+    (bridge/des_topology_wrap.cxx), the step loop on the GPU, the reference's "Compute" line."""
+    import json
+    import sys
+    if not os.path.exists(B200):
+        pytest.skip("bridge binary not built")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--driver", "--size", "100k", "--steps", "20"],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-800:]
+    line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert line.get("impl") == "driver" and "unavailable" not in line, line
+    assert line["value"] > 0 and line["steps"] >= 300
+    assert "103680 tets" in line["config"]["workload"]

@@ -18,10 +18,27 @@ REF2D = os.path.join(ROOT, "oracle", "_ref", "dynearthsol2d.ref")
 COMPARE = "/root/reference/benchmarks-cores/compare.py"
 
 
+def write_poly(path, xlength=150e3, zlength=100e3):
+    """The planar straight-line graph test-tiny.cfg meshes (mesh.poly_filename = cube.poly): a
+    rectangle of one region, its four sides flagged x0 / z0 / x1 / z1 (triangle's .poly layout:
+    points, segments with boundary flags, no holes, one region with material 0 and relative
+    size 1)."""
+    pts = [(0.0, 0.0), (0.0, -zlength), (xlength, -zlength), (xlength, 0.0)]
+    flags = [1, 16, 2, 32]      # BOUNDX0, BOUNDZ0, BOUNDX1, BOUNDZ1 (constants.hpp:27-37)
+    with open(path, "w") as f:
+        f.write("4 2 0 0\n")
+        for i, (x, z) in enumerate(pts):
+            f.write("%d %r %r\n" % (i, x, z))
+        f.write("4 1\n")
+        for j in range(4):
+            f.write("%d %d %d %d\n" % (j, j, (j + 1) % 4, flags[j]))
+        f.write("0\n1\n0 %r %r 0 1.0\n" % (xlength / 2, -zlength / 2))
+
+
 def run(wd, threads):
     os.makedirs(wd, exist_ok=True)
-    for f in ("tiny2d.cfg", "cube.poly"):
-        shutil.copy(os.path.join(HERE, "cfg", f), wd)
+    shutil.copy(os.path.join(HERE, "cfg", "tiny2d.cfg"), wd)
+    write_poly(os.path.join(wd, "cube.poly"))
     env = dict(os.environ, OMP_NUM_THREADS=str(threads))
     r = subprocess.run([REF2D, "tiny2d.cfg"], cwd=wd, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-1000:], r.stderr[-1000:])
