@@ -90,6 +90,7 @@ struct DesGpu {
     // (profiles/r02_order_ab_tetgen_1M.json); every array crosses the C-ABI in the caller's order
     // and each node's support keeps the caller's element order, so no result changes.
     int reorder_mode = 0;                           // 0 caller's order, 1 elements by smallest node, 2 Morton
+    bool reorder_from_env = false;                  // asked for by DES_REORDER, not by des_gpu_set_reorder
     // Meshes of up to graph_max_elems elements run des_gpu_step as ONE CUDA Graph launch: at 14 k
     // tets the 11-16 kernels of a step take ~35 us on the device and ~100 us to launch one by one
     // (DES_GRAPH=0 turns it off, DES_GRAPH=n sets the element limit).
@@ -626,7 +627,10 @@ int des_gpu_create(const DesParam *param, int device, DesGpu **out)
     h->device = device;
     h->hp = *param;
     if (const char *sv = getenv("DES_ELEM_ORDER")) h->reorder_mode = atoi(sv) != 0 ? 1 : 0;
-    if (const char *sv = getenv("DES_REORDER")) h->reorder_mode = (!strcmp(sv, "morton") || atoi(sv) == 2) ? 2 : (atoi(sv) == 1 ? 1 : 0);
+    if (const char *sv = getenv("DES_REORDER")) {
+        h->reorder_mode = (!strcmp(sv, "morton") || atoi(sv) == 2) ? 2 : (atoi(sv) == 1 ? 1 : 0);
+        h->reorder_from_env = true;
+    }
     if (const char *sv = getenv("DES_DEFER")) {     // bit 1 ddp, 2 surface scale, 4 compute_dt on E-A
         const int v = atoi(sv);
         h->defer_ddp = v & 1; h->defer_scale = (v >> 1) & 1; h->dt_rides = (v >> 2) & 1;
@@ -683,10 +687,14 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     // internal element order: stable counting sort by smallest node index -- consecutive
     // elements then share nodes, so a warp's gathers touch ~40 % fewer 128-byte lines than in
     // the mesh generators' orders (measured: profiles/)
-    h->reorder = h->reorder_mode != 0;
-    if (h->reorder_mode == 2 && !m->coord)
-        return fail(h, DES_E_ARG, "Morton order needs DesMesh.coord");
-    if (h->reorder_mode == 2) {
+    int mode = h->reorder_mode;
+    if (mode == 2 && !m->coord) {
+        // an explicit request cannot be met; the environment's blanket request just does not apply
+        if (!h->reorder_from_env) return fail(h, DES_E_ARG, "Morton order needs DesMesh.coord");
+        mode = 0;
+    }
+    h->reorder = mode != 0;
+    if (mode == 2) {
         // 21 bits per axis of the bounding box; ties by the caller's id (std::sort on pairs)
         const double *x = m->coord;
         double lo[3], hi[3];
@@ -1145,7 +1153,11 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
         default:             LAUNCH(KC_ELEM_B, (k2_elem_b<S, R, DES_RH_EVP, A>), E, 128, h->P, D, dt, dtr, afirst, pre); break; }
         const bool single = h->hp.nmat == 1;
         // a deferred Output::average_fields rides on the rotation (des_gpu_average_fields)
-        if (!rot && h->avg_pending) { int rc = average_now(h); if (rc) return rc; }
+        if (!rot && h->avg_pending) {
+            // (the sums must see the stress with everything the previous step left applied)
+            int rc = resolve_pending(h); if (rc) return rc;
+            rc = average_now(h); if (rc) return rc;
+        }
         const bool avg = rot && h->avg_pending != 0;
         const int afirst = (h->avg_pending == 2) ? 1 : 0;
         const int pre = (h->nmd_pending ? 1 : 0) | (h->scale_pending ? 2 : 0);
@@ -1194,7 +1206,12 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
             LAUNCH(KC_SURFACE, k_surf_correct_vol, D0.ntop_elems, 128, D0);
             if (D0.ntop_elems > 0) h->scale_pending = true;
         }
-        else LAUNCH(KC_SURFACE, k_surf_correct_elems, D0.ntop_elems, 128, D0);
+        else {
+            // the divisions act on the stress AFTER NMD_stress's correction (reference order): a
+            // diagonal correction still pending for the next E-B has to land first
+            if (h->nmd_pending) { int rc = resolve_pending(h); if (rc) return rc; }
+            LAUNCH(KC_SURFACE, k_surf_correct_elems, D0.ntop_elems, 128, D0);
+        }
     }
     }
     else {
@@ -1222,6 +1239,7 @@ int des_gpu_set_reorder(DesGpu *h, int mode)
 {
     if (!h || mode < 0 || mode > 2) return DES_E_ARG;
     h->reorder_mode = mode;     // takes effect at the next des_gpu_upload_mesh
+    h->reorder_from_env = false;
     return DES_OK;
 }
 

@@ -68,7 +68,10 @@ void rcb_split(const double *cx, const double *cy, const double *cz, std::vector
     const double *c = ax == 0 ? cx : (ax == 1 ? cy : cz);
     const int left = np_ / 2;
     const size_t k = b + size_t(std::llround(double(e - b) * left / np_));
-    std::sort(ids.begin() + b, ids.begin() + e, [c](int x, int y) { return c[x] < c[y] || (c[x] == c[y] && x < y); });
+    // only the split matters: nth_element under the same total order (coordinate, then id)
+    if (k > b && k < e)
+        std::nth_element(ids.begin() + b, ids.begin() + k, ids.begin() + e,
+                         [c](int x, int y) { return c[x] < c[y] || (c[x] == c[y] && x < y); });
     rcb_split(cx, cy, cz, ids, b, k, p0, left, part);
     rcb_split(cx, cy, cz, ids, k, e, p0 + left, np_ - left, part);
 }
