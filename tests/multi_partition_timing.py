@@ -17,6 +17,17 @@ import bench
 from dynearthsol_b200 import core
 
 
+def initial_state(prob):
+    """What init() leaves (dynearthsol.cxx:159-228): boundary velocities applied, nodal mass
+    computed -- done once on a single-device handle (the twins), then uploaded like the
+    reference's own host arrays."""
+    g, dt = bench.make_model(prob, 0)
+    st = dict(prob["state"])
+    st.update(g.download_state("vel", "mass", "tmass", "volume_n", "volume"))
+    g.close()
+    return st
+
+
 def run(prob, devices, nsteps):
     g = core.DesGpu(core.make_param(**prob["phys"]), 0, devices=devices)
     t0 = time.time()
@@ -48,6 +59,7 @@ def main():
     size = sys.argv[2] if len(sys.argv) > 2 else "6M"
     parts = int(sys.argv[3]) if len(sys.argv) > 3 else 4
     prob = bench.build_problem(size)
+    prob["state"] = initial_state(prob)
     ndev = max(1, torch.cuda.device_count())
     a, ia = run(prob, None, 20)
     b, ib = run(prob, [i % ndev for i in range(parts)], 20)
