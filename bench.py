@@ -46,6 +46,9 @@ def alg_bytes(r):
         "elem_a": 16 + 4 + 8 + 8 + 64 + 56 * r,                 # conn, markers, radiogenic, volume W, record W; coord+vel+T
         "node_a": 64 + 32 + 56 * r,                             # record R, CSR; T rw, mass/tmass/volume_n/ntmp W, bcflag, idx
         "elem_b": 16 + 4 + 96 + 96 + 48 + 16 + 8 + 8 + 8 + 8 + 8 * r,  # conn, markers, stress rw, strain rw, strain_rate W, plstrain rw, dpl W, volume R, dpressure W, dp*vol W; ntmp
+        # (SURVEY's count; the schedule also moves, compulsorily under its nodal barriers: the NMD
+        #  scalar handed from E-C to the next E-B, 8 W + 8 R, and E-C's re-read of stress, conn,
+        #  volume, markers -- DESIGN.md section 4: 923 B per element-step instead of 803)
         "node_b": 8 + 32 + 20 * r,                              # dp*vol R, CSR; volume_n, ntmp W, idx
         "elem_c": 8 + 96 + 8 * r,                               # dpressure R, force record W; ntmp
         "node_c": 96 + 32 + 136 * r,                            # force record R, CSR; coord rw, vel rw, force W, mass, bcflag, idx
@@ -452,7 +455,11 @@ def main():
                 "traffic_source": tr["source"] if tr else None,
                 "peak_source": peak_src,
                 "step": {"alg_bytes_per_elem_step": step_alg, "achieved_gbs": value * step_alg / 1e9,
-                         "frac": value * step_alg / 1e9 / peak},
+                         "frac": value * step_alg / 1e9 / peak,
+                         # what a three-phase schedule has to move and what ncu measured
+                         "compulsory_bytes_per_elem_step_under_the_nodal_barriers": step_alg + 120.0,
+                         "frac_on_compulsory_bytes": value * (step_alg + 120.0) / 1e9 / peak,
+                         "dram_bytes_per_elem_step_ncu": tr["dram_bytes_per_elem_step"] if tr and "dram_bytes_per_elem_step" in tr else None},
                 "kernels": per_kernel}
 
     # ---- end to end through the C-ABI with pinned host buffers -------------------------
