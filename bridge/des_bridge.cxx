@@ -68,7 +68,7 @@ void fill_param(DesParam &q, const Param &param, const Variables &var)
     q.vbc_val_lateral[0] = bc.vbc_val_x0_l; q.vbc_val_lateral[1] = bc.vbc_val_x1_l;
     q.vbc_val_lateral[2] = bc.vbc_val_y0_l; q.vbc_val_lateral[3] = bc.vbc_val_y1_l;
     q.vbc_val_z1_loading_period = var.vbc_val_z1_loading_period;
-    for (int i = 0; i < 6; ++i) q.stress_bc_types[i] = var.stress_bc_types[i];
+    for (int i = 0; i < 6; ++i) { q.stress_bc_types[i] = var.stress_bc_types[i]; q.stress_bc_values[i] = var.stress_bc_values[i]; }
     q.max_vbc_val = var.max_vbc_val;
     q.zlength = param.mesh.zlength;
     const Mat &m = param.mat;

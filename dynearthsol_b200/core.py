@@ -56,6 +56,7 @@ class DesParam(C.Structure):
         ("pls0", _MATV), ("pls1", _MATV), ("cohesion0", _MATV), ("cohesion1", _MATV),
         ("friction_angle0", _MATV), ("friction_angle1", _MATV),
         ("dilation_angle0", _MATV), ("dilation_angle1", _MATV), ("porosity", _MATV),
+        ("stress_bc_values", C.c_double * 6),
     ]
 
 
@@ -353,13 +354,13 @@ def make_param(**kw):
             for m in range(nmat):
                 arr[m] = float(a[m])
     for name, n in (("vbc_types", DES_NBDRY), ("vbc_values", DES_NBDRY), ("vbc_val_lateral", 4),
-                    ("stress_bc_types", 6)):
+                    ("stress_bc_types", 6), ("stress_bc_values", 6)):
         if name in kw:
             arr = getattr(p, name)
             for i in range(n):
                 arr[i] = kw[name][i]
     unknown = set(kw) - set(d) - set(MAT_ARRAYS) - {"vbc_types", "vbc_values", "vbc_val_lateral",
-                                                    "stress_bc_types"}
+                                                    "stress_bc_types", "stress_bc_values"}
     if unknown:
         raise TypeError("unknown DesParam fields: %s" % sorted(unknown))
     return p

@@ -273,8 +273,8 @@ int fill_dev_params(DesGpu *h)
     if (p.ref_pressure_option < 0 || p.ref_pressure_option > 2)
         return fail(h, DES_E_UNSUPPORTED, "ref_pressure_option must be 0..2");
     for (int i = 0; i < 6; ++i)
-        if (p.stress_bc_types[i] != 0 && !p.has_body_force_adjustment)
-            return fail(h, DES_E_UNSUPPORTED, "apply_stress_bcs_neumann (stress_bc_*) is not built");
+        if (p.stress_bc_types[i] < 0 || p.stress_bc_types[i] > 3)
+            return fail(h, DES_E_ARG, "stress_bc_types must be 0..3");
 
     P.gravity = p.gravity; P.damping_factor = p.damping_factor;
     P.surf_diff = p.surface_diffusivity; P.surf_base_level = p.surf_base_level;
@@ -299,6 +299,11 @@ int fill_dev_params(DesGpu *h)
     // without gravity (bc.cxx:667): no gravity, no foundation force
     P.has_elastic_foundation = p.has_elastic_foundation && p.gravity != 0;
     P.rheol_type = p.rheol_type; P.nmat = p.nmat; P.mattype_ref = p.mattype_ref;
+    // fields.cxx:690: the prescribed tractions are skipped while the body-force adjustment runs
+    for (int i = 0; i < 6; ++i) {
+        P.stress_bc_types[i] = p.has_body_force_adjustment ? 0 : p.stress_bc_types[i];
+        P.stress_bc_values[i] = p.stress_bc_values[i];
+    }
     int nmemo = 0;
     for (int m = 0; m < p.nmat; ++m) {
         P.rho0[m] = p.rho0[m]; P.alpha[m] = p.alpha[m];
@@ -401,6 +406,52 @@ int build_stress_bcs(DesGpu *h, const DesMesh *m)
     if ((rc = upload_new(h, &D.sbc_idx, idx.data(), idx.size()))) return rc;
     if ((rc = upload_new(h, &D.sbc_ent, ent.data(), ent.size()))) return rc;
     CK(cudaStreamSynchronize(h->stream));   // the std::vectors above die here
+    return DES_OK;
+}
+
+// apply_stress_bcs_neumann (bc.cxx:829-912) is a serial loop: boundaries 0..5 with a traction
+// type, their facets in list order, the three nodes of each facet: `force[node] += ...`.  Per
+// node that is a fixed sequence of additions; the lists below keep it (boundary, then facet).
+int build_neumann_bcs(DesGpu *h, const DesMesh *m)
+{
+    Dev &D = h->D;
+    const int E = m->nelem;
+    std::vector<int> felem, ffacet, fbdry;
+    std::map<int, std::vector<int> > rows;
+    unsigned mask = 0;
+    static const int nof[4][3] = {{1,2,3},{0,3,2},{0,1,3},{0,2,1}};
+    for (int i = 0; i < 6; ++i) {
+        if (h->P.stress_bc_types[i] == 0 || m->nbfacets[i] == 0) continue;
+        mask |= 1u << i;
+        for (int n = 0; n < m->nbfacets[i]; ++n) {
+            const int e = m->bfacets[i][2*n], f = m->bfacets[i][2*n + 1];
+            const int k = int(felem.size());
+            felem.push_back(e); ffacet.push_back(f); fbdry.push_back(i);
+            for (int j = 0; j < 3; ++j) rows[m->connectivity[size_t(nof[f][j]) * E + e]].push_back(k);
+        }
+    }
+    h->P.nbc_mask = mask;
+    D.nnbc_facets = int(felem.size());
+    int rc;
+    if (!h->h_einv.empty()) for (int &e : felem) e = h->h_einv[e];
+    if ((rc = upload_new(h, &D.nbc_felem, felem.data(), felem.size()))) return rc;
+    if ((rc = upload_new(h, &D.nbc_ffacet, ffacet.data(), ffacet.size()))) return rc;
+    if ((rc = upload_new(h, &D.nbc_fbdry, fbdry.data(), fbdry.size()))) return rc;
+    if ((rc = dalloc(h, &D.nbc_ftr, felem.size() * 3))) return rc;
+    std::vector<int> idx(1, 0), ent, row;
+    if (!rows.empty()) {
+        row.assign(m->nnode, -1);
+        int r = 0;
+        for (auto &kv : rows) {
+            row[h->h_ninv.empty() ? kv.first : h->h_ninv[kv.first]] = r++;
+            ent.insert(ent.end(), kv.second.begin(), kv.second.end());
+            idx.push_back(int(ent.size()));
+        }
+    }
+    if ((rc = upload_new(h, &D.nbc_row, row.data(), row.size()))) return rc;
+    if ((rc = upload_new(h, &D.nbc_idx, idx.data(), idx.size()))) return rc;
+    if ((rc = upload_new(h, &D.nbc_ent, ent.data(), ent.size()))) return rc;
+    CK(cudaStreamSynchronize(h->stream));
     return DES_OK;
 }
 
@@ -924,6 +975,7 @@ int des_gpu_upload_mesh(DesGpu *h, const DesMesh *m)
     CK(cudaMemsetAsync(D.maxdh_bits, 0, sizeof(unsigned long long), h->stream));
 
     if ((rc = build_stress_bcs(h, m))) return rc;
+    if ((rc = build_neumann_bcs(h, m))) return rc;
 
     h->dt_blocks = 148 * 32;     // ~40 elements per thread at 51 M tets: enough warps in flight for the gathers (592 blocks: 2.05 ms, measured)
     {
@@ -1186,6 +1238,7 @@ static int segment_impl(DesGpu *h, int seg, int part, double dt, double time)
     }
     if (do_node) {
     LAUNCH(KC_SBC, k_sbc_facets, D0.nsbc_facets, 128, h->P, D0, h->compensation_pressure);
+    LAUNCH(KC_SBC, k_nbc_facets, D0.nnbc_facets, 128, h->P, D0);
     int bc_z1 = h->hp.vbc_types[5];
     if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;     // bc.cxx:344
     LAUNCH(KC_NODE_C, k3_node_c, N, 256, h->P, D0, dt, bc_z1, mm ? 15 : 7);

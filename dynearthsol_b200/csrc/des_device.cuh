@@ -29,6 +29,9 @@ struct DevParams {
     int surface_process_option, ref_pressure_option, has_winkler_foundation, has_water_loading;
     int has_elastic_foundation, rheol_type, nmat, mattype_ref;
     unsigned sbc_mask;              // bcflag bits of boundaries with a live stress bc
+    unsigned nbc_mask;              // bcflag bits of boundaries with a prescribed traction (stress_bc_types)
+    int stress_bc_types[6];         // 1 / 2 / 3: traction along x / y / z (bc.cxx:862-873)
+    double stress_bc_values[6];
     int nmemo;
     double rho0[DES_MAX_MAT], alpha[DES_MAX_MAT];
     double bulk_modulus[DES_MAX_MAT], shear_modulus[DES_MAX_MAT];

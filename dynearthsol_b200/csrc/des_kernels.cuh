@@ -48,6 +48,14 @@ struct Dev {
     double *sbc_ftr;            // [nsbc_facets][9]
     const int *sbc_row;         // [N] row in sbc_idx or -1
     const int *sbc_idx, *sbc_ent;   // CSR over boundary nodes: packed facet*3 + l
+    // prescribed tractions (apply_stress_bcs_neumann, bc.cxx:829-912): the facets of the boundaries
+    // with stress_bc_types != 0 and, per node, the facets it belongs to in the reference's serial
+    // order (boundary, then facet)
+    int nnbc_facets;
+    const int *nbc_felem, *nbc_ffacet, *nbc_fbdry;  // [nnbc_facets]
+    double *nbc_ftr;            // [nnbc_facets][3]
+    const int *nbc_row;         // [N] row in nbc_idx or -1
+    const int *nbc_idx, *nbc_ent;
     // slant-boundary tables for apply_vbcs
     const int *edge_slot;       // [100]
     const double *edge_vec;
@@ -409,11 +417,47 @@ k_sbc_facets(const __grid_constant__ DevParams P, const __grid_constant__ Dev D,
             tmp[j*3 + d] = p * normal[d] / 3;
 }
 
+// apply_stress_bcs_neumann's facet part, bc.cxx:844-885: what every node of facet n receives
+__global__ void __launch_bounds__(128)
+k_nbc_facets(const __grid_constant__ DevParams P, const __grid_constant__ Dev D)
+{
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= D.nnbc_facets) return;
+    const int e = D.nbc_felem[n], f = D.nbc_ffacet[n], ib = D.nbc_fbdry[n];
+    const int4 c4 = D.conn[e];
+    const int cn[4] = {c4.x, c4.y, c4.z, c4.w};
+    const double4 p0 = D.xT[cn[c_node_of_facet[f][0]]];
+    const double4 p1 = D.xT[cn[c_node_of_facet[f][1]]];
+    const double4 p2 = D.xT[cn[c_node_of_facet[f][2]]];
+    // normal_vector_of_facet, bc.cxx:24-40
+    const double v01[3] = {p1.x - p0.x, p1.y - p0.y, p1.z - p0.z};
+    const double v02[3] = {p2.x - p0.x, p2.y - p0.y, p2.z - p0.z};
+    double normal[3];
+    normal[0] = (v01[1] * v02[2] - v01[2] * v02[1]) / 2;
+    normal[1] = (v01[2] * v02[0] - v01[0] * v02[2]) / 2;
+    normal[2] = (v01[0] * v02[1] - v01[1] * v02[0]) / 2;
+    double traction[3] = {0.0, 0.0, 0.0};
+    traction[P.stress_bc_types[ib] - 1] = P.stress_bc_values[ib];
+    for (int d = 0; d < 3; ++d) D.nbc_ftr[size_t(n) * 3 + d] = traction[d] * normal[d] / 3;
+}
+
 // ---------------------------------------------------------------------------------------
 // N-C: update_force node loop (fields.cxx:658-676), apply_stress_bcs node loops
 // (bc.cxx:783-823), apply_damping (fields.cxx:483-579), update_velocity (:734-737),
 // apply_vbcs (bc.cxx:396-651), update_coordinate (fields.cxx:774-778)
 // ---------------------------------------------------------------------------------------
+// apply_stress_bcs_neumann's node part (bc.cxx:888-900) for one node: its facets in the
+// reference's order, `force += traction * normal / 3` component by component
+__device__ __forceinline__ void nbc_node(const Dev &D, int n, double f[3])
+{
+    const int row = D.nbc_row[n];
+    if (row < 0) return;
+    for (int q = D.nbc_idx[row]; q < D.nbc_idx[row + 1]; ++q) {
+        const double *tr = D.nbc_ftr + size_t(D.nbc_ent[q]) * 3;
+        f[0] += tr[0]; f[1] += tr[1]; f[2] += tr[2];
+    }
+}
+
 __global__ void __launch_bounds__(256)
 k_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, double dt, int bc_z1,
          int mode)
@@ -448,6 +492,7 @@ k_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, dou
         }
         if (P.has_elastic_foundation && (flag & BOUNDZ0))
             f[2] -= P.elastic_foundation_constant * (x.z - D.coord0[n].z);
+        if (flag & P.nbc_mask) nbc_node(D, n, f);
         const double crit = (P.damping_option == 4) ? 2.0 * sqrt(D.mass[n] * D.ymass[n]) : 0.0;
         #pragma unroll
         for (int j = 0; j < 3; ++j) {

@@ -558,6 +558,7 @@ k3_node_c(const __grid_constant__ DevParams P, const __grid_constant__ Dev D, do
     }
     if (P.has_elastic_foundation && (flag & BOUNDZ0))
         f[2] -= P.elastic_foundation_constant * (x.z - D.coord0[n].z);
+    if (flag & P.nbc_mask) nbc_node(D, n, f);
     const double crit = (P.damping_option == 4) ? 2.0 * sqrt(D.mass[n] * D.ymass[n]) : 0.0;
     #pragma unroll
     for (int j = 0; j < 3; ++j) {

@@ -154,6 +154,7 @@ int des_gpu_update_force(DesGpu *h)
 {
     int rc = twin_ready(h); if (rc) return rc;
     LAUNCH(KC_TWIN, k_sbc_facets, h->D.nsbc_facets, 128, h->P, h->D, h->compensation_pressure);
+    LAUNCH(KC_TWIN, k_nbc_facets, h->D.nnbc_facets, 128, h->P, h->D);
     LAUNCH_M(KC_TWIN, k_elem_c, false, h->D.nelem, 256, h->P, h->D, 0);
     LAUNCH(KC_TWIN, k_node_c, h->D.nnode, 256, h->P, h->D, 0.0, 0, 1);
     CK(cudaGetLastError());

@@ -72,7 +72,8 @@ typedef struct DesParam {
     double vbc_values[DES_NBDRY];   /* var.vbc_values */
     double vbc_val_lateral[4];      /* bc.vbc_val_{x0,x1,y0,y1}_l (type 6) */
     double vbc_val_z1_loading_period;
-    int stress_bc_types[6];         /* must be all 0 (neumann path: DES_E_UNSUPPORTED) */
+    int stress_bc_types[6];         /* var.stress_bc_types (dynearthsol.cxx:110-115): 0 none, 1 / 2 / 3 = traction along
+                                     * x / y / z on that boundary -- apply_stress_bcs_neumann, bc.cxx:829-912 */
     double max_vbc_val;             /* var.max_vbc_val (find_max_vbc, bc.cxx:66-91) */
     /* mesh */
     double zlength;                 /* mesh.zlength (Winkler datum) */
@@ -91,6 +92,7 @@ typedef struct DesParam {
     double friction_angle0[DES_MAX_MAT], friction_angle1[DES_MAX_MAT];
     double dilation_angle0[DES_MAX_MAT], dilation_angle1[DES_MAX_MAT];
     double porosity[DES_MAX_MAT];
+    double stress_bc_values[6];     /* var.stress_bc_values (dynearthsol.cxx:117-122) */
 } DesParam;
 
 /* Topology produced by the reference's host mesh code (mesh.cxx), immutable between

@@ -16,7 +16,7 @@ from refharness import Ref  # noqa: E402
 MESH_ARRAYS = ["connectivity", "bcflag", "support_idx", "support_arr", "support_lidx", "bnormals",
                "edge_vec", "edge_slot", "top_elems", "top_nodes", "support_surf_idx",
                "support_surf_arr", "elem_and_nodes", "connectivity_surface", "vbc_types",
-               "vbc_values", "stress_bc_types", "segment", "segflag"] + \
+               "vbc_values", "stress_bc_types", "stress_bc_values", "segment", "segflag"] + \
               ["bfacets%d" % i for i in range(10)] + ["bnodes%d" % i for i in range(10)]
 STATE_ARRAYS = ["coord", "vel", "coord0", "temperature", "stress", "strain", "strain_rate",
                 "plstrain", "delta_plstrain", "volume", "volume_old", "viscosity", "dpressure",

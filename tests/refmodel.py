@@ -31,6 +31,8 @@ def param_from_dump(d, **override):
     kw["vbc_values"] = [float(x) for x in d["mesh_vbc_values"]]
     kw["vbc_val_lateral"] = [float(d["p_vbc_val_%s_l" % s]) for s in ("x0", "x1", "y0", "y1")]
     kw["stress_bc_types"] = [int(x) for x in d["mesh_stress_bc_types"]]
+    if "mesh_stress_bc_values" in d:
+        kw["stress_bc_values"] = [float(x) for x in d["mesh_stress_bc_values"]]
     kw.update(override)
     return core.make_param(**kw)
 

@@ -48,6 +48,12 @@ VARIANTS = {
     "vbc-z2-z3-loading-period": ({"bc.has_winkler_foundation": "no", "bc.vbc_z0": 2, "bc.vbc_z1": 3,
                                   "bc.vbc_val_z1": "-2e-11", "bc.vbc_val_z1_loading_period": "5e8"},
                                  "z1 bc switched off after ~8.7 steps (bc.cxx:346)"),
+    # apply_stress_bcs_neumann (bc.cxx:829-912): prescribed tractions along x / y / z on four boundaries
+    "neumann-tractions": ({"bc.stress_bc_x1": 1, "bc.stress_val_x1": "2e7", "bc.stress_bc_y0": 2,
+                           "bc.stress_val_y0": "-1e7", "bc.stress_bc_z1": 3, "bc.stress_val_z1": "3e6",
+                           "bc.stress_bc_x0": 3, "bc.stress_val_x0": "1e6",
+                           "bc.vbc_x1": 0, "bc.vbc_y0": 0},
+                          "force += traction * normal / 3 on the facet nodes, serial boundary / facet order"),
     # control switches
     "no-thermal-diffusion": ({"control.has_thermal_diffusion": "no"}, "tmass = 0 quirk (geometry.cxx:1836)"),
     "not-quasi-static": ({"control.is_quasi_static": "no"}, "true density in compute_mass, elastic dt"),
@@ -78,7 +84,7 @@ def test_cfg_variant(name):
 def test_variants_reach_their_branch():
     """The variants are not no-ops: each moves the reference's result away from the base run."""
     base = ref_dump("box-ep", [1, 20])
-    for name in ("water-loading", "elastic-foundation", "elastic-foundation-no-gravity",
+    for name in ("water-loading", "elastic-foundation", "elastic-foundation-no-gravity", "neumann-tractions",
                  "lithostatic-walls-refp0", "vbc-3-5-7-2-z1-z2", "not-quasi-static", "fixed-mesh"):
         d = ref_dump("box-ep", [1, 20], over=VARIANTS[name][0])
         assert not np.array_equal(d["s20_force"], base["s20_force"]), name
