@@ -1,5 +1,6 @@
 // See des_bridge.hpp.  Compiled with the reference's flags (-DTHREED -DSOA) against its headers.
 #include <cstdio>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <algorithm>
@@ -12,6 +13,7 @@
 #include "matprops.hpp"
 #include "markerset.hpp"
 #include "output.hpp"
+#include "remeshing.hpp"
 #include "utils.hpp"
 #include "des_bridge.hpp"
 
@@ -261,6 +263,114 @@ int des_bridge_step(DesBridge *b, const Param &param, Variables &var)
     if ((rc = des_gpu_upload_state(b->h, &s))) return fail(b, rc, "upload_state");
     if ((rc = des_bridge_markers_changed(b, param, var))) return rc;
     if ((rc = des_gpu_step_segment(b->h, 5, var.dt, var.time))) return fail(b, rc, "step_segment");
+    return 0;
+}
+
+// ---- control.has_PT: the step as the reference's un-fused call sequence (the twins) -----------
+namespace {
+
+#define TW(call) do { int rc_ = (call); if (rc_) return fail(b, rc_, #call); } while (0)
+
+// the surface-marker work surface_processes() does on the host on quality-check steps
+// (bc.cxx:1829-1843), between the two halves of update_mesh
+int marker_interlude(DesBridge *b, const Param &param, Variables &var)
+{
+    DesState s;
+    std::memset(&s, 0, sizeof(s));
+    s.coord = var.coord->data();
+    s.volume = var.volume->data();
+    s.dhacc = var.surfinfo.dhacc->data();
+    s.edvacc_surf = var.surfinfo.edvacc_surf->data();
+    TW(des_gpu_download_state(b->h, &s));
+    var.markersets[0]->correct_surface_marker(param, var, *var.surfinfo.dhacc, *var.elemmarkers,
+                                              *var.markers_in_elem);
+    for (int i = 0; i < var.surfinfo.ntop; i++)
+        (*var.surfinfo.dhacc)[(*var.surfinfo.top_nodes)[i]] = 0.;
+    var.markersets[0]->set_surface_marker(param, var, param.mesh.smallest_size, param.mat.mattype_sed,
+                                          *var.surfinfo.edvacc_surf, *var.elemmarkers, *var.markers_in_elem);
+    std::memset(&s, 0, sizeof(s));
+    s.dhacc = var.surfinfo.dhacc->data();
+    s.edvacc_surf = var.surfinfo.edvacc_surf->data();
+    TW(des_gpu_upload_state(b->h, &s));
+    return des_bridge_markers_changed(b, param, var);
+}
+
+// the body both pseudo-transient loops share (dynearthsol.cxx:562-584 and 812-860)
+int pt_iterations(DesBridge *b, Param &param, Variables &var, double &residual_old, bool with_remesh)
+{
+    TW(des_gpu_set_pt_jump(b->h, 1));
+    param.control.PT_jump = true;
+    for (int pt_step = 0; pt_step < param.control.PT_max_iter; ++pt_step) {
+        TW(des_gpu_apply_vbcs(b->h, var.time));
+        if (param.control.has_moving_mesh) TW(des_gpu_update_mesh(b->h, var.dt));
+        TW(des_gpu_update_strain_rate(b->h));
+        TW(des_gpu_compute_dvoldt(b->h));
+        TW(des_gpu_compute_edvoldt(b->h));
+        TW(des_gpu_update_stress(b->h, var.dt));
+        TW(des_gpu_update_force(b->h));
+        TW(des_gpu_update_velocity(b->h, var.dt));
+        TW(des_gpu_residual_force(b->h, &var.l2_residual));
+        const double relative_change = std::fabs((var.l2_residual - residual_old) / residual_old);
+        if (relative_change < param.control.PT_relative_tolerance) break;
+        residual_old = var.l2_residual;
+        if (with_remesh && pt_step % param.mesh.quality_check_step_interval == 0 && param.control.has_moving_mesh) {
+            int index; double min_quality;
+            const int bad = des_bridge_bad_mesh_quality(b, param, var, index, min_quality);
+            if (bad < 0) return 1;
+            if (bad) {
+                if (des_bridge_download(b, var, DES_DL_ALL)) return 1;
+                if (param.sim.has_output_during_remeshing) var.output->write_exact(var);
+                remesh(param, var, bad);
+                if (des_bridge_upload(b, param, var)) return 1;
+                TW(des_gpu_set_pt_jump(b->h, 1));
+                if (param.sim.has_output_during_remeshing) var.output->write_exact(var);
+            }
+        }
+    }
+    param.control.PT_jump = false;
+    TW(des_gpu_set_pt_jump(b->h, 0));
+    return 0;
+}
+
+} // namespace
+
+int des_bridge_step_pt(DesBridge *b, Param &param, Variables &var)
+{
+    // dynearthsol.cxx:776-876 (no hydraulics): every call goes to its fine-grained twin
+    if (param.control.has_thermal_diffusion) TW(des_gpu_update_temperature(b->h, var.dt));
+    TW(des_gpu_update_strain_rate(b->h));
+    TW(des_gpu_compute_dvoldt(b->h));
+    TW(des_gpu_compute_edvoldt(b->h));
+    TW(des_gpu_update_stress(b->h, var.dt));
+    if (param.control.is_using_mixed_stress) TW(des_gpu_nmd_stress(b->h));
+    TW(des_gpu_update_force(b->h));
+    TW(des_gpu_update_velocity(b->h, var.dt));
+    TW(des_gpu_residual_force(b->h, &var.l2_residual));
+    double residual_old = var.l2_residual;
+    if (param.control.has_PT) { int rc = pt_iterations(b, param, var, residual_old, true); if (rc) return rc; }
+    TW(des_gpu_apply_vbcs(b->h, var.time));
+    if (param.control.has_moving_mesh) {
+        const bool marker_step = var.steps != 0 && var.steps % param.mesh.quality_check_step_interval == 0;
+        if (!marker_step) TW(des_gpu_update_mesh(b->h, var.dt));
+        else {
+            TW(des_gpu_update_mesh_part(b->h, var.dt, 0));
+            int rc = marker_interlude(b, param, var); if (rc) return rc;
+            TW(des_gpu_update_mesh_part(b->h, var.dt, 1));
+        }
+    }
+    if (param.mat.rheol_type & MatProps::rh_elastic) TW(des_gpu_rotate_stress(b->h, var.dt));
+    return 0;
+}
+
+int des_bridge_initial_body_force_adjustment(DesBridge *b, Param &param, Variables &var)
+{
+    // dynearthsol.cxx:546-591, 753-761: "only works with the PT loop"; the prescribed tractions
+    // stay off until it is done (fields.cxx:690)
+    TW(des_gpu_residual_force(b->h, &var.l2_residual));
+    double residual_old = var.l2_residual;
+    if (param.control.has_PT) { int rc = pt_iterations(b, param, var, residual_old, false); if (rc) return rc; }
+    param.ic.has_body_force_adjustment = false;
+    TW(des_gpu_set_body_force_adjustment(b->h, 0));
     return 0;
 }
 

@@ -28,6 +28,12 @@ int des_bridge_upload(DesBridge *b, const Param &param, const Variables &var);
 // the block dynearthsol.cxx:776-876 (refresh_elem_cache ... rotate_stress); var.steps,
 // var.time already incremented by the caller as in the reference (:773-774)
 int des_bridge_step(DesBridge *b, const Param &param, Variables &var);
+// control.has_PT: the same block as the reference's un-fused call sequence through the fine-grained
+// twins, with the pseudo-transient loop (dynearthsol.cxx:803-864) between update_velocity and
+// apply_vbcs; sets var.l2_residual.  (param is not const: the loop toggles control.PT_jump.)
+int des_bridge_step_pt(DesBridge *b, Param &param, Variables &var);
+// initial_body_force_adjustment (dynearthsol.cxx:546-591, 753-761), before the step loop
+int des_bridge_initial_body_force_adjustment(DesBridge *b, Param &param, Variables &var);
 // compute_dt (dynearthsol.cxx:893): device reductions + the reference's scalar algebra;
 // also sets var.max_global_vel_mag, var.global_dt_min, var.surfinfo.max_surf_vel
 double des_bridge_compute_dt(DesBridge *b, const Param &param, Variables &var);

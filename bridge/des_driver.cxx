@@ -4,7 +4,7 @@
 // parsing, init(), mesh generation, markers, phase changes, remeshing, output.
 //
 // main() below follows dynearthsol.cxx:593-1030 for the configurations in scope (isostasy
-// spin-up and restart included; no GoSPL, PT loop, hydraulics, rate-and-state/ATS, monitor): the statements that remain are
+// spin-up, restart and the pseudo-transient loop included; no GoSPL, hydraulics, rate-and-state/ATS, monitor): the statements that remain are
 // the reference's own calls; the lines marked [B200] are the swaps INTEGRATION.md lists.
 #include <cstdio>
 #include <cstdlib>
@@ -44,10 +44,8 @@ int main(int argc, const char* argv[])
     }
     Param param;
     get_input_parameters(argv[1], param);
-    if (param.control.has_PT) return unsupported("control.has_PT");
     if (param.control.has_hydraulic_diffusion) return unsupported("control.has_hydraulic_diffusion");
     if (param.control.use_global_velocity_scaling) return unsupported("control.use_global_velocity_scaling");
-    if (param.ic.has_body_force_adjustment) return unsupported("ic.has_body_force_adjustment");
 
     static Variables var;
     init_var(param, var);
@@ -92,6 +90,11 @@ int main(int argc, const char* argv[])
     const double starting_step = var.steps;
     int next_regular_frame = 1;
 
+    if (param.ic.has_body_force_adjustment) {
+        // [B200] initial_body_force_adjustment(param, var);   (dynearthsol.cxx:753-761)
+        if (des_bridge_initial_body_force_adjustment(gpu, param, var)) return 1;
+    }
+
     std::cout << "Starting simulation (explicit core on the GPU)...\n";
     do {
         var.steps ++;
@@ -99,7 +102,9 @@ int main(int argc, const char* argv[])
         // [B200] dynearthsol.cxx:776-876: refresh_elem_cache, update_temperature,
         // update_strain_rate, compute_dvoldt, compute_edvoldt, update_stress, NMD_stress,
         // update_force, update_velocity, apply_vbcs, update_mesh, rotate_stress
-        if (des_bridge_step(gpu, param, var)) return 1;
+        // (with control.has_PT the block runs as the reference's own call sequence through the
+        // fine-grained twins, the pseudo-transient loop of dynearthsol.cxx:803-864 in the middle)
+        if (param.control.has_PT ? des_bridge_step_pt(gpu, param, var) : des_bridge_step(gpu, param, var)) return 1;
 
         const int slow_updates_interval = 10;
         if (var.steps % slow_updates_interval == 0) {

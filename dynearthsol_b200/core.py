@@ -125,7 +125,8 @@ ABI_SYMBOLS = [
     "des_gpu_update_temperature", "des_gpu_update_strain_rate", "des_gpu_compute_dvoldt",
     "des_gpu_compute_edvoldt", "des_gpu_update_stress", "des_gpu_nmd_stress",
     "des_gpu_update_force", "des_gpu_update_velocity", "des_gpu_apply_vbcs",
-    "des_gpu_update_mesh", "des_gpu_compute_volume", "des_gpu_compute_mass",
+    "des_gpu_update_mesh", "des_gpu_update_mesh_part", "des_gpu_set_pt_jump",
+    "des_gpu_set_body_force_adjustment", "des_gpu_compute_volume", "des_gpu_compute_mass",
     "des_gpu_rotate_stress", "des_gpu_residual_force", "des_gpu_isostasy_constrain_velocity",
     "des_gpu_launch_count", "des_gpu_enable_kernel_timing", "des_gpu_kernel_time",
     "des_gpu_device_ptr", "des_host_build_support", "des_abi_sizeof",
@@ -176,6 +177,9 @@ def load_library():
               "compute_volume", "compute_mass", "isostasy_constrain_velocity"]:
         getattr(L, "des_gpu_" + f).argtypes = [H]
     L.des_gpu_residual_force.argtypes = [H, _DP]
+    L.des_gpu_update_mesh_part.argtypes = [H, C.c_double, C.c_int]
+    L.des_gpu_set_pt_jump.argtypes = [H, C.c_int]
+    L.des_gpu_set_body_force_adjustment.argtypes = [H, C.c_int]
     L.des_gpu_launch_count.argtypes = [H]
     L.des_gpu_launch_count.restype = C.c_longlong
     L.des_gpu_enable_kernel_timing.argtypes = [H, C.c_int]

@@ -111,6 +111,9 @@ struct DesGpu {
     DtPartial *dt_partials = nullptr; int dt_blocks = 0;
     size_t dt_cap = 0;                  // partials the buffer holds; slot [dt_cap] takes k_dt_final's result
     // work of the step that ended which the next E-B applies first (resolve_pending otherwise):
+    // driver states of the pseudo-transient loop (dynearthsol.cxx:803-864, 546-591)
+    bool pt_jump = false;               // param.control.PT_jump: face velocity values held at 0, no surface processes
+    unsigned nbc_mask_full = 0;         // P.nbc_mask when the prescribed tractions are live
     bool nmd_pending = false;           // stress diagonal += ddp[e]       (E-C stored the scalar)
     bool scale_pending = false;         // top elements: stress, strain, plstrain /= rdv (k_surf_correct_vol)
     bool ea_prerun = false;             // des_gpu_compute_dt already ran the next step's E-A (with the dt reductions)
@@ -299,9 +302,8 @@ int fill_dev_params(DesGpu *h)
     // without gravity (bc.cxx:667): no gravity, no foundation force
     P.has_elastic_foundation = p.has_elastic_foundation && p.gravity != 0;
     P.rheol_type = p.rheol_type; P.nmat = p.nmat; P.mattype_ref = p.mattype_ref;
-    // fields.cxx:690: the prescribed tractions are skipped while the body-force adjustment runs
     for (int i = 0; i < 6; ++i) {
-        P.stress_bc_types[i] = p.has_body_force_adjustment ? 0 : p.stress_bc_types[i];
+        P.stress_bc_types[i] = p.stress_bc_types[i];
         P.stress_bc_values[i] = p.stress_bc_values[i];
     }
     int nmemo = 0;
@@ -430,7 +432,10 @@ int build_neumann_bcs(DesGpu *h, const DesMesh *m)
             for (int j = 0; j < 3; ++j) rows[m->connectivity[size_t(nof[f][j]) * E + e]].push_back(k);
         }
     }
-    h->P.nbc_mask = mask;
+    // fields.cxx:690: the prescribed tractions are skipped while the body-force adjustment runs
+    // (des_gpu_set_body_force_adjustment flips it back)
+    h->nbc_mask_full = mask;
+    h->P.nbc_mask = h->hp.has_body_force_adjustment ? 0u : mask;
     D.nnbc_facets = int(felem.size());
     int rc;
     if (!h->h_einv.empty()) for (int &e : felem) e = h->h_einv[e];
@@ -1286,6 +1291,24 @@ int des_gpu_step_segment(DesGpu *h, int seg, double dt, double time)
     if (h->multi) return multi_step_segment(h, seg, dt, time);
     CK(cudaSetDevice(h->device));
     return segment_impl(h, seg, -1, dt, time);
+}
+
+int des_gpu_set_pt_jump(DesGpu *h, int on)
+{
+    if (!h) return DES_E_ARG;
+    if (h->multi) return fail(h, DES_E_UNSUPPORTED, "the pseudo-transient loop runs on a single-device handle");
+    h->pt_jump = on != 0;
+    return DES_OK;
+}
+
+int des_gpu_set_body_force_adjustment(DesGpu *h, int on)
+{
+    if (!h) return DES_E_ARG;
+    if (h->multi) return fail(h, DES_E_UNSUPPORTED, "the body-force adjustment runs on a single-device handle");
+    h->hp.has_body_force_adjustment = on != 0;
+    h->P.nbc_mask = on ? 0u : h->nbc_mask_full;
+    free_graphs(h);     // P is baked into captured launches
+    return DES_OK;
 }
 
 int des_gpu_set_reorder(DesGpu *h, int mode)

@@ -174,25 +174,41 @@ int des_gpu_apply_vbcs(DesGpu *h, double time)
     int rc = twin_ready(h); if (rc) return rc;
     int bc_z1 = h->hp.vbc_types[5];
     if (time > h->hp.vbc_val_z1_loading_period) bc_z1 = 0;
-    LAUNCH(KC_TWIN, k_node_c, h->D.nnode, 256, h->P, h->D, 0.0, bc_z1, 4);
+    DevParams P = h->P;
+    if (h->pt_jump) for (int i = 0; i < 6; ++i) P.vbc_values[i] = 0.0;      // bc.cxx:330-344
+    LAUNCH(KC_TWIN, k_node_c, h->D.nnode, 256, P, h->D, 0.0, bc_z1, 4);
     CK(cudaGetLastError());
     return DES_OK;
 }
 
-// update_mesh, dynearthsol.cxx:448-492: update_coordinate, surface_processes, volume swap,
-// compute_volume, compute_mass
-int des_gpu_update_mesh(DesGpu *h, double dt)
+// update_mesh, dynearthsol.cxx:448-492: update_coordinate, surface_processes (not while
+// PT_jump is set), volume swap, compute_volume, compute_mass.  part 0 = up to and including
+// surface_processes (the host's surface-marker routines run after it on quality-check steps,
+// bc.cxx:1829-1843), part 1 = the rest, -1 = all of it.
+static int update_mesh_impl(DesGpu *h, double dt, int part)
 {
     int rc = twin_ready(h); if (rc) return rc;
-    LAUNCH(KC_TWIN, k_node_c, h->D.nnode, 256, h->P, h->D, dt, 0, 8);
-    if ((rc = run_surface(h, dt, true))) return rc;
-    h->last_dt = dt;
-    std::swap(h->D.volume, h->D.volume_old);
-    LAUNCH(KC_TWIN, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, 0.0, 3, 0);
-    LAUNCH(KC_TWIN, (k_node_a<true, false>), h->D.nnode, 256, h->P, h->D, 0.0, 0);
-    if ((rc = ymass_update(h))) return rc;
+    if (part != 1) {
+        LAUNCH(KC_TWIN, k_node_c, h->D.nnode, 256, h->P, h->D, dt, 0, 8);
+        if (!h->pt_jump && (rc = run_surface(h, dt, true))) return rc;
+        h->last_dt = dt;
+    }
+    if (part != 0) {
+        std::swap(h->D.volume, h->D.volume_old);
+        LAUNCH(KC_TWIN, (k_elem_a<true, false>), h->D.nelem, 256, h->P, h->D, 0.0, 3, 0);
+        LAUNCH(KC_TWIN, (k_node_a<true, false>), h->D.nnode, 256, h->P, h->D, 0.0, 0);
+        if ((rc = ymass_update(h))) return rc;
+    }
     CK(cudaGetLastError());
     return DES_OK;
+}
+
+int des_gpu_update_mesh(DesGpu *h, double dt) { return update_mesh_impl(h, dt, -1); }
+
+int des_gpu_update_mesh_part(DesGpu *h, double dt, int part)
+{
+    if (part != 0 && part != 1) return DES_E_ARG;
+    return update_mesh_impl(h, dt, part);
 }
 
 int des_gpu_isostasy_constrain_velocity(DesGpu *h)

@@ -280,6 +280,16 @@ int des_gpu_update_force(DesGpu *h);                                /* fields.cx
 int des_gpu_update_velocity(DesGpu *h, double dt);                  /* fields.cxx:725 */
 int des_gpu_apply_vbcs(DesGpu *h, double time);                     /* bc.cxx:227 */
 int des_gpu_update_mesh(DesGpu *h, double dt);                      /* dynearthsol.cxx:448 */
+/* the same in two parts: 0 = update_coordinate + surface_processes, 1 = volume swap, compute_volume,
+ * compute_mass; on quality-check steps the host's surface-marker routines run between them */
+int des_gpu_update_mesh_part(DesGpu *h, double dt, int part);
+/* param.control.PT_jump of the pseudo-transient loops (dynearthsol.cxx:561,811): while set,
+ * des_gpu_apply_vbcs holds the six face values at zero (bc.cxx:330-344) and des_gpu_update_mesh
+ * runs without surface_processes (dynearthsol.cxx:456) */
+int des_gpu_set_pt_jump(DesGpu *h, int on);
+/* param.ic.has_body_force_adjustment (dynearthsol.cxx:753-761): while set, update_force skips the
+ * prescribed tractions (fields.cxx:690) */
+int des_gpu_set_body_force_adjustment(DesGpu *h, int on);
 int des_gpu_compute_volume(DesGpu *h);                              /* geometry.cxx:170 */
 int des_gpu_compute_mass(DesGpu *h);                                /* geometry.cxx:1743 */
 int des_gpu_rotate_stress(DesGpu *h, double dt);                    /* fields.cxx:827 */

@@ -32,6 +32,8 @@ def run(binary, cfg, wd, **extra_env):
     ("t3d-iso.cfg", "t3di", 2),             # + isostasy spin-up before the step loop (51 twin-call iterations)
     ("orift.cfg", "orift", 4),              # oblique-rift-3d.cfg (300 steps): EVP, 2 materials, PREM, averaged fields
     ("orift-full.cfg", "oriftfull", 3),     # oblique-rift-3d.cfg at its configured length (0.1 Myr, ~38 000 steps)
+    ("t3d-pt.cfg", "t3dpt", 4),             # control.has_PT: the step through the twins + 3 pseudo-transient iterations
+    ("t3d-pt-bfa.cfg", "t3dbf", 4),         # + initial_body_force_adjustment, prescribed tractions switched on after it
 ])
 def test_driver_matches_reference_frames(cfg, model, frames, tmp_path):
     if not (os.path.exists(REF) and os.path.exists(B200)):
