@@ -117,7 +117,7 @@ class DesQuality(C.Structure):
 
 # every symbol include/des_gpu.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
-    "des_gpu_create", "des_gpu_create_multi", "des_gpu_partition_info", "des_gpu_set_reorder",
+    "des_gpu_create", "des_gpu_create_multi", "des_gpu_partition_info", "des_host_partition", "des_gpu_set_reorder",
     "des_gpu_destroy", "des_gpu_last_error", "des_gpu_upload_mesh",
     "des_gpu_upload_state", "des_gpu_download_state", "des_gpu_upload_elemmarkers",
     "des_gpu_set_compensation_pressure", "des_gpu_step", "des_gpu_compute_dt",
@@ -157,6 +157,7 @@ def load_library():
     L.des_gpu_create_multi.argtypes = [C.POINTER(DesParam), C.c_int, _IP, C.POINTER(H)]
     L.des_gpu_partition_info.argtypes = [H, _IP, _DP, _DP, _IP, _IP, _IP]
     L.des_gpu_set_reorder.argtypes = [H, C.c_int]
+    L.des_host_partition.argtypes = [C.c_int, C.c_int, _IP, _DP, C.c_int, _IP, _IP, _IP, _IP, _IP]
     L.des_gpu_destroy.argtypes = [H]
     L.des_gpu_last_error.argtypes = [H]
     L.des_gpu_last_error.restype = C.c_char_p
@@ -238,6 +239,22 @@ def host_build_support(nnode, conn):
     if rc:
         raise DesError(rc, "des_host_build_support")
     return idx, arr, lidx
+
+
+def host_partition(coord, conn, nparts):
+    """The multi-device handle's partitioner on the host (des_host_partition): returns
+    (elem_part [E], node_owner [N], local_elems, local_nodes, ghost_nodes [nparts each])."""
+    L = load_library()
+    coord = np.ascontiguousarray(coord, dtype=np.float64)
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    N, E = coord.shape[1], conn.shape[1]
+    part = np.empty(E, dtype=np.int32); owner = np.empty(N, dtype=np.int32)
+    le = np.empty(nparts, dtype=np.int32); ln = np.empty(nparts, dtype=np.int32); gh = np.empty(nparts, dtype=np.int32)
+    rc = L.des_host_partition(N, E, _ptr(conn, C.c_int), _ptr(coord, C.c_double), nparts, _ptr(part, C.c_int),
+                              _ptr(owner, C.c_int), _ptr(le, C.c_int), _ptr(ln, C.c_int), _ptr(gh, C.c_int))
+    if rc:
+        raise DesError(rc, "des_host_partition")
+    return part, owner, le, ln, gh
 
 
 def _ck_plain(rc, what):

@@ -646,6 +646,40 @@ int des_gpu_create_multi(const DesParam *param, int ndev, const int *devices, De
     return fill_dev_params(h);      // the same option checks as one device
 }
 
+// The partitioner of a multi-device handle on its own (no GPU): part of every element, owner of
+// every node, and per part the number of local elements (its own + the redundant layer), local
+// nodes and ghost nodes -- what des_gpu_upload_mesh will build.
+int des_host_partition(int nnode, int nelem, const int *connectivity, const double *coord, int nparts,
+                       int *elem_part, int *node_owner, int *local_elems, int *local_nodes, int *ghost_nodes)
+{
+    if (nnode <= 0 || nelem <= 0 || !connectivity || !coord || nparts < 1 || nparts > 64) return DES_E_ARG;
+    const size_t E = nelem;
+    for (size_t k = 0; k < E * 4; ++k) if ((unsigned)connectivity[k] >= (unsigned)nnode) return DES_E_ARG;
+    std::vector<int> part, owner;
+    partition_elements(nnode, nelem, connectivity, coord, nparts, part, owner);
+    if (elem_part) std::copy(part.begin(), part.end(), elem_part);
+    if (node_owner) std::copy(owner.begin(), owner.end(), node_owner);
+    if (local_elems || local_nodes || ghost_nodes) {
+        std::vector<char> mark(nnode);
+        for (int r = 0; r < nparts; ++r) {
+            std::fill(mark.begin(), mark.end(), 0);
+            int ne = 0, nn = 0, ng = 0;
+            for (size_t e = 0; e < E; ++e) {
+                bool touch = false;
+                for (int i = 0; i < 4; ++i) touch = touch || owner[connectivity[i * E + e]] == r;
+                if (!touch) continue;
+                ++ne;
+                for (int i = 0; i < 4; ++i) mark[connectivity[i * E + e]] = 1;
+            }
+            for (int n = 0; n < nnode; ++n) if (mark[n]) { ++nn; if (owner[n] != r) ++ng; }
+            if (local_elems) local_elems[r] = ne;
+            if (local_nodes) local_nodes[r] = nn;
+            if (ghost_nodes) ghost_nodes[r] = ng;
+        }
+    }
+    return DES_OK;
+}
+
 int des_gpu_partition_info(DesGpu *h, int *nparts, double *partition_seconds, double *upload_seconds,
                            int *local_elems, int *local_nodes, int *ghost_nodes)
 {

@@ -76,6 +76,37 @@ void rcb_split(const double *cx, const double *cy, const double *cz, std::vector
     rcb_split(cx, cy, cz, ids, k, e, p0 + left, np_ - left, part);
 }
 
+// RCB of the element centroids into P parts; a node is owned by the lowest part among the
+// elements around it (0 for a node on no element).  Pure host integer work (also behind
+// des_host_partition, which the CPU tests call).
+void partition_elements(int N, int E, const int *conn, const double *coord, int P,
+                        std::vector<int> &part, std::vector<int> &owner)
+{
+    part.assign(E, 0);
+    {
+        std::vector<double> cx(E), cy(E), cz(E);
+        #pragma omp parallel for
+        for (int e = 0; e < E; ++e) {
+            double s[3] = {0, 0, 0};
+            for (int i = 0; i < 4; ++i) {
+                const int n = conn[size_t(i) * E + e];
+                for (int d = 0; d < 3; ++d) s[d] += coord[size_t(d) * N + n];
+            }
+            cx[e] = s[0] / 4; cy[e] = s[1] / 4; cz[e] = s[2] / 4;
+        }
+        std::vector<int> ids(E);
+        std::iota(ids.begin(), ids.end(), 0);
+        rcb_split(cx.data(), cy.data(), cz.data(), ids, 0, size_t(E), 0, P, part);
+    }
+    owner.assign(N, INT_MAX);
+    for (int i = 0; i < 4; ++i)
+        for (int e = 0; e < E; ++e) {
+            int &o = owner[conn[size_t(i) * E + e]];
+            o = std::min(o, part[e]);
+        }
+    for (int n = 0; n < N; ++n) if (owner[n] == INT_MAX) owner[n] = 0;
+}
+
 int multi_fail(DesGpu *h, int code, const std::string &msg) { return fail(h, code, "multi: " + msg); }
 
 #define MCK(part, call) do { int rc_ = (call); if (rc_) return multi_fail(h, rc_, std::string(#call) + ": " + \
@@ -139,31 +170,9 @@ int multi_upload_mesh(DesGpu *h, const DesMesh *m, const double *coord)
     multi_free_parts(h);
     M.N = N; M.E = E; M.etop = m->etop; M.ntop = m->ntop;
     const int *conn = m->connectivity;
-    // 1. RCB of the element centroids
-    std::vector<int> part(E);
-    {
-        std::vector<double> cx(E), cy(E), cz(E);
-        #pragma omp parallel for
-        for (int e = 0; e < E; ++e) {
-            double s[3] = {0, 0, 0};
-            for (int i = 0; i < 4; ++i) {
-                const int n = conn[size_t(i) * E + e];
-                for (int d = 0; d < 3; ++d) s[d] += coord[size_t(d) * N + n];
-            }
-            cx[e] = s[0] / 4; cy[e] = s[1] / 4; cz[e] = s[2] / 4;
-        }
-        std::vector<int> ids(E);
-        std::iota(ids.begin(), ids.end(), 0);
-        rcb_split(cx.data(), cy.data(), cz.data(), ids, 0, size_t(E), 0, P, part);
-    }
-    // 2. node owner = lowest part around it
-    std::vector<int> owner(N, INT_MAX);
-    for (int i = 0; i < 4; ++i)
-        for (int e = 0; e < E; ++e) {
-            int &o = owner[conn[size_t(i) * E + e]];
-            o = std::min(o, part[e]);
-        }
-    for (int n = 0; n < N; ++n) if (owner[n] == INT_MAX) owner[n] = 0;      // a node on no element
+    // 1. RCB of the element centroids, 2. node owner = lowest part around it
+    std::vector<int> part, owner;
+    partition_elements(N, E, conn, coord, P, part, owner);
     // global top tables
     std::vector<int> gtop(N, -1);
     for (int i = 0; i < m->ntop; ++i) gtop[m->top_nodes[i]] = i;

@@ -176,6 +176,11 @@ int des_gpu_partition_info(DesGpu *h, int *nparts, double *partition_seconds, do
  * environment variable DES_REORDER=morton selects 2 at create.  des_gpu_device_ptr then
  * returns arrays in the internal order. */
 int des_gpu_set_reorder(DesGpu *h, int mode);
+/* the same partitioner without a device (pure host integer work): RCB part of every element
+ * [nelem], owner of every node [nnode], and per part the local element / node / ghost-node counts
+ * des_gpu_upload_mesh would build ([nparts] each; any output may be NULL) */
+int des_host_partition(int nnode, int nelem, const int *connectivity, const double *coord, int nparts,
+                       int *elem_part, int *node_owner, int *local_elems, int *local_nodes, int *ghost_nodes);
 /* end() (dynearthsol.cxx:440-445) */
 int des_gpu_destroy(DesGpu *h);
 const char *des_gpu_last_error(const DesGpu *h);

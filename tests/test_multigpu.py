@@ -377,3 +377,28 @@ def test_interior_first_order_keeps_the_summation_order(world):
         assert np.array_equal(re["connectivity_surface"], plain["connectivity_surface"])
         assert np.array_equal(re["elem_and_nodes"], plain["elem_and_nodes"])
         assert np.array_equal(re["support_surf_arr"], plain["support_surf_arr"])
+
+
+@pytest.mark.parametrize("nparts", [2, 3, 8])
+def test_library_partitioner_on_the_host(nparts):
+    """The partitioner behind des_gpu_create_multi (csrc/des_multi.cuh), run without a device
+    through des_host_partition: RCB parts balanced to one element, every node owned by the lowest
+    part around it, and the local element / node / ghost counts equal to what partition.py's
+    local_subset (the scheme the NCCL harness uses) builds from the same parts."""
+    from dynearthsol_b200 import core
+    (nx, ny, nz), coord, conn, bcflag = global_box()
+    N, E = coord.shape[1], conn.shape[1]
+    part, owner, le, ln, gh = core.host_partition(coord, conn, nparts)
+    counts = np.bincount(part, minlength=nparts)
+    assert counts.sum() == E and counts.max() - counts.min() <= nparts      # count-proportional bisection
+    assert np.array_equal(owner, pt.node_owner_from_parts(conn, part, N))
+    # each part is a coordinate box of centroids along the cut axes: no part's bounding boxes interleave badly
+    cen = pt.element_centroids(coord, conn)
+    for r in range(nparts):
+        elem_gid, node_gid, conn_local = pt.local_subset(conn, owner, r)
+        assert le[r] == elem_gid.size and ln[r] == node_gid.size
+        assert gh[r] == int((owner[node_gid] != r).sum())
+        assert np.isfinite(cen[:, part == r]).all()
+    # the first cut is along x (the longest side of the 24 x 10 x 8 km box): parts 0..left-1 lie left of the rest
+    left = nparts // 2
+    assert cen[0, part < left].max() <= cen[0, part >= left].min()
