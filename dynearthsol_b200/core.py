@@ -120,7 +120,7 @@ ABI_SYMBOLS = [
     "des_gpu_create", "des_gpu_create_multi", "des_gpu_partition_info", "des_host_partition", "des_gpu_set_reorder",
     "des_gpu_destroy", "des_gpu_last_error", "des_gpu_upload_mesh",
     "des_gpu_upload_state", "des_gpu_download_state", "des_gpu_upload_elemmarkers",
-    "des_gpu_set_compensation_pressure", "des_gpu_step", "des_gpu_compute_dt",
+    "des_gpu_set_compensation_pressure", "des_gpu_step", "des_gpu_compute_dt", "des_gpu_compute_dt_static",
     "des_dt_from_reductions", "des_gpu_sync",
     "des_gpu_update_temperature", "des_gpu_update_strain_rate", "des_gpu_compute_dvoldt",
     "des_gpu_compute_edvoldt", "des_gpu_update_stress", "des_gpu_nmd_stress",
@@ -168,6 +168,7 @@ def load_library():
     L.des_gpu_set_compensation_pressure.argtypes = [H, C.c_double]
     L.des_gpu_step.argtypes = [H, C.c_double, C.c_double, C.c_int]
     L.des_gpu_compute_dt.argtypes = [H, C.POINTER(DesDtReductions)]
+    L.des_gpu_compute_dt_static.argtypes = [H, C.POINTER(DesDtReductions)]
     L.des_dt_from_reductions.argtypes = [C.POINTER(DesParam), C.POINTER(DesDtReductions), _DP]
     L.des_dt_from_reductions.restype = C.c_double
     L.des_gpu_sync.argtypes = [H]
@@ -580,6 +581,13 @@ class DesGpu:
     def compute_dt_reductions(self):
         r = DesDtReductions()
         self._ck(self.lib.des_gpu_compute_dt(self.h, C.byref(r)))
+        return r
+
+    def compute_dt_reductions_static(self):
+        """des_gpu_compute_dt_static: the same reductions out of the library's static device
+        scratch, no allocation (no counterpart in the reference; include/des_gpu.h)."""
+        r = DesDtReductions()
+        self._ck(self.lib.des_gpu_compute_dt_static(self.h, C.byref(r)))
         return r
 
     def compute_dt(self):

@@ -13,6 +13,7 @@
 #include <vector>
 #include <algorithm>
 #include <limits>
+#include <mutex>
 
 #include "des_kernels2.cuh"
 #include "des_aux.cuh"
@@ -1863,6 +1864,97 @@ void *des_gpu_device_ptr(DesGpu *h, const char *name)
 }
 
 } // extern "C"
+
+// ---- des_gpu_compute_dt_static: compute_dt's reductions without any allocation --------------
+// No counterpart in the reference; added for callers that
+// may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+// k_dt's per-block partial results and k_dt_final's combined result live in the file-scope
+// device array below instead of the handle's cudaMalloc'ed dt_partials.  The array exists once
+// per GPU that loads this library and is held until the process exits:
+// (DES_STATIC_DT_BLOCKS + 1) * 40 bytes = 655 400 bytes.  One block reduces
+// DES_STATIC_DT_ELEMS_PER_BLOCK elements, so the entry serves meshes of up to
+// DES_STATIC_DT_BLOCKS * DES_STATIC_DT_ELEMS_PER_BLOCK = 16 777 216 elements and refuses
+// larger ones.
+#define DES_STATIC_DT_BLOCKS 16384
+#define DES_STATIC_DT_ELEMS_PER_BLOCK 1024
+#define DES_STATIC_MAX_DEVICES 64
+
+static_assert((long long)DES_STATIC_DT_BLOCKS * DES_STATIC_DT_ELEMS_PER_BLOCK == DES_STATIC_DT_MAX_ELEMS,
+              "include/des_gpu.h states the limit");
+
+static __device__ __align__(256) DtPartial des_static_dt_scratch[DES_STATIC_DT_BLOCKS + 1];
+
+namespace {
+
+// In host code `des_static_dt_scratch` is only a stand-in for the symbol, not a device address:
+// the address the kernels get is looked up once per device, with that device current.
+DtPartial *g_static_dt_addr[DES_STATIC_MAX_DEVICES];
+std::mutex g_static_dt_mutex;
+
+int static_dt_scratch(DesGpu *h, DtPartial **out)
+{
+    if (h->device < 0 || h->device >= DES_STATIC_MAX_DEVICES)
+        return fail(h, DES_E_UNSUPPORTED, "des_gpu_compute_dt_static: device index beyond " +
+                    std::to_string(DES_STATIC_MAX_DEVICES - 1));
+    std::lock_guard<std::mutex> lock(g_static_dt_mutex);
+    if (!g_static_dt_addr[h->device]) {
+        CK(cudaSetDevice(h->device));
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, des_static_dt_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(h, DES_E_CUDA, std::string("cudaGetSymbolAddress(des_static_dt_scratch): ") +
+                        cudaGetErrorString(e));
+        g_static_dt_addr[h->device] = static_cast<DtPartial *>(p);
+    }
+    *out = g_static_dt_addr[h->device];
+    return DES_OK;
+}
+
+} // namespace
+
+extern "C" int des_gpu_compute_dt_static(DesGpu *h, DesDtReductions *out)
+{
+    if (!h || !out) return DES_E_ARG;
+    if (!h->have_mesh || !h->have_state) return fail(h, DES_E_STATE, "upload mesh and state first");
+    if (h->multi) return fail(h, DES_E_UNSUPPORTED, "des_gpu_compute_dt_static runs on a single-device handle");
+    const long long E = h->D.nelem;
+    const long long max_elems = (long long)DES_STATIC_DT_BLOCKS * DES_STATIC_DT_ELEMS_PER_BLOCK;
+    if (E > max_elems)
+        return fail(h, DES_E_ARG, "des_gpu_compute_dt_static: the mesh has " + std::to_string(E) +
+                    " elements, the static scratch serves at most " + std::to_string(max_elems) +
+                    " (" + std::to_string(DES_STATIC_DT_BLOCKS) + " block partials); use des_gpu_compute_dt");
+    CK(cudaSetDevice(h->device));
+    DtPartial *scratch = nullptr;
+    int rc = static_dt_scratch(h, &scratch);
+    if (rc) return rc;
+    DtPartial *result = scratch + DES_STATIC_DT_BLOCKS;
+    const int nparts = std::max(1, int((E + DES_STATIC_DT_ELEMS_PER_BLOCK - 1) / DES_STATIC_DT_ELEMS_PER_BLOCK));
+    // The array keeps the previous call's contents.  Every partial that k_dt_final reads is
+    // written by this call's k_dt first; the result slot is cleared so that a launch that
+    // failed cannot hand back the previous call's numbers.
+    CK(cudaMemsetAsync(result, 0, sizeof(DtPartial), h->stream));
+    // nothing of the handle's deferred end-of-step work is touched: like the non-riding path of
+    // des_gpu_compute_dt, k_dt evaluates the volume itself while compute_volume is pending
+    const int fresh_volume = (h->tail_pending && h->hp.has_moving_mesh) ? 1 : 0;
+    if (h->hp.nmat == 1) k_dt<true><<<nparts, 256, 0, h->stream>>>(h->P, h->D, scratch, fresh_volume);
+    else k_dt<false><<<nparts, 256, 0, h->stream>>>(h->P, h->D, scratch, fresh_volume);
+    k_dt_final<<<1, 1024, 0, h->stream>>>(nparts, (const DtPartial *)scratch, result);
+    h->launches += 2;
+    DtPartial r;
+    unsigned long long bits = 0;
+    int status = 0;
+    CK(cudaMemcpyAsync(&r, result, sizeof(DtPartial), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&bits, h->D.maxdh_bits, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&status, h->D.status, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    if (status & 1) return fail(h, DES_E_NAN, "an element volume became non-positive or NaN (compute_volume)");
+    out->minl = r.minl; out->dt_maxwell = r.dt_maxwell; out->dt_diffusion = r.dt_diffusion;
+    out->global_dt_min = r.global_dt_min; out->global_max_vem = r.max_vem;
+    double maxdh; memcpy(&maxdh, &bits, sizeof(double));
+    out->max_surf_vel = (h->surf_ran && h->last_dt > 0) ? maxdh / h->last_dt : 0.0;   // bc.cxx:1825
+    return DES_OK;
+}
 
 #include "des_twins.cuh"
 #include "des_topology_api.cuh"

@@ -228,6 +228,20 @@ int des_gpu_step_segment(DesGpu *h, int segment, double dt, double time);
  * tetrahedron: the host then writes its error frame -- downloads still work -- and dies).
  * The element loop rides on the next step's first kernel, so the call costs no extra pass. */
 int des_gpu_compute_dt(DesGpu *h, DesDtReductions *out);
+/* No counterpart in the reference: added for callers that
+ * may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The same reductions as des_gpu_compute_dt -- same inputs (the handle's resident
+ * mesh and state), same outputs, bit-identical values -- but the per-block partial results live
+ * in a file-scope static __device__ array of the library (655 400 bytes on every GPU that loads
+ * it, held until the process exits) and the call allocates nothing: no cudaMalloc, cudaFree or
+ * allocating library routine.  It runs as its own pass over the elements (it does not ride on the
+ * next step's first kernel) and leaves the handle's step schedule untouched.
+ * Limit: meshes of at most DES_STATIC_DT_MAX_ELEMS elements; larger ones are refused with
+ * DES_E_ARG and a message naming the limit.  Single-device handles only (DES_E_UNSUPPORTED for a
+ * group).  Every call on a device shares the one array: calls that overlap on the same GPU
+ * (two handles on different streams, two host threads) race -- serialise them. */
+#define DES_STATIC_DT_MAX_ELEMS 16777216
+int des_gpu_compute_dt_static(DesGpu *h, DesDtReductions *out);
 /* host scalar algebra of geometry.cxx:1597-1630 (no GPU work); returns dt, <=0 on error */
 double des_dt_from_reductions(const DesParam *param, const DesDtReductions *r,
                               double *max_global_vel_mag);
