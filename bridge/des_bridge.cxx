@@ -318,6 +318,7 @@ int pt_iterations(DesBridge *b, Param &param, Variables &var, double &residual_o
             const int bad = des_bridge_bad_mesh_quality(b, param, var, index, min_quality);
             if (bad < 0) return 1;
             if (bad) {
+                des_bridge_output_barrier();
                 if (des_bridge_download(b, var, DES_DL_ALL)) return 1;
                 if (param.sim.has_output_during_remeshing) var.output->write_exact(var);
                 remesh(param, var, bad);
@@ -496,6 +497,9 @@ int des_bridge_flush_averages(DesBridge *b, const Param &param, Variables &var)
     var.time = time; var.steps = steps;
     return 0;
 }
+
+DesGpu *des_bridge_handle(DesBridge *b) { return b ? b->h : nullptr; }
+double des_bridge_avg_time0(const DesBridge *b) { return b->avg_time0; }
 
 const char *des_bridge_last_error(const DesBridge *b) { return b ? b->err.c_str() : "null bridge"; }
 

@@ -54,6 +54,19 @@ int des_bridge_average_fields(DesBridge *b, const Param &param, const Variables 
 // before Output::write on a frame step: hands the device accumulators to the Output object
 // (through its own average_fields, so output.cxx stays untouched)
 int des_bridge_flush_averages(DesBridge *b, const Param &param, Variables &var);
+// Output::write for a regular frame (dynearthsol.cxx:928) without the trip through `Variables`:
+// the device delivers each array in the on-disk layout (des_gpu_download_frame) and the file is
+// written through the reference's BinaryOutput (bridge/des_frame_writer.cxx), in the background
+// when sim.has_marker_output = no.  Replaces des_bridge_download + des_bridge_flush_averages +
+// var.output->write(var).
+int des_bridge_write_frame(DesBridge *b, const Param &param, Variables &var);
+bool des_bridge_direct_output_ok(DesBridge *b, const Variables &var);
+// waits for a frame that is still being written; before any other use of var.output, before
+// remesh() and before the run ends
+void des_bridge_output_barrier();
+void des_bridge_frame_timing(double *download_s, double *write_s);
+DesGpu *des_bridge_handle(DesBridge *b);
+double des_bridge_avg_time0(const DesBridge *b);
 const char *des_bridge_last_error(const DesBridge *b);
 void des_bridge_destroy(DesBridge *b);
 

@@ -136,13 +136,26 @@ int main(int argc, const char* argv[])
                 (param.sim.is_outputting_averaged_fields &&
                     (var.steps % param.mesh.quality_check_step_interval == 0)))
             ) {
-                // [B200] bring the output fields back into Variables before Output::write
-                des_bridge_download(gpu, var, DES_DL_ALL);
-                if (param.sim.is_outputting_averaged_fields)
-                    if (des_bridge_flush_averages(gpu, param, var)) return 1;
-                if (next_regular_frame % param.sim.checkpoint_frame_interval == 0)
-                    var.output->write_checkpoint(param, var);
-                var.output->write(var);
+                const bool checkpoint = next_regular_frame % param.sim.checkpoint_frame_interval == 0;
+                if (des_bridge_direct_output_ok(gpu, var)) {
+                    // [B200] var.output->write(var);   (dynearthsol.cxx:928) -- the frame's arrays come
+                    // from the device in the on-disk layout, nothing passes through Variables
+                    if (checkpoint) {
+                        des_bridge_output_barrier();
+                        des_bridge_download(gpu, var, DES_DL_ALL);
+                        var.output->write_checkpoint(param, var);
+                    }
+                    if (des_bridge_write_frame(gpu, param, var)) return 1;
+                }
+                else {
+                    // [B200] bring the output fields back into Variables before Output::write
+                    des_bridge_download(gpu, var, DES_DL_ALL);
+                    if (param.sim.is_outputting_averaged_fields)
+                        if (des_bridge_flush_averages(gpu, param, var)) return 1;
+                    if (checkpoint)
+                        var.output->write_checkpoint(param, var);
+                    var.output->write(var);
+                }
                 next_regular_frame ++;
                 var.reference_frame_time = starting_time +
                     next_regular_frame * param.sim.output_time_interval_in_yr * YEAR2SEC;
@@ -158,6 +171,7 @@ int main(int argc, const char* argv[])
                 if (quality_is_bad < 0) return 1;
                 if (quality_is_bad) {
                     // [B200] full state to the host, host remesh, full re-upload (cost reported)
+                    des_bridge_output_barrier();    // a frame still being written reads the old mesh
                     int64_t t0 = get_nanoseconds();
                     des_bridge_download(gpu, var, DES_DL_ALL);
                     int64_t t1 = get_nanoseconds();
@@ -190,6 +204,7 @@ int main(int argc, const char* argv[])
               (param.sim.is_outputting_averaged_fields &&
                var.steps % param.mesh.quality_check_step_interval != 0)));
 
+    des_bridge_output_barrier();
     des_bridge_download(gpu, var, DES_DL_ALL);
     des_bridge_destroy(gpu);
     end(var);

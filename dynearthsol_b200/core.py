@@ -100,6 +100,21 @@ class DesDtReductions(C.Structure):
                 ("max_surf_vel", C.c_double)]
 
 
+FRAME_NODE3 = ("coordinate", "velocity", "velocity_averaged", "force")
+FRAME_NODE1 = ("temperature",)
+FRAME_ELEM6 = ("strain_rate", "strain", "stress", "stress_averaged")
+FRAME_ELEM1 = ("plstrain", "plstrain_rate", "viscosity", "density", "mesh_quality", "material")
+
+
+class DesFrame(C.Structure):
+    """The arrays of one output frame in the on-disk layout (include/des_gpu.h: DesFrame)."""
+    _fields_ = ([("averaged", C.c_int), ("inv_dt", C.c_double), ("stress_avg_scale", C.c_double)] +
+                [(k, C.POINTER(C.c_double)) for k in (
+                    "coordinate", "velocity", "velocity_averaged", "temperature", "plstrain",
+                    "plstrain_rate", "strain_rate", "strain", "stress", "viscosity", "stress_averaged",
+                    "density", "mesh_quality", "material", "force")])
+
+
 class DesQualityParam(C.Structure):
     """Param.mesh members bad_mesh_quality reads (remeshing.cxx:2752-2866)."""
     _fields_ = [("smallest_size", C.c_double), ("resolution", C.c_double),
@@ -136,6 +151,7 @@ ABI_SYMBOLS = [
     "des_gpu_set_interior", "des_gpu_step_segment_part",
     "des_gpu_mesh_quality", "des_quality_verdict", "des_gpu_average_fields",
     "des_gpu_download_averages", "des_gpu_check_nan",
+    "des_gpu_download_frame", "des_host_alloc", "des_host_free",
     "des_gpu_build_support", "des_gpu_find_boundary_facets", "des_host_boundary_flags",
     "des_host_boundary_nodes", "des_host_bucket_facets", "des_host_surface_topology",
 ]
@@ -218,7 +234,11 @@ def load_library():
     L.des_gpu_check_nan.argtypes = [H, C.POINTER(C.c_int)]
     L.des_gpu_average_fields.argtypes = [H, C.c_int]
     L.des_gpu_download_averages.argtypes = [H, _DP, _DP, _DP, _DP]
-    for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions, DesQualityParam, DesQuality)):
+    L.des_gpu_download_frame.argtypes = [H, C.POINTER(DesFrame)]
+    L.des_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    L.des_host_free.argtypes = [C.c_void_p]
+    for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions, DesQualityParam, DesQuality,
+                            DesFrame)):
         if L.des_abi_sizeof(i) != C.sizeof(st):
             raise ImportError("ABI mismatch: %s is %d bytes in the library, %d in core.py"
                               % (st.__name__, L.des_abi_sizeof(i), C.sizeof(st)))
@@ -628,6 +648,24 @@ class DesGpu:
         N, E = self.nnode, self.nelem
         out = [np.empty(3 * N), np.empty(6 * E), np.empty(6 * E), np.empty(E)]
         self._ck(self.lib.des_gpu_download_averages(self.h, *[_ptr(a, C.c_double) for a in out]))
+        return out
+
+    def download_frame(self, averaged=False, inv_dt=0.0, stress_avg_scale=0.0, names=None):
+        """des_gpu_download_frame: Output::_write's arrays (output.cxx:95-245) in the on-disk
+        layout, [n][components]; returns {name: array}."""
+        f = DesFrame()
+        f.averaged = int(bool(averaged)); f.inv_dt = float(inv_dt); f.stress_avg_scale = float(stress_avg_scale)
+        out = {}
+        for group, n, w in ((FRAME_NODE3, self.nnode, 3), (FRAME_NODE1, self.nnode, 1),
+                            (FRAME_ELEM6, self.nelem, 6), (FRAME_ELEM1, self.nelem, 1)):
+            for k in group:
+                if names is not None and k not in names:
+                    continue
+                if names is None and not averaged and k in ("velocity_averaged", "stress_averaged"):
+                    continue
+                out[k] = np.empty((n, w) if w > 1 else n, dtype=np.float64)
+                setattr(f, k, _ptr(out[k], C.c_double))
+        self._ck(self.lib.des_gpu_download_frame(self.h, C.byref(f)))
         return out
 
     def sync(self):

@@ -1800,6 +1800,7 @@ int des_abi_sizeof(int which)
     case 3: return int(sizeof(DesDtReductions));
     case 4: return int(sizeof(DesQualityParam));
     case 5: return int(sizeof(DesQuality));
+    case 6: return int(sizeof(DesFrame));
     default: return -1;
     }
 }
@@ -1958,3 +1959,4 @@ extern "C" int des_gpu_compute_dt_static(DesGpu *h, DesDtReductions *out)
 
 #include "des_twins.cuh"
 #include "des_topology_api.cuh"
+#include "des_frame.cuh"

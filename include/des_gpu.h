@@ -18,6 +18,8 @@
 #ifndef DES_GPU_H
 #define DES_GPU_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -285,6 +287,41 @@ int des_gpu_average_fields(DesGpu *h, int first);
  * was uploaded. */
 int des_gpu_download_averages(DesGpu *h, double *coord0, double *strain0, double *stress_avg,
                               double *delta_plstrain_avg);
+
+/* ---- one output frame straight from the device ----------------
+ * The arrays Output::_write (output.cxx:95-245) hands to BinaryOutput, already in the layout
+ * BinaryOutput::write_array puts on disk (Array2D::pack_to, binaryio.cxx:151-166: [n][components])
+ * and with _write's own host loops applied on the device: the averaged variants
+ * (output.cxx:131-190), density = MatProps::rho(e) (:192-196), mesh quality = elem_quality(e)
+ * (:198-202), material = the most abundant marker type (:214-220).  The caller fwrites them.
+ * Every pointer is a HOST buffer (des_host_alloc gives pinned ones: the copies then run at PCIe
+ * speed); NULL = not wanted.  Values are bit-identical to what the reference writes. */
+typedef struct DesFrame {
+    int averaged;               /* !disable_averaging && is_averaged, output.cxx:103 */
+    double inv_dt;              /* 1 / (time - time0), output.cxx:105 (averaged only) */
+    double stress_avg_scale;    /* 1 / (average_interval + 1), output.cxx:185 (averaged only) */
+    double *coordinate;         /* [nnode][3] */
+    double *velocity;           /* [nnode][3] */
+    double *velocity_averaged;  /* [nnode][3]  (coord - coord0) * inv_dt; averaged only */
+    double *temperature;        /* [nnode] */
+    double *plstrain;           /* [nelem] */
+    double *plstrain_rate;      /* [nelem]     delta_plstrain, or its running sum * inv_dt */
+    double *strain_rate;        /* [nelem][6]  strain_rate, or (strain - strain0) * inv_dt */
+    double *strain;             /* [nelem][6] */
+    double *stress;             /* [nelem][6] */
+    double *viscosity;          /* [nelem] */
+    double *stress_averaged;    /* [nelem][6]  running sum * stress_avg_scale; averaged only */
+    double *density;            /* [nelem] */
+    double *mesh_quality;       /* [nelem] */
+    double *material;           /* [nelem]     (a double, as the reference writes it) */
+    double *force;              /* [nnode][3] */
+} DesFrame;
+/* Single-device handles (a group handle answers DES_E_UNSUPPORTED: use des_gpu_download_state).
+ * averaged = 1 needs des_gpu_average_fields since the interval began (DES_E_STATE otherwise). */
+int des_gpu_download_frame(DesGpu *h, const DesFrame *frame);
+/* page-locked host memory for callers without the CUDA runtime (cudaHostAlloc / cudaFreeHost) */
+int des_host_alloc(size_t bytes, void **out);
+int des_host_free(void *p);
 
 /* ---- fine-grained twins of the reference calls (PT loop dynearthsol.cxx:803-864,
  * isostasy_adjustment :506-539, remeshing.cxx:3133-3168; also the per-function parity

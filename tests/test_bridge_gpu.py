@@ -34,6 +34,7 @@ def run(binary, cfg, wd, **extra_env):
     ("orift-full.cfg", "oriftfull", 3),     # oblique-rift-3d.cfg at its configured length (0.1 Myr, ~38 000 steps)
     ("t3d-pt.cfg", "t3dpt", 4),             # control.has_PT: the step through the twins + 3 pseudo-transient iterations
     ("t3d-pt-bfa.cfg", "t3dbf", 4),         # + initial_body_force_adjustment, prescribed tractions switched on after it
+    ("t3d-nomarkers.cfg", "t3dnm", 6),      # sim.has_marker_output = no: frames written on a background thread
 ])
 def test_driver_matches_reference_frames(cfg, model, frames, tmp_path):
     if not (os.path.exists(REF) and os.path.exists(B200)):
@@ -120,6 +121,47 @@ def test_driver_over_several_devices_matches_reference_frames(cfg, model, frames
         b = desframe.read_frame(str(tmp_path / "gpu" / fn))
         worst, report, bad = desframe.compare_frames(a, b)
         assert not bad, "frame %d: %s   [all: %s]" % (k, bad, " ".join(report))
+
+
+def _bytes_without_walltime(path):
+    raw = bytearray(open(path, "rb").read())
+    for line in bytes(raw[:desframe.HEADER]).splitlines()[1:]:
+        if line.startswith(b"walltime_sec\t"):
+            p = int(line.split(b"\t")[1])
+            raw[p:p + 8] = b"\0" * 8
+    return bytes(raw)
+
+
+@pytest.mark.parametrize("cfg,model,frames", [
+    ("t3d.cfg", "t3d", 6),                  # plain fields + marker sets (written synchronously)
+    ("orift.cfg", "orift", 4),              # averaged fields, two materials, viscosity
+    ("t3d-remesh.cfg", "t3dr", 5),          # the frame buffers follow the new mesh size
+    ("t3d-nomarkers.cfg", "t3dnm", 6),      # background thread
+])
+def test_direct_frames_are_the_files_output_write_makes(cfg, model, frames, tmp_path):
+    """Frames written from the device in the on-disk layout (des_gpu_download_frame +
+    bridge/des_frame_writer.cxx, the default) against the same binary going through Variables and
+    the reference's Output::write (DES_BRIDGE_DIRECT_OUTPUT=0): the same bytes, header included,
+    except the wall-clock scalar; and the same .info rows except their wall-clock column."""
+    if not os.path.exists(B200):
+        pytest.skip("bridge binary not built")
+    out = run(B200, cfg, str(tmp_path / "direct"), DES_BRIDGE_FRAME_TIMING="1")
+    run(B200, cfg, str(tmp_path / "write"), DES_BRIDGE_DIRECT_OUTPUT="0")
+    assert "[B200] frame from the device" in out
+    if cfg == "t3d-nomarkers.cfg":
+        assert "in the background" in out
+    for k in range(frames):
+        fn = "%s.save.%06d" % (model, k)
+        a = _bytes_without_walltime(str(tmp_path / "write" / fn))
+        b = _bytes_without_walltime(str(tmp_path / "direct" / fn))
+        assert len(a) == len(b), (fn, len(a), len(b))
+        assert a == b, fn
+    rows = [[l.split() for l in open(str(tmp_path / w / (model + ".info")))] for w in ("write", "direct")]
+    assert len(rows[0]) == len(rows[1]) == frames
+    for ra, rb in zip(*rows):
+        assert len(ra) == len(rb)
+        diff = [i for i, (x, y) in enumerate(zip(ra, rb)) if x != y]
+        assert len(diff) <= 1, (ra, rb)     # the run-time column
 
 
 def test_driver_restart_matches_reference_frames(tmp_path):
