@@ -1960,3 +1960,4 @@ extern "C" int des_gpu_compute_dt_static(DesGpu *h, DesDtReductions *out)
 #include "des_twins.cuh"
 #include "des_topology_api.cuh"
 #include "des_frame.cuh"
+#include "des_transfer_api.cuh"

@@ -425,6 +425,58 @@ int des_host_surface_topology(int nnode, int ntop, const int *bnodes_z1, const d
                               int etop, const int *conn_surface,
                               int *top_nodes, int max_top_elems, int *ntop_elems, int *top_elems,
                               int *elem_and_nodes, int *ssup_idx, int *ssup_arr);
+/* ---- remesh field transfer: what remesh() asks of
+ * nearest_neighbor_interpolation and barycentric_node_interpolation (remeshing.cxx:3058-3069),
+ * on device `device`, between an OLD and a NEW mesh.  No handle: remesh() runs between a full
+ * download and a fresh upload.  Every pointer is a HOST array in the reference's own layout
+ * (Array2D SoA: component d of item i at [d*n + i]; conn_t has 4 components, a surface facet
+ * uses the first 3).  The k-nearest-neighbour searches are exact, ascending by (distance^2,
+ * index): nanoflann's result order with equal distances resolved by the lower index (nanoflann
+ * resolves them by its tree traversal order); every arithmetic statement keeps the reference's
+ * operation order, so integer outputs and transferred fields are bit-identical. ------------- */
+typedef struct DesTransferMeshes {
+    int old_nnode;              /* old_coord.size() */
+    const double *old_coord;    /* [3][old_nnode] */
+    int old_ncell;              /* old elements, or old top-surface facets */
+    const int *old_conn;        /* [4][old_ncell]  old_connectivity / old_connectivity_surface */
+    const double *old_size;     /* [old_ncell]     the volumes (areas) given to Barycentric_transformation */
+    int new_nnode;
+    const double *new_coord;    /* [3][new_nnode]  *var.coord */
+    int new_ncell;              /* new elements / facets (unused by the node transfer) */
+    const int *new_conn;        /* [4][new_ncell]  (unused by the node transfer) */
+} DesTransferMeshes;
+typedef struct DesTransferField {
+    const double *src;          /* [ncomp][old items] */
+    double *dst;                /* [ncomp][new items], caller-allocated */
+    int ncomp;                  /* 1 (double_vec), 3 (array_t) or 6 (tensor_t) */
+} DesTransferField;
+typedef struct DesTransferStats {
+    int nchanged;               /* cells: entries with is_changed > 0 after the nearest-neighbour
+                                 * pass; nodes: new nodes the one-ring search did not place */
+    int nsample;                /* cells: sample points per changed cell */
+    int n_on_face, n_outside;   /* nodes: taken as lying on a face / outside the old domain */
+    double search_seconds, acm_seconds, field_seconds;   /* wall clock, copies included */
+} DesTransferStats;
+/* nearest_neighbor_interpolation (nn-interpolation.cxx:661-702): nearest old centroid of every
+ * new cell (find_nearest_neighbor, :16-75), volume-ratio mapping of the changed ones through
+ * sample points located in the 32 nearest old cells (find_acm_elem_ratios, :77-318), then
+ * inject_field (:433-523) for every field.  is_surface = 0: elements (old_size = volume);
+ * 1: the facets of the top surface (old_size = area; centroids compared in x, y).
+ * is_changed (may be NULL) receives var.remesh_is_changed: 0 same centroid, 1 remapped by
+ * ratios, -1 changed but kept on its nearest neighbour. */
+int des_remesh_transfer_cells(int device, const DesTransferMeshes *m, int is_surface, int nfields,
+                              const DesTransferField *fields, int *is_changed, DesTransferStats *stats);
+/* barycentric_node_interpolation (brc-interpolation.cxx:345-423): the old element around every
+ * new node -- nearest old node, its one ring, then the capped breadth-first search and the two
+ * fallbacks of prepare_interpolation (:98-341) -- and interpolate_field (:18-96) for every field.
+ * old_support_idx / _arr: create_support's lists of the OLD mesh.  el [new_nnode] and
+ * brc [new_nnode][4] (may be NULL) receive the enclosing element and the four weights.
+ * DES_E_UNSUPPORTED: a new node's search met more than 16 384 old elements within three rings
+ * of its nearest old node (per-node scratch of the search). */
+int des_remesh_transfer_nodes(int device, const DesTransferMeshes *m, const int *old_support_idx,
+                              const int *old_support_arr, int nfields, const DesTransferField *fields,
+                              int *el, double *brc, DesTransferStats *stats);
+
 /* sizeof() of the ABI structs as compiled, so a foreign-language binding can verify its
  * own layout: which = 0 DesParam, 1 DesMesh, 2 DesState, 3 DesDtReductions, 4 DesQualityParam, 5 DesQuality */
 int des_abi_sizeof(int which);

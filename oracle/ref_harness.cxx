@@ -127,6 +127,130 @@ extern "C" void __wrap__Z22create_boundary_facetsR9Variables(Variables &var)
     else __real__Z22create_boundary_facetsR9Variables(var);
 }
 
+
+// ---- remesh field transfer: recorder ---------------------------
+// The library is also linked with --wrap on nearest_neighbor_interpolation
+// (nn-interpolation.cxx:661) and barycentric_node_interpolation (brc-interpolation.cxx:345).
+// The calls inside the reference's own remesh() (remeshing.cxx:3058-3069) arrive here, go on to
+// the reference's own functions (__real_) and -- when desref_capture_transfers(1) was called --
+// what they were given and what they made is kept for the tests to fetch
+// (desref_captured_nbytes / desref_captured_get).  Nothing numeric is restated here.
+#include <map>
+#include "barycentric-fn.hpp"
+#include "nn-interpolation.hpp"
+#include "brc-interpolation.hpp"
+#define DESREF_NN  _Z30nearest_neighbor_interpolationRK5ParamR9VariablesRK26Barycentric_transformationRK7Array2DIdLi3EERKS7_IiLi4EEb
+#define DESREF_BRC _Z30barycentric_node_interpolationRK5ParamR9VariablesRK26Barycentric_transformationRK7Array2DIdLi3EERKS7_IiLi4EE
+#define DESREF_CAT2(a, b) a##b
+#define DESREF_CAT(a, b) DESREF_CAT2(a, b)
+extern "C" void DESREF_CAT(__real_, DESREF_NN)(const Param &, Variables &, const Barycentric_transformation &,
+                                               const array_t &, const conn_t &, const bool);
+extern "C" void DESREF_CAT(__real_, DESREF_BRC)(const Param &, Variables &, const Barycentric_transformation &,
+                                                const array_t &, const conn_t &);
+static int g_capture = 0;
+static std::map<std::string, std::vector<char>> g_captured;
+static void keep(const std::string &name, const void *p, size_t nbytes)
+{
+    const char *c = static_cast<const char *>(p);
+    g_captured[name].assign(c, c + nbytes);
+}
+template <typename A> static void keep2d(const std::string &name, const A &a)
+{
+    keep(name, a.data(), sizeof(*a.data()) * a.num_elements());
+}
+template <typename V> static void keepvec(const std::string &name, const V *v)
+{
+    if (v) keep(name, v->data(), sizeof((*v)[0]) * v->size());
+}
+
+extern "C" void DESREF_CAT(__wrap_, DESREF_NN)(const Param &param, Variables &var,
+                                               const Barycentric_transformation &bary,
+                                               const array_t &old_coord, const conn_t &old_conn,
+                                               const bool is_surface)
+{
+    const std::string k = is_surface ? "nn1_" : "nn0_";
+    if (g_capture) {
+        keep2d(k + "old_coord", old_coord);
+        keep2d(k + "old_conn", old_conn);
+        keep2d(k + "new_coord", *var.coord);
+        if (is_surface) {
+            keep2d(k + "new_conn", *var.connectivity_surface);
+            // the areas remesh() gave bary_surface (remeshing.cxx:2889-2892): the same function
+            // on the same coordinates
+            std::vector<double> area(old_conn.size());
+            for (int i = 0; i < old_conn.size(); ++i)
+                area[i] = compute_area_facet(old_coord.view_const(old_conn[i]));
+            keep(k + "old_size", area.data(), sizeof(double) * area.size());
+            keepvec(k + "src_edvacc_surf", var.surfinfo.edvacc_surf);
+        } else {
+            keep2d(k + "new_conn", *var.connectivity);
+            keepvec(k + "old_size", var.volume);
+            keepvec(k + "src_plstrain", var.plstrain);
+            keepvec(k + "src_delta_plstrain", var.delta_plstrain);
+            keep2d(k + "src_strain", *var.strain);
+            keepvec(k + "src_radiogenic_source", var.radiogenic_source);
+            keepvec(k + "src_dyn_fric_coeff", var.dyn_fric_coeff);
+            keepvec(k + "src_state_variable", var.state_variable);
+            keepvec(k + "src_volume_old", var.volume_old);
+            keep2d(k + "src_stress", *var.stress);
+            keepvec(k + "src_stressyy", var.stressyy);
+            keepvec(k + "src_spr_blend_weight", var.spr_blend_weight);
+            keepvec(k + "src_spr_p_ref_old", var.spr_p_ref_old);
+        }
+    }
+    DESREF_CAT(__real_, DESREF_NN)(param, var, bary, old_coord, old_conn, is_surface);
+    if (g_capture) {
+        if (is_surface) {
+            keepvec(k + "dst_edvacc_surf", var.surfinfo.edvacc_surf);
+        } else {
+            keepvec(k + "is_changed", var.remesh_is_changed);
+            keepvec(k + "dst_plstrain", var.plstrain);
+            keepvec(k + "dst_delta_plstrain", var.delta_plstrain);
+            keep2d(k + "dst_strain", *var.strain);
+            keepvec(k + "dst_radiogenic_source", var.radiogenic_source);
+            keepvec(k + "dst_dyn_fric_coeff", var.dyn_fric_coeff);
+            keepvec(k + "dst_state_variable", var.state_variable);
+            keepvec(k + "dst_volume_old", var.volume_old);
+            keep2d(k + "dst_stress", *var.stress);
+            keepvec(k + "dst_stressyy", var.stressyy);
+            keepvec(k + "dst_spr_blend_weight", var.spr_blend_weight);
+            keepvec(k + "dst_spr_p_ref_old", var.spr_p_ref_old);
+        }
+    }
+}
+
+extern "C" void DESREF_CAT(__wrap_, DESREF_BRC)(const Param &param, Variables &var,
+                                                const Barycentric_transformation &bary,
+                                                const array_t &old_coord, const conn_t &old_conn)
+{
+    const std::string k = "brc_";
+    if (g_capture) {
+        keep2d(k + "old_coord", old_coord);
+        keep2d(k + "old_conn", old_conn);
+        keep2d(k + "new_coord", *var.coord);
+        keepvec(k + "old_size", var.volume);
+        keepvec(k + "new_bcflag", var.bcflag);
+        // the OLD mesh's node -> element lists (remesh() rebuilds them after this call)
+        keep(k + "old_support_arr", var.support.arr_data.data(), sizeof(int) * size_t(old_conn.size()) * NODES_PER_ELEM);
+        keep(k + "old_support_idx", var.support.idx_data.data(), sizeof(int) * (size_t(old_coord.size()) + 1));
+        keepvec(k + "src_temperature", var.temperature);
+        keepvec(k + "src_ppressure", var.ppressure);
+        keepvec(k + "src_dppressure", var.dppressure);
+        keep2d(k + "src_vel", *var.vel);
+        keep2d(k + "src_coord0", *var.coord0);
+        if (var.stress_n) keep2d(k + "src_stress_n", *var.stress_n);
+    }
+    DESREF_CAT(__real_, DESREF_BRC)(param, var, bary, old_coord, old_conn);
+    if (g_capture) {
+        keepvec(k + "dst_temperature", var.temperature);
+        keepvec(k + "dst_ppressure", var.ppressure);
+        keepvec(k + "dst_dppressure", var.dppressure);
+        keep2d(k + "dst_vel", *var.vel);
+        keep2d(k + "dst_coord0", *var.coord0);
+        if (var.stress_n) keep2d(k + "dst_stress_n", *var.stress_n);
+    }
+}
+
 namespace {
 Param *g_param = nullptr;
 Variables *g_var = nullptr;
@@ -531,6 +655,23 @@ int desref_get_mesh_param(const char *name, double *out)
 }
 
 double desref_l2_residual() { return g_var->l2_residual; }
+
+// The reference's own remesh() (remeshing.cxx:2869) on the current state; with
+// desref_capture_transfers(1) the inputs and outputs of its field-transfer calls are recorded.
+int desref_capture_transfers(int on) { g_capture = on; if (!on) g_captured.clear(); return 0; }
+int desref_remesh(int bad_quality) { remesh(*g_param, *g_var, bad_quality); return 0; }
+long desref_captured_nbytes(const char *name)
+{
+    auto it = g_captured.find(name);
+    return it == g_captured.end() ? -1 : long(it->second.size());
+}
+int desref_captured_get(const char *name, void *out, long nbytes)
+{
+    auto it = g_captured.find(name);
+    if (it == g_captured.end() || long(it->second.size()) != nbytes) return -1;
+    std::memcpy(out, it->second.data(), nbytes);
+    return 0;
+}
 
 // Run n explicit steps; returns wall seconds.
 double desref_step(int n)

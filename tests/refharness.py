@@ -87,6 +87,45 @@ class Ref:
         assert self.lib.desref_get_matvec(name.encode(), a.ctypes.data, n) == 0, name
         return a
 
+    # ---- remesh field transfer ----
+    _CAPTURED_INT = ("_conn", "is_changed", "bcflag", "support_arr", "support_idx")
+
+    def remesh_captured(self, bad_quality=1):
+        """The reference's own remesh() (remeshing.cxx:2869) on the current state, with the inputs
+        and outputs of its nearest_neighbor_interpolation / barycentric_node_interpolation calls
+        recorded by the harness: a dict name -> flat array (nn0_ elements, nn1_ top surface,
+        brc_ nodes; old_* / new_* meshes, src_* / dst_* fields in the reference's own layout)."""
+        L = self.lib
+        L.desref_captured_nbytes.argtypes = [C.c_char_p]; L.desref_captured_nbytes.restype = C.c_long
+        L.desref_captured_get.argtypes = [C.c_char_p, C.c_void_p, C.c_long]
+        L.desref_capture_transfers(1)
+        assert L.desref_remesh(int(bad_quality)) == 0
+        out = {}
+        for pre, names in (("nn0_", ("old_coord", "old_conn", "new_coord", "new_conn", "old_size", "is_changed")
+                            + tuple(d + f for d in ("src_", "dst_") for f in (
+                                "plstrain", "delta_plstrain", "strain", "radiogenic_source", "dyn_fric_coeff",
+                                "state_variable", "volume_old", "stress", "stressyy", "spr_blend_weight",
+                                "spr_p_ref_old"))),
+                           ("nn1_", ("old_coord", "old_conn", "new_coord", "new_conn", "old_size",
+                                     "src_edvacc_surf", "dst_edvacc_surf")),
+                           ("brc_", ("old_coord", "old_conn", "new_coord", "old_size", "new_bcflag",
+                                     "old_support_arr", "old_support_idx")
+                            + tuple(d + f for d in ("src_", "dst_") for f in (
+                                "temperature", "ppressure", "dppressure", "vel", "coord0", "stress_n")))):
+            for nm in names:
+                key = pre + nm
+                n = L.desref_captured_nbytes(key.encode())
+                if n < 0:
+                    continue
+                isint = any(nm.endswith(t) for t in self._CAPTURED_INT)
+                dt = np.uint32 if nm.endswith("bcflag") else (np.int32 if isint else np.float64)
+                a = np.empty(n // np.dtype(dt).itemsize, dtype=dt)
+                if n:
+                    assert L.desref_captured_get(key.encode(), a.ctypes.data, n) == 0, key
+                out[key] = a
+        L.desref_capture_transfers(0)
+        return out
+
     def call(self, fn):
         assert self.lib.desref_call(fn.encode()) == 0, fn
 
