@@ -115,6 +115,21 @@ class DesFrame(C.Structure):
                     "density", "mesh_quality", "material", "force")])
 
 
+class DesTransferMeshes(C.Structure):
+    _fields_ = [("old_nnode", C.c_int), ("old_coord", _DP), ("old_ncell", C.c_int), ("old_conn", _IP),
+                ("old_size", _DP), ("new_nnode", C.c_int), ("new_coord", _DP), ("new_ncell", C.c_int),
+                ("new_conn", _IP)]
+
+
+class DesTransferField(C.Structure):
+    _fields_ = [("src", _DP), ("dst", _DP), ("ncomp", C.c_int)]
+
+
+class DesTransferStats(C.Structure):
+    _fields_ = [("nchanged", C.c_int), ("nsample", C.c_int), ("n_on_face", C.c_int), ("n_outside", C.c_int),
+                ("search_seconds", C.c_double), ("acm_seconds", C.c_double), ("field_seconds", C.c_double)]
+
+
 class DesQualityParam(C.Structure):
     """Param.mesh members bad_mesh_quality reads (remeshing.cxx:2752-2866)."""
     _fields_ = [("smallest_size", C.c_double), ("resolution", C.c_double),
@@ -154,6 +169,7 @@ ABI_SYMBOLS = [
     "des_gpu_download_frame", "des_host_alloc", "des_host_free",
     "des_gpu_build_support", "des_gpu_find_boundary_facets", "des_host_boundary_flags",
     "des_host_boundary_nodes", "des_host_bucket_facets", "des_host_surface_topology",
+    "des_remesh_transfer_cells", "des_remesh_transfer_nodes",
 ]
 
 _lib = None
@@ -231,6 +247,10 @@ def load_library():
                                          C.POINTER(C.c_int * (DES_NBDRY + 1)), _IP, _IP]
     L.des_host_surface_topology.argtypes = [C.c_int, C.c_int, _IP, _DP, _IP, _IP, C.c_int, _IP, _IP,
                                             C.c_int, _IP, _IP, _IP, _IP, _IP]
+    L.des_remesh_transfer_cells.argtypes = [C.c_int, C.POINTER(DesTransferMeshes), C.c_int, C.c_int,
+                                            C.POINTER(DesTransferField), _IP, C.POINTER(DesTransferStats)]
+    L.des_remesh_transfer_nodes.argtypes = [C.c_int, C.POINTER(DesTransferMeshes), _IP, _IP, C.c_int,
+                                            C.POINTER(DesTransferField), _IP, _DP, C.POINTER(DesTransferStats)]
     L.des_gpu_check_nan.argtypes = [H, C.POINTER(C.c_int)]
     L.des_gpu_average_fields.argtypes = [H, C.c_int]
     L.des_gpu_download_averages.argtypes = [H, _DP, _DP, _DP, _DP]
@@ -238,7 +258,7 @@ def load_library():
     L.des_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     L.des_host_free.argtypes = [C.c_void_p]
     for i, st in enumerate((DesParam, DesMesh, DesState, DesDtReductions, DesQualityParam, DesQuality,
-                            DesFrame)):
+                            DesFrame, DesTransferMeshes, DesTransferField, DesTransferStats)):
         if L.des_abi_sizeof(i) != C.sizeof(st):
             raise ImportError("ABI mismatch: %s is %d bytes in the library, %d in core.py"
                               % (st.__name__, L.des_abi_sizeof(i), C.sizeof(st)))
@@ -370,6 +390,71 @@ def build_topology(coord, conn, segment, segflag, device=0):
     m.update(host_surface_topology(N, bn[5], coord[0], idx, arr, cs))
     m["seg_elem"], m["seg_facet"] = se, sf
     return m
+
+
+def _transfer_args(old_coord, old_conn, old_size, new_coord, new_conn, fields, n_old, n_new):
+    """ctypes views of the two meshes and the field list; returns (meshes, field array, outputs, keep-alive)."""
+    oc = np.ascontiguousarray(old_coord, dtype=np.float64).reshape(-1)
+    ocn = np.ascontiguousarray(old_conn, dtype=np.int32).reshape(-1)
+    osz = np.ascontiguousarray(old_size, dtype=np.float64).reshape(-1)
+    nc = np.ascontiguousarray(new_coord, dtype=np.float64).reshape(-1)
+    keep = [oc, ocn, osz, nc]
+    m = DesTransferMeshes(oc.size // 3, _ptr(oc, C.c_double), ocn.size // 4, _ptr(ocn, C.c_int),
+                          _ptr(osz, C.c_double), nc.size // 3, _ptr(nc, C.c_double), 0, None)
+    if osz.size != m.old_ncell:
+        raise ValueError("old_size has %d entries for %d old cells" % (osz.size, m.old_ncell))
+    if new_conn is not None:
+        ncn = np.ascontiguousarray(new_conn, dtype=np.int32).reshape(-1)
+        keep.append(ncn)
+        m.new_ncell, m.new_conn = ncn.size // 4, _ptr(ncn, C.c_int)
+    no, nn = n_old(m), n_new(m)
+    arr = (DesTransferField * max(len(fields), 1))()
+    out = {}
+    for i, (name, src) in enumerate(fields.items()):
+        src = np.ascontiguousarray(src, dtype=np.float64).reshape(-1)
+        if src.size % no:
+            raise ValueError("field %s: %d values for %d old items" % (name, src.size, no))
+        w = src.size // no
+        dst = np.full(w * nn, np.nan)
+        keep.append(src)
+        out[name] = dst
+        arr[i] = DesTransferField(_ptr(src, C.c_double), _ptr(dst, C.c_double), w)
+    return m, arr, out, keep
+
+
+def remesh_transfer_cells(old_coord, old_conn, old_size, new_coord, new_conn, fields, is_surface=False, device=0):
+    """nearest_neighbor_interpolation (nn-interpolation.cxx:661-702) on the device: element fields
+    (or, is_surface, top-facet fields) from the old mesh to the new one.  Arrays in the reference's
+    SoA layouts; fields: {name: [ncomp][old cells]}.  Returns ({name: [ncomp][new cells]},
+    is_changed, stats)."""
+    L = load_library()
+    m, arr, out, keep = _transfer_args(old_coord, old_conn, old_size, new_coord, new_conn, fields,
+                                       lambda m: m.old_ncell, lambda m: m.new_ncell)
+    changed = np.empty(m.new_ncell, dtype=np.int32)
+    st = DesTransferStats()
+    _ck_plain(L.des_remesh_transfer_cells(device, C.byref(m), int(bool(is_surface)), len(fields), arr,
+                                          _ptr(changed, C.c_int), C.byref(st)), "des_remesh_transfer_cells")
+    return out, changed, st
+
+
+def remesh_transfer_nodes(old_coord, old_conn, old_size, old_support_idx, old_support_arr, new_coord, fields,
+                          device=0):
+    """barycentric_node_interpolation (brc-interpolation.cxx:345-423) on the device: nodal fields from
+    the old mesh to the new nodes.  Returns ({name: [ncomp][new nodes]}, el, brc [n][4], stats)."""
+    L = load_library()
+    m, arr, out, keep = _transfer_args(old_coord, old_conn, old_size, new_coord, None, fields,
+                                       lambda m: m.old_nnode, lambda m: m.new_nnode)
+    sidx = np.ascontiguousarray(old_support_idx, dtype=np.int32)
+    sarr = np.ascontiguousarray(old_support_arr, dtype=np.int32)
+    if sidx.size != m.old_nnode + 1 or sarr.size != 4 * m.old_ncell:
+        raise ValueError("support lists do not match the old mesh")
+    el = np.empty(m.new_nnode, dtype=np.int32)
+    brc = np.empty(4 * m.new_nnode)
+    st = DesTransferStats()
+    _ck_plain(L.des_remesh_transfer_nodes(device, C.byref(m), _ptr(sidx, C.c_int), _ptr(sarr, C.c_int),
+                                          len(fields), arr, _ptr(el, C.c_int), _ptr(brc, C.c_double),
+                                          C.byref(st)), "des_remesh_transfer_nodes")
+    return out, el, brc.reshape(-1, 4), st
 
 
 def make_param(**kw):

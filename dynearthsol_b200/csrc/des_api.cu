@@ -1801,6 +1801,9 @@ int des_abi_sizeof(int which)
     case 4: return int(sizeof(DesQualityParam));
     case 5: return int(sizeof(DesQuality));
     case 6: return int(sizeof(DesFrame));
+    case 7: return int(sizeof(DesTransferMeshes));
+    case 8: return int(sizeof(DesTransferField));
+    case 9: return int(sizeof(DesTransferStats));
     default: return -1;
     }
 }

@@ -478,7 +478,8 @@ int des_remesh_transfer_nodes(int device, const DesTransferMeshes *m, const int 
                               int *el, double *brc, DesTransferStats *stats);
 
 /* sizeof() of the ABI structs as compiled, so a foreign-language binding can verify its
- * own layout: which = 0 DesParam, 1 DesMesh, 2 DesState, 3 DesDtReductions, 4 DesQualityParam, 5 DesQuality */
+ * own layout: which = 0 DesParam, 1 DesMesh, 2 DesState, 3 DesDtReductions, 4 DesQualityParam, 5 DesQuality,
+ * 6 DesFrame, 7 DesTransferMeshes, 8 DesTransferField, 9 DesTransferStats */
 int des_abi_sizeof(int which);
 
 /* ---- instrumentation ----------------------------------------------------------------- */

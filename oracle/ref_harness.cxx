@@ -149,6 +149,13 @@ extern "C" void DESREF_CAT(__real_, DESREF_BRC)(const Param &, Variables &, cons
                                                 const array_t &, const conn_t &);
 static int g_capture = 0;
 static std::map<std::string, std::vector<char>> g_captured;
+// conn_t has four columns, a surface facet uses three: the fourth is never written by the
+// reference (uninitialised); recorded as zeros so that the fixtures are reproducible
+static void zero_fourth_column(const std::string &name)
+{
+    std::vector<char> &v = g_captured[name];
+    std::fill(v.begin() + v.size() / 4 * 3, v.end(), 0);
+}
 static void keep(const std::string &name, const void *p, size_t nbytes)
 {
     const char *c = static_cast<const char *>(p);
@@ -163,6 +170,7 @@ template <typename V> static void keepvec(const std::string &name, const V *v)
     if (v) keep(name, v->data(), sizeof((*v)[0]) * v->size());
 }
 
+#ifndef DESREF_NO_RECORDER   /* oracle/Makefile: the wrapcheck build links bridge/des_transfer_wrap.cxx here instead */
 extern "C" void DESREF_CAT(__wrap_, DESREF_NN)(const Param &param, Variables &var,
                                                const Barycentric_transformation &bary,
                                                const array_t &old_coord, const conn_t &old_conn,
@@ -175,6 +183,8 @@ extern "C" void DESREF_CAT(__wrap_, DESREF_NN)(const Param &param, Variables &va
         keep2d(k + "new_coord", *var.coord);
         if (is_surface) {
             keep2d(k + "new_conn", *var.connectivity_surface);
+            zero_fourth_column(k + "old_conn");
+            zero_fourth_column(k + "new_conn");
             // the areas remesh() gave bary_surface (remeshing.cxx:2889-2892): the same function
             // on the same coordinates
             std::vector<double> area(old_conn.size());
@@ -250,6 +260,8 @@ extern "C" void DESREF_CAT(__wrap_, DESREF_BRC)(const Param &param, Variables &v
         if (var.stress_n) keep2d(k + "dst_stress_n", *var.stress_n);
     }
 }
+
+#endif
 
 namespace {
 Param *g_param = nullptr;
@@ -660,6 +672,34 @@ double desref_l2_residual() { return g_var->l2_residual; }
 // desref_capture_transfers(1) the inputs and outputs of its field-transfer calls are recorded.
 int desref_capture_transfers(int on) { g_capture = on; if (!on) g_captured.clear(); return 0; }
 int desref_remesh(int bad_quality) { remesh(*g_param, *g_var, bad_quality); return 0; }
+// The reference's barycentric_node_interpolation (brc-interpolation.cxx:345) from the CURRENT
+// mesh and nodal fields onto `new_nnode` arbitrary points (tests put them where the capped
+// breadth-first search, the on-a-face and the outside-the-domain branches are taken).  The
+// call goes through the recorder above; the model itself is left untouched.
+int desref_transfer_nodes_case(int new_nnode, const double *new_coord, const unsigned *new_bcflag)
+{
+    Variables v2 = *g_var;      // shallow: the pointers replaced below are the ones the call re-news
+    v2.nnode = new_nnode;
+    v2.coord = new array_t(new_nnode);
+    std::memcpy(v2.coord->data(), new_coord, sizeof(double) * 3 * size_t(new_nnode));
+    v2.bcflag = new uint_vec(new_bcflag, new_bcflag + new_nnode);
+    v2.temperature = new double_vec(*g_var->temperature);
+    v2.ppressure = new double_vec(*g_var->ppressure);
+    v2.dppressure = new double_vec(*g_var->dppressure);
+    v2.vel = new array_t(g_var->nnode);
+    std::memcpy(v2.vel->data(), g_var->vel->data(), sizeof(double) * 3 * size_t(g_var->nnode));
+    v2.coord0 = new array_t(g_var->nnode);
+    std::memcpy(v2.coord0->data(), g_var->coord0->data(), sizeof(double) * 3 * size_t(g_var->nnode));
+    v2.stress_n = nullptr;
+    v2.stressyy_n = nullptr;
+    {
+        Barycentric_transformation bary(*g_var->coord, *g_var->connectivity, *g_var->volume);
+        barycentric_node_interpolation(*g_param, v2, bary, *g_var->coord, *g_var->connectivity);
+    }
+    delete v2.coord; delete v2.bcflag; delete v2.temperature; delete v2.ppressure;
+    delete v2.dppressure; delete v2.vel; delete v2.coord0;
+    return 0;
+}
 long desref_captured_nbytes(const char *name)
 {
     auto it = g_captured.find(name);

@@ -144,3 +144,21 @@ int hostcheck_knn(int npts, const double *pts, int nq, const double *q, int k, i
     return 0;
 }
 }
+
+#ifdef HOSTCHECK_AS_ABI
+// oracle/Makefile's wrapcheck build only: the two entry points bridge/des_transfer_wrap.cxx calls,
+// answered by the host loops above, so that the wrap file's handling of `Variables` can be run
+// against the reference where there is no GPU.  The product library never contains this.
+extern "C" {
+int des_remesh_transfer_cells(int, const DesTransferMeshes *m, int is_surface, int nfields,
+                              const DesTransferField *fields, int *is_changed, DesTransferStats *stats)
+{
+    return hostcheck_transfer_cells(m, is_surface, nfields, fields, is_changed, stats, nullptr);
+}
+int des_remesh_transfer_nodes(int, const DesTransferMeshes *m, const int *sup_idx, const int *sup_arr, int nfields,
+                              const DesTransferField *fields, int *el, double *brc, DesTransferStats *stats)
+{
+    return hostcheck_transfer_nodes(m, sup_idx, sup_arr, nfields, fields, el, brc, stats);
+}
+}
+#endif

@@ -14,10 +14,10 @@ def available():
 class Ref:
     """One reference model per process (the reference keeps static state)."""
 
-    def __init__(self, cfg_path, workdir=None, fast_init=False):
+    def __init__(self, cfg_path, workdir=None, fast_init=False, lib=None):
         # fast_init: bench.py's CPU arm on meshes the reference's O(nseg * nelem) boundary-facet
         # search cannot initialise (oracle/ref_harness.cxx: desref_fast_init); never for fixtures
-        self.lib = C.CDLL(LIB)
+        self.lib = C.CDLL(lib or LIB)
         L = self.lib
         if fast_init:
             L.desref_fast_init(1)
@@ -96,10 +96,25 @@ class Ref:
         recorded by the harness: a dict name -> flat array (nn0_ elements, nn1_ top surface,
         brc_ nodes; old_* / new_* meshes, src_* / dst_* fields in the reference's own layout)."""
         L = self.lib
-        L.desref_captured_nbytes.argtypes = [C.c_char_p]; L.desref_captured_nbytes.restype = C.c_long
-        L.desref_captured_get.argtypes = [C.c_char_p, C.c_void_p, C.c_long]
         L.desref_capture_transfers(1)
         assert L.desref_remesh(int(bad_quality)) == 0
+        return self._captured()
+
+    def transfer_nodes_captured(self, new_coord, new_bcflag):
+        """The reference's barycentric_node_interpolation from the current mesh and nodal fields onto
+        arbitrary points new_coord ([3][n] flat), recorded like remesh_captured: the brc_ entries."""
+        L = self.lib
+        new_coord = np.ascontiguousarray(new_coord, dtype=np.float64)
+        new_bcflag = np.ascontiguousarray(new_bcflag, dtype=np.uint32)
+        L.desref_transfer_nodes_case.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.desref_capture_transfers(1)
+        assert L.desref_transfer_nodes_case(new_bcflag.size, new_coord.ctypes.data, new_bcflag.ctypes.data) == 0
+        return {k: v for k, v in self._captured().items() if k.startswith("brc_")}
+
+    def _captured(self):
+        L = self.lib
+        L.desref_captured_nbytes.argtypes = [C.c_char_p]; L.desref_captured_nbytes.restype = C.c_long
+        L.desref_captured_get.argtypes = [C.c_char_p, C.c_void_p, C.c_long]
         out = {}
         for pre, names in (("nn0_", ("old_coord", "old_conn", "new_coord", "new_conn", "old_size", "is_changed")
                             + tuple(d + f for d in ("src_", "dst_") for f in (

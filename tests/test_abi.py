@@ -36,7 +36,8 @@ def test_header_symbols_exported():
 def test_struct_sizes_match():
     L = core.load_library()
     for i, st in enumerate((core.DesParam, core.DesMesh, core.DesState, core.DesDtReductions,
-                            core.DesQualityParam, core.DesQuality, core.DesFrame)):
+                            core.DesQualityParam, core.DesQuality, core.DesFrame, core.DesTransferMeshes,
+                            core.DesTransferField, core.DesTransferStats)):
         assert L.des_abi_sizeof(i) == C.sizeof(st)
     assert L.des_abi_sizeof(99) == -1
 
