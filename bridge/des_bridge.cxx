@@ -12,6 +12,7 @@
 #include "parameters.hpp"
 #include "matprops.hpp"
 #include "markerset.hpp"
+#include "phasechanges.hpp"
 #include "output.hpp"
 #include "remeshing.hpp"
 #include "utils.hpp"
@@ -28,6 +29,13 @@ struct DesBridge {
     std::vector<int> flat_markers;
     std::vector<std::vector<int> > flat_facets;
     double avg_time0 = 0;       // Output::time0 of the running averaging interval
+    // device-resident markers (des_gpu_upload_markers): stale after every host change to the
+    // material marker set -- init / remesh (des_bridge_upload), the surface-marker routines and the
+    // host phase_changes (des_bridge_markers_changed)
+    bool markers_stale = true;
+    int ndev = 1;
+    std::vector<int> mk_elem, mk_mattype, mk_changed, mk_new, mk_hyd, hyd_count;
+    std::vector<double> mk_eta;
 };
 
 namespace {
@@ -134,6 +142,7 @@ void state_pointers(DesState &s, const Variables &var, bool all)
 
 int des_bridge_upload(DesBridge *b, const Param &param, const Variables &var)
 {
+    b->markers_stale = true;
     DesMesh m;
     std::memset(&m, 0, sizeof(m));
     m.nnode = var.nnode; m.nelem = var.nelem;
@@ -210,6 +219,7 @@ DesBridge *des_bridge_create(const Param &param, const Variables &var, int devic
         for (const char *q = s; *q; ) { devs.push_back(std::atoi(q)); while (*q && *q != ',') ++q; if (*q) ++q; }
         ndev = int(devs.size());
     }
+    b->ndev = (ndev > 1 || !devs.empty()) ? std::max(ndev, 2) : 1;   // > 1: a group handle (even over one device)
     int rc = (ndev > 1 || !devs.empty())
         ? des_gpu_create_multi(&b->p, ndev, devs.empty() ? nullptr : devs.data(), &b->h)
         : des_gpu_create(&b->p, device, &b->h);
@@ -401,8 +411,79 @@ int des_bridge_download(DesBridge *b, Variables &var, int what)
     return 0;
 }
 
+// phase_changes (dynearthsol.cxx:885-887) with the marker lookups on the device: the markers'
+// element / shape-function weights / rock type stay resident between host changes
+// (des_gpu_upload_markers), des_gpu_phase_changes reads the resident coordinates and temperature,
+// keeps the device's rock types and elemmarkers current and returns the markers that changed; here
+// they are written into the reference's MarkerSet and elemmarkers exactly as phasechanges.cxx:143-147
+// does, and the hydration block (:160-176, host marker bookkeeping) follows.  No geometry
+// download, no elemmarkers upload.  A handle over several devices, or DES_BRIDGE_PHASE=ref, takes
+// the reference's own phase_changes on downloaded fields.
+int des_bridge_phase_changes(DesBridge *b, const Param &param, Variables &var)
+{
+    if (param.mat.nmat == 1 || param.mat.phase_change_option == 0) return 0;      // phasechanges.cxx:111
+    static const bool want_ref = std::getenv("DES_BRIDGE_PHASE") && std::strcmp(std::getenv("DES_BRIDGE_PHASE"), "ref") == 0;
+    const int opt = param.mat.phase_change_option;
+    if (want_ref || b->ndev > 1 || (opt != 1 && opt != 101)) {
+        int rc = des_bridge_download(b, var, DES_DL_GEOMETRY);
+        if (rc) return rc;
+        phase_changes(param, var);
+        return des_bridge_markers_changed(b, param, var);
+    }
+    MarkerSet &ms = *var.markersets[0];
+    const int n = ms.get_nmarkers();
+    int rc;
+    if (b->markers_stale) {
+        b->mk_elem.resize(n); b->mk_mattype.resize(n); b->mk_eta.resize(size_t(4) * std::max(n, 1));
+        for (int m = 0; m < n; ++m) {
+            b->mk_elem[m] = ms.get_elem(m);
+            b->mk_mattype[m] = ms.get_mattype(m);
+            for (int i = 0; i < NODES_PER_ELEM; ++i) b->mk_eta[size_t(i) * n + m] = ms.get_eta(m)[i];
+        }
+        if ((rc = des_gpu_upload_markers(b->h, n, n, b->mk_elem.data(), b->mk_eta.data(), b->mk_mattype.data())))
+            return fail(b, rc, "upload_markers");
+        b->markers_stale = false;
+    }
+    const int *hyd = nullptr;
+    if (var.hydrous_elemmarkers) {
+        b->hyd_count.resize(var.nelem);
+        for (int e = 0; e < var.nelem; ++e) b->hyd_count[e] = (*var.hydrous_elemmarkers)[e][0];
+        hyd = b->hyd_count.data();
+    }
+    b->mk_changed.resize(std::max(n, 1)); b->mk_new.resize(std::max(n, 1)); b->mk_hyd.resize(std::max(n, 1));
+    int nchanged = 0;
+    if ((rc = des_gpu_phase_changes(b->h, opt, hyd, n, &nchanged, b->mk_changed.data(), b->mk_new.data(),
+                                    b->mk_hyd.data())))
+        return fail(b, rc, "phase_changes");
+    for (int k = 0; k < nchanged; ++k) {            // phasechanges.cxx:143-147
+        const int m = b->mk_changed[k], e = ms.get_elem(m), current_mt = ms.get_mattype(m), new_mt = b->mk_new[k];
+        ms.set_mattype(m, new_mt);
+        --(*var.elemmarkers)[e][current_mt];
+        ++(*var.elemmarkers)[e][new_mt];
+    }
+    if (opt == 1)
+        for (int m = 0; m < n; ++m) ms.set_tmp(m, b->mk_hyd[m]);                  // :131
+    if (param.control.has_hydration_processes) {    // :160-176: a hydrous marker where one dehydrated
+        MarkerSet &hydms = *var.markersets[var.hydrous_marker_index];
+        auto &hydem = *var.hydrous_elemmarkers;
+        for (int e = 0; e < var.nelem; ++e) {
+            const int nmarkers = (*var.markers_in_elem)[e].size();
+            for (int i = 0; i < nmarkers; ++i) {
+                const int m = (*var.markers_in_elem)[e][i];
+                if (ms.get_tmp(m) == 0) continue;
+                const int el = ms.get_elem(m);
+                ConstShapefnAccessor eta = ms.get_eta(m);
+                hydms.append_marker(eta, el, 0, 0., 0., 0., 0., 0.);
+                ++hydem[el][0];
+            }
+        }
+    }
+    return 0;
+}
+
 int des_bridge_markers_changed(DesBridge *b, const Param &param, const Variables &var)
 {
+    b->markers_stale = true;
     flatten_markers(b, param, var);
     int rc = des_gpu_upload_elemmarkers(b->h, b->flat_markers.data());
     if (rc) return fail(b, rc, "upload_elemmarkers");

@@ -17,6 +17,7 @@
 #include "geometry.hpp"
 #include "input.hpp"
 #include "matprops.hpp"
+#include "markerset.hpp"
 #include "output.hpp"
 #include "phasechanges.hpp"
 #include "remeshing.hpp"
@@ -108,11 +109,15 @@ int main(int argc, const char* argv[])
 
         const int slow_updates_interval = 10;
         if (var.steps % slow_updates_interval == 0) {
-            if (param.mat.phase_change_option != 0 && param.mat.nmat > 1) {
-                // [B200] phase_changes reads coord and temperature on the host
-                des_bridge_download(gpu, var, DES_DL_GEOMETRY);
-                phase_changes(param, var);
-                des_bridge_markers_changed(gpu, param, var);
+            // [B200] phase_changes(param, var); var.mat->refresh_elem_cache();   (dynearthsol.cxx:885-887)
+            // -- the marker lookups run on the device-resident markers, coordinates and temperature
+            if (des_bridge_phase_changes(gpu, param, var)) return 1;
+            if (param.control.has_hydration_processes) {
+                // advect_hydrous_markers (dynearthsol.cxx:889-892) stays host code: it walks the
+                // hydrous marker set through coord, volume and the support lists
+                if (des_bridge_download(gpu, var, DES_DL_GEOMETRY)) return 1;
+                advect_hydrous_markers(param, var, 10*var.dt, *var.markersets[var.hydrous_marker_index],
+                                       *var.hydrous_elemmarkers);
             }
             // [B200] var.dt = compute_dt(param, var);   (dynearthsol.cxx:893)
             var.dt = des_bridge_compute_dt(gpu, param, var);

@@ -170,6 +170,7 @@ ABI_SYMBOLS = [
     "des_gpu_build_support", "des_gpu_find_boundary_facets", "des_host_boundary_flags",
     "des_host_boundary_nodes", "des_host_bucket_facets", "des_host_surface_topology",
     "des_remesh_transfer_cells", "des_remesh_transfer_nodes",
+    "des_gpu_upload_markers", "des_gpu_phase_changes", "des_gpu_download_elemmarkers",
 ]
 
 _lib = None
@@ -251,6 +252,9 @@ def load_library():
                                             C.POINTER(DesTransferField), _IP, C.POINTER(DesTransferStats)]
     L.des_remesh_transfer_nodes.argtypes = [C.c_int, C.POINTER(DesTransferMeshes), _IP, _IP, C.c_int,
                                             C.POINTER(DesTransferField), _IP, _DP, C.POINTER(DesTransferStats)]
+    L.des_gpu_upload_markers.argtypes = [H, C.c_int, C.c_int, _IP, _DP, _IP]
+    L.des_gpu_phase_changes.argtypes = [H, C.c_int, _IP, C.c_int, _IP, _IP, _IP, _IP]
+    L.des_gpu_download_elemmarkers.argtypes = [H, _IP]
     L.des_gpu_check_nan.argtypes = [H, C.POINTER(C.c_int)]
     L.des_gpu_average_fields.argtypes = [H, C.c_int]
     L.des_gpu_download_averages.argtypes = [H, _DP, _DP, _DP, _DP]
@@ -633,6 +637,34 @@ class DesGpu:
         if a.size != self.nelem * self.param.nmat:
             raise ValueError("elemmarkers: expected nelem*nmat ints")
         self._ck(self.lib.des_gpu_upload_elemmarkers(self.h, _ptr(a, C.c_int)))
+
+    def upload_markers(self, elem, eta, mattype):
+        """markersets[0]: element, shape-function weights [4][n] and rock type of every marker."""
+        elem = np.ascontiguousarray(elem, dtype=np.int32)
+        mattype = np.ascontiguousarray(mattype, dtype=np.int32)
+        eta = np.ascontiguousarray(eta, dtype=np.float64).reshape(4, -1)
+        self._markers = elem.size
+        self._ck(self.lib.des_gpu_upload_markers(self.h, elem.size, eta.shape[1], _ptr(elem, C.c_int),
+                                               _ptr(eta, C.c_double), _ptr(mattype, C.c_int)))
+
+    def phase_changes(self, option=1, hydrous_count=None, cap=None):
+        """phase_changes (phasechanges.cxx:109) on the resident markers: (changed marker ids,
+        their new rock types, hyd_inc of every marker)."""
+        n = self._markers
+        cap = n if cap is None else cap
+        nch = C.c_int(0)
+        cm = np.empty(max(cap, 1), dtype=np.int32); ct = np.empty(max(cap, 1), dtype=np.int32)
+        hyd = np.empty(max(n, 1), dtype=np.int32)
+        hc = None if hydrous_count is None else np.ascontiguousarray(hydrous_count, dtype=np.int32)
+        self._ck(self.lib.des_gpu_phase_changes(self.h, option, None if hc is None else _ptr(hc, C.c_int), cap,
+                                              C.byref(nch), _ptr(cm, C.c_int), _ptr(ct, C.c_int), _ptr(hyd, C.c_int)))
+        k = min(nch.value, cap)
+        return cm[:k].copy(), ct[:k].copy(), hyd[:n], nch.value
+
+    def download_elemmarkers(self):
+        out = np.empty(self.nelem * self.param.nmat, dtype=np.int32)
+        self._ck(self.lib.des_gpu_download_elemmarkers(self.h, _ptr(out, C.c_int)))
+        return out.reshape(self.nelem, -1)
 
     def set_reorder(self, mode):
         """0 caller's order, 1 elements by smallest node, 2 Morton (nodes + elements; the mesh

@@ -122,6 +122,12 @@ struct DesGpu {
     // Output::average_fields accumulators (mesh-lifetime allocations, internal element order)
     double *avg_coord0 = nullptr;   // the element accumulators live in Dev (avg_stress, avg_strain0, avg_dpl)
     bool avg_valid = false;
+    // device-resident markers of the material marker set (des_markers.cuh; mesh-lifetime allocations)
+    int *mk_elem = nullptr, *mk_mattype = nullptr, *mk_changed = nullptr, *mk_pos = nullptr, *mk_hyd = nullptr,
+        *mk_out = nullptr;
+    double *mk_eta = nullptr;       // [4][mk_cap]
+    char *mk_scan_tmp = nullptr; size_t mk_scan_bytes = 0;
+    size_t mk_cap = 0; int mk_n = 0;
     int avg_pending = 0;        // 1 accumulate / 2 snapshot: deferred into the next E-B (with the rotation)
     // timing
     bool timing = false;
@@ -246,6 +252,8 @@ void free_mesh(DesGpu *h)
     h->send_buf = h->recv_buf = nullptr;
     h->avg_coord0 = nullptr;
     h->avg_valid = false;
+    h->mk_elem = h->mk_mattype = h->mk_changed = h->mk_pos = h->mk_hyd = h->mk_out = nullptr;
+    h->mk_eta = nullptr; h->mk_scan_tmp = nullptr; h->mk_scan_bytes = 0; h->mk_cap = 0; h->mk_n = 0;
     h->avg_pending = 0;
     h->eperm = h->einv = nullptr;
     h->h_einv.clear();
@@ -1964,3 +1972,4 @@ extern "C" int des_gpu_compute_dt_static(DesGpu *h, DesDtReductions *out)
 #include "des_topology_api.cuh"
 #include "des_frame.cuh"
 #include "des_transfer_api.cuh"
+#include "des_markers.cuh"

@@ -288,6 +288,31 @@ int des_gpu_average_fields(DesGpu *h, int first);
 int des_gpu_download_averages(DesGpu *h, double *coord0, double *strain0, double *stress_avg,
                               double *delta_plstrain_avg);
 
+/* ---- phase_changes on device-resident markers -------------------
+ * The arrays of the material marker set, markersets[0] (markerset.hpp:106-110): element, the
+ * four shape-function weights (shapefn SoA, component i of marker m at eta[i*stride + m]) and
+ * rock type of every marker.  Upload after init / restart / remesh and whenever host code has
+ * moved, added or removed markers (surface processes, replenishment); between those points the
+ * device keeps them, and des_gpu_phase_changes keeps the rock types current.  Single-device
+ * handles (a group handle answers DES_E_UNSUPPORTED: the host path stays). */
+int des_gpu_upload_markers(DesGpu *h, int nmarkers, int stride, const int *elem, const double *eta,
+                           const int *mattype);
+/* phase_changes (dynearthsol.cxx:885; phasechanges.cxx:109-158) with MarkerSet::get_ZPT
+ * (markerset.cxx:973-986) and ref_pressure (matprops.cxx:153-174) read from the resident
+ * coordinates and temperature: option 1 = simple_subduction (phasechanges.cxx:10-84), 101 = the
+ * custom template (which changes nothing); anything else DES_E_UNSUPPORTED (the reference's
+ * EXIT_CONFIG_VALUE).  hydrous_count [nelem] = (*var.hydrous_elemmarkers)[e][0], NULL = all zero.
+ * The device applies the changes to its rock types and elemmarkers counters (no
+ * des_gpu_upload_elemmarkers needed afterwards) and returns the markers that changed in ascending
+ * marker order: *nchanged of them, the first min(*nchanged, cap) in changed_marker /
+ * changed_mattype (the host then does set_mattype and moves its own elemmarkers counts,
+ * phasechanges.cxx:143-147).  hyd_inc [nmarkers] (may be NULL) receives what the reference stores
+ * with set_tmp (:131) for its hydration block (:160-176), which stays host code. */
+int des_gpu_phase_changes(DesGpu *h, int option, const int *hydrous_count, int cap, int *nchanged,
+                          int *changed_marker, int *changed_mattype, int *hyd_inc);
+/* the device's elemmarkers counters, [nelem][nmat] in the caller's element order */
+int des_gpu_download_elemmarkers(DesGpu *h, int *elemmarkers);
+
 /* ---- one output frame straight from the device ----------------
  * The arrays Output::_write (output.cxx:95-245) hands to BinaryOutput, already in the layout
  * BinaryOutput::write_array puts on disk (Array2D::pack_to, binaryio.cxx:151-166: [n][components])

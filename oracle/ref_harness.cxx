@@ -28,6 +28,7 @@
 #include "ic.hpp"
 #include "input.hpp"
 #include "matprops.hpp"
+#include "markerset.hpp"
 #include "mesh.hpp"
 #include "output.hpp"
 #include "remeshing.hpp"
@@ -567,6 +568,7 @@ int desref_set_int(const char *name, int val)
     else if (n == "has_water_loading") p.bc.has_water_loading = val;
     else if (n == "has_elastic_foundation") p.bc.has_elastic_foundation = val;
     else if (n == "steps") g_var->steps = val;
+    else if (n == "phase_change_option") p.mat.phase_change_option = val;
     else return -1;
     return 0;
 }
@@ -624,6 +626,7 @@ int desref_call(const char *fn)
     else if (f == "rotate_stress") rotate_stress(var, *var.stress, *var.strain);
     else if (f == "compute_dt") var.dt = compute_dt(param, var);
     else if (f == "calculate_residual_force") var.l2_residual = calculate_residual_force(var, *var.force_residual);
+    else if (f == "phase_changes") phase_changes(param, var);
     else if (f == "visc_all") {
         for (int e = 0; e < var.nelem; ++e) (*var.viscosity)[e] = var.mat->visc(e);
     }
@@ -700,6 +703,46 @@ int desref_transfer_nodes_case(int new_nnode, const double *new_coord, const uns
     delete v2.dppressure; delete v2.vel; delete v2.coord0;
     return 0;
 }
+// ---- the material marker set, markersets[0], through MarkerSet's own accessors ----------------
+int desref_marker_count() { return g_var->markersets[0]->get_nmarkers(); }
+// elem [n], eta [4][n], mattype [n], tmp [n] (what phase_changes leaves with set_tmp); NULL = skip
+int desref_markers_get(int *elem, double *eta, int *mattype, double *tmp)
+{
+    const MarkerSet &ms = *g_var->markersets[0];
+    const int n = ms.get_nmarkers();
+    for (int m = 0; m < n; ++m) {
+        if (elem) elem[m] = ms.get_elem(m);
+        if (mattype) mattype[m] = ms.get_mattype(m);
+        if (tmp) tmp[m] = ms.get_tmp(m);
+        if (eta) for (int i = 0; i < NODES_PER_ELEM; ++i) eta[size_t(i) * n + m] = ms.get_eta(m)[i];
+    }
+    return n;
+}
+// new rock types for every marker; elemmarkers is recounted from them (as create_elemmarkers does)
+int desref_markers_set_mattype(const int *mattype)
+{
+    MarkerSet &ms = *g_var->markersets[0];
+    const int n = ms.get_nmarkers(), nmat = g_param->mat.nmat;
+    for (int e = 0; e < g_var->nelem; ++e)
+        for (int k = 0; k < nmat; ++k) (*g_var->elemmarkers)[e][k] = 0;
+    for (int m = 0; m < n; ++m) {
+        if (mattype[m] < 0 || mattype[m] >= nmat) return -1;
+        ms.set_mattype(m, mattype[m]);
+        ++(*g_var->elemmarkers)[ms.get_elem(m)][mattype[m]];
+    }
+    return 0;
+}
+// (*var.hydrous_elemmarkers)[e][0]: set != 0 writes, else reads; -1 when the model has none
+int desref_hydrous_count(int *count, int set)
+{
+    if (!g_var->hydrous_elemmarkers) return -1;
+    for (int e = 0; e < g_var->nelem; ++e) {
+        if (set) (*g_var->hydrous_elemmarkers)[e][0] = count[e];
+        else count[e] = (*g_var->hydrous_elemmarkers)[e][0];
+    }
+    return 0;
+}
+
 long desref_captured_nbytes(const char *name)
 {
     auto it = g_captured.find(name);

@@ -11,6 +11,12 @@ SKIP = ("walltime_sec",)
 HEADER = 4096
 
 
+def is_int_field(name):
+    """integer arrays of a frame, for every marker set ("markerset", "hydrous-markerset", ...)"""
+    return (name in INT_FIELDS or name.endswith("markerset size")
+            or ("markerset." in name and name.rsplit(".", 1)[1] in ("elem", "mattype", "id", "genesis")))
+
+
 def read_frame(path):
     with open(path, "rb") as f:
         raw = f.read()
@@ -27,7 +33,7 @@ def read_frame(path):
     for (name, p), e in zip(pos, ends):
         if name in SKIP:
             continue
-        dt = np.int32 if name in INT_FIELDS else np.float64
+        dt = np.int32 if is_int_field(name) else np.float64
         out[name] = np.frombuffer(raw[p:e], dtype=dt)
     return out
 
@@ -41,7 +47,7 @@ def compare_frames(old, new, tol=1e-8):
         b = new[name]
         if a.shape != b.shape:
             bad.append("%s: size %d vs %d" % (name, a.size, b.size)); continue
-        if name in INT_FIELDS:
+        if is_int_field(name):
             if not np.array_equal(a, b):
                 bad.append(name + ": integer field differs")
             continue

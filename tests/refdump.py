@@ -92,6 +92,31 @@ def quality_cases(r, out):
     out["q2_result"] = np.asarray([code, idx], dtype=np.int32)
 
 
+def phase_case(r, out, seed=11):
+    """phase_changes (phasechanges.cxx:109-158) on the last dumped mesh: every marker gets a random
+    rock type, every node a random temperature, every element a random hydrous-marker count, so
+    that each arm of simple_subduction (:10-84) is taken by many markers; inputs and outputs as pc_*."""
+    if r.int("phase_change_option") == 0 or r.hydrous_count() is None:
+        return
+    rng = np.random.default_rng(seed)
+    n, ne, nmat = r.int("nnode"), r.int("nelem"), r.int("nmat")
+    elem, eta, mt, _ = r.markers()
+    mt0 = rng.choice(np.arange(nmat), size=mt.size, p=[0.2, 0.2, 0.2, 0.05, 0.2, 0.05] + [0.1 / (nmat - 6)] * (nmat - 6)).astype(np.int32)
+    r.set_marker_mattype(mt0)
+    T = rng.uniform(300.0, 1500.0, n)
+    r.set("temperature", T)
+    hyd = (rng.random(ne) < 0.5).astype(np.int32) * rng.integers(1, 4, ne).astype(np.int32)
+    r.hydrous_count(hyd)
+    out["pc_elem"], out["pc_eta"], out["pc_mattype0"] = elem, eta, mt0
+    out["pc_temperature"], out["pc_coord"], out["pc_hydrous"] = T, r.get("coord"), hyd
+    out["pc_elemmarkers0"] = r.get("elemmarkers")
+    out["pc_option"] = np.int32(r.int("phase_change_option"))
+    r.call("phase_changes")
+    _, _, mt1, tmp = r.markers()
+    out["pc_mattype1"], out["pc_tmp"] = mt1, tmp
+    out["pc_elemmarkers1"] = r.get("elemmarkers")
+
+
 def snapshot(r, out, prefix):
     for a in STATE_ARRAYS:
         out[prefix + a] = r.get(a)
@@ -156,6 +181,7 @@ def dump(cfg, out_path, steps=(1,), sets=(), by_function=True, perturb_at=None):
         for s in MESH_PARAMS:
             out["m_" + s] = np.float64(r.mesh_param(s))
         quality_cases(r, out)
+        phase_case(r, out)
         out["steps"] = np.asarray(sorted(steps), dtype=np.int32)
         np.savez_compressed(out_path, **out)
 

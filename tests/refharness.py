@@ -141,6 +141,28 @@ class Ref:
         L.desref_capture_transfers(0)
         return out
 
+    # ---- the material marker set (markersets[0]) and phase_changes ----
+    def markers(self):
+        """(elem [n], eta [4][n], mattype [n], tmp [n]) through MarkerSet's own accessors."""
+        L = self.lib
+        n = L.desref_marker_count()
+        elem = np.empty(n, np.int32); mt = np.empty(n, np.int32); eta = np.empty((4, n)); tmp = np.empty(n)
+        L.desref_markers_get.argtypes = [C.c_void_p] * 4
+        assert L.desref_markers_get(elem.ctypes.data, eta.ctypes.data, mt.ctypes.data, tmp.ctypes.data) == n
+        return elem, eta, mt, tmp
+
+    def set_marker_mattype(self, mattype):
+        mattype = np.ascontiguousarray(mattype, dtype=np.int32)
+        self.lib.desref_markers_set_mattype.argtypes = [C.c_void_p]
+        assert self.lib.desref_markers_set_mattype(mattype.ctypes.data) == 0
+
+    def hydrous_count(self, new=None):
+        """(*var.hydrous_elemmarkers)[e][0]; None when the model has no hydrous marker set."""
+        a = np.zeros(self.int("nelem"), np.int32) if new is None else np.ascontiguousarray(new, dtype=np.int32)
+        self.lib.desref_hydrous_count.argtypes = [C.c_void_p, C.c_int]
+        rc = self.lib.desref_hydrous_count(a.ctypes.data, 0 if new is None else 1)
+        return None if rc else a
+
     def call(self, fn):
         assert self.lib.desref_call(fn.encode()) == 0, fn
 

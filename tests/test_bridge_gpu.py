@@ -35,6 +35,7 @@ def run(binary, cfg, wd, **extra_env):
     ("t3d-pt.cfg", "t3dpt", 4),             # control.has_PT: the step through the twins + 3 pseudo-transient iterations
     ("t3d-pt-bfa.cfg", "t3dbf", 4),         # + initial_body_force_adjustment, prescribed tractions switched on after it
     ("t3d-nomarkers.cfg", "t3dnm", 6),      # sim.has_marker_output = no: frames written on a background thread
+    ("orift-phase.cfg", "oriftpc", 4),      # phase changes on device-resident markers + hydration (8 rock types)
 ])
 def test_driver_matches_reference_frames(cfg, model, frames, tmp_path):
     if not (os.path.exists(REF) and os.path.exists(B200)):

@@ -164,3 +164,17 @@ def test_bridge_wrap_file_through_the_reference_remesh(tmp_path):
     a, b = np.load(outs[0]), np.load(outs[1])
     for k in a.files:
         assert np.array_equal(a[k], b[k]), k
+
+
+def test_checker_code_is_not_in_the_product_binaries():
+    """The host loops of tests/hostcheck exist only in the checker libraries: neither libdes_b200.so
+    nor the bridge binary defines or imports a hostcheck symbol, and the library's transfer entry
+    points come from its own CUDA translation unit."""
+    lib = core.LIB_PATH
+    out = subprocess.run(["nm", "-D", "--defined-only", lib], capture_output=True, text=True, check=True).stdout
+    assert "des_remesh_transfer_cells" in out and "hostcheck" not in out
+    b200 = os.path.join(tc.ROOT, "bridge", "_build", "dynearthsol3d.b200")
+    if os.path.exists(b200):
+        syms = subprocess.run(["nm", b200], capture_output=True, text=True, check=True).stdout
+        assert "hostcheck" not in syms
+        assert " U des_remesh_transfer_cells" in syms       # resolved by libdes_b200.so at load time
