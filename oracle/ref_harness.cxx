@@ -703,6 +703,49 @@ int desref_transfer_nodes_case(int new_nnode, const double *new_coord, const uns
     delete v2.dppressure; delete v2.vel; delete v2.coord0;
     return 0;
 }
+// The reference's nearest_neighbor_interpolation (nn-interpolation.cxx:661) for the ELEMENT fields
+// from the current mesh onto an arbitrary new mesh; through the recorder; returns the seconds the
+// reference's call took.  The model itself is left untouched.
+static double_vec *copy_or_zeros(const double_vec *v, int n)
+{
+    return v ? new double_vec(*v) : new double_vec(n, 0.0);
+}
+double desref_transfer_cells_case(int new_nnode, const double *new_coord, int new_nelem, const int *new_conn)
+{
+    Variables v2 = *g_var;      // shallow: the pointers replaced below are the ones the call re-news
+    const int oe = g_var->nelem;
+    v2.nnode = new_nnode; v2.nelem = new_nelem;
+    v2.coord = new array_t(new_nnode);
+    std::memcpy(v2.coord->data(), new_coord, sizeof(double) * 3 * size_t(new_nnode));
+    v2.connectivity = new conn_t(new_nelem);
+    std::memcpy(v2.connectivity->data(), new_conn, sizeof(int) * 4 * size_t(new_nelem));
+    v2.remesh_is_changed = new int_vec(new_nelem);
+    v2.plstrain = copy_or_zeros(g_var->plstrain, oe);
+    v2.delta_plstrain = copy_or_zeros(g_var->delta_plstrain, oe);
+    v2.radiogenic_source = copy_or_zeros(g_var->radiogenic_source, oe);
+    v2.dyn_fric_coeff = copy_or_zeros(g_var->dyn_fric_coeff, oe);
+    v2.state_variable = copy_or_zeros(g_var->state_variable, oe);
+    v2.volume_old = copy_or_zeros(g_var->volume_old, oe);
+    v2.stressyy = copy_or_zeros(g_var->stressyy, oe);
+    v2.spr_p_ref_old = new double_vec(oe, 0.0);
+    v2.spr_blend_weight = nullptr;
+    v2.strain = new tensor_t(oe);
+    std::memcpy(v2.strain->data(), g_var->strain->data(), sizeof(double) * NSTR * size_t(oe));
+    v2.stress = new tensor_t(oe);
+    std::memcpy(v2.stress->data(), g_var->stress->data(), sizeof(double) * NSTR * size_t(oe));
+    double seconds;
+    {
+        Barycentric_transformation bary(*g_var->coord, *g_var->connectivity, *g_var->volume);
+        auto t0 = std::chrono::steady_clock::now();
+        nearest_neighbor_interpolation(*g_param, v2, bary, *g_var->coord, *g_var->connectivity, false);
+        seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+    delete v2.coord; delete v2.connectivity; delete v2.remesh_is_changed; delete v2.plstrain;
+    delete v2.delta_plstrain; delete v2.radiogenic_source; delete v2.dyn_fric_coeff; delete v2.state_variable;
+    delete v2.volume_old; delete v2.stressyy; delete v2.spr_p_ref_old; delete v2.strain; delete v2.stress;
+    return seconds;
+}
+
 // ---- the material marker set, markersets[0], through MarkerSet's own accessors ----------------
 int desref_marker_count() { return g_var->markersets[0]->get_nmarkers(); }
 // elem [n], eta [4][n], mattype [n], tmp [n] (what phase_changes leaves with set_tmp); NULL = skip

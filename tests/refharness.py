@@ -111,6 +111,19 @@ class Ref:
         assert L.desref_transfer_nodes_case(new_bcflag.size, new_coord.ctypes.data, new_bcflag.ctypes.data) == 0
         return {k: v for k, v in self._captured().items() if k.startswith("brc_")}
 
+    def transfer_cells_captured(self, new_coord, new_conn):
+        """The reference's nearest_neighbor_interpolation of the element fields from the current mesh
+        onto (new_coord [3][n], new_conn [4][e]), recorded: (the nn0_ entries, the call's seconds)."""
+        L = self.lib
+        new_coord = np.ascontiguousarray(new_coord, dtype=np.float64).reshape(-1)
+        new_conn = np.ascontiguousarray(new_conn, dtype=np.int32).reshape(-1)
+        L.desref_transfer_cells_case.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        L.desref_transfer_cells_case.restype = C.c_double
+        L.desref_capture_transfers(1)
+        sec = L.desref_transfer_cells_case(new_coord.size // 3, new_coord.ctypes.data, new_conn.size // 4,
+                                           new_conn.ctypes.data)
+        return {k: v for k, v in self._captured().items() if k.startswith("nn0_")}, sec
+
     def _captured(self):
         L = self.lib
         L.desref_captured_nbytes.argtypes = [C.c_char_p]; L.desref_captured_nbytes.restype = C.c_long
