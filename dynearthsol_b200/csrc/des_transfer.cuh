@@ -33,6 +33,7 @@
 namespace tr {
 
 constexpr int KMAX = 32;            // nn_t / ratio_t width (nn-interpolation.hpp:4-5)
+constexpr int ACM_K1 = 6;           // first, short search of find_acm_elem_ratios' sample points
 constexpr int BFS_HCAP = 32768;     // visited-set slots per node in the breadth-first search
 constexpr int BFS_FCAP = 8192;      // frontier entries per node
 
@@ -226,9 +227,20 @@ TR_HD int acm_sample_one(int e, const double *eta, int npc, int new_ncell, const
             x[d] += new_coord[size_t(d) * new_nnode + new_conn[size_t(n) * new_ncell + e]] * eta[n];
     }
     int id[KMAX]; double d2[KMAX];
-    const int cnt = knn(g, x, max_el, id, d2);
     const int dim = npc - 1;
+    // The enclosing cell is nearly always among the few nearest centroids.  The k nearest in
+    // ascending (distance, index) order are the first k of the max_el nearest, so a hit among the
+    // first ACM_K1 is the hit the full list would give; only a miss pays for the full search.
+    const int k1 = max_el < ACM_K1 ? max_el : ACM_K1;
+    int cnt = knn(g, x, k1, id, d2);
     for (int jj = 0; jj < cnt; ++jj) {
+        double r[3];
+        transform(coeff + size_t(id[jj]) * 12, dim, x, r);
+        if (is_inside(dim, r)) return id[jj];
+    }
+    if (k1 == max_el) return -1;
+    cnt = knn(g, x, max_el, id, d2);
+    for (int jj = k1; jj < cnt; ++jj) {
         double r[3];
         transform(coeff + size_t(id[jj]) * 12, dim, x, r);
         if (is_inside(dim, r)) return id[jj];
