@@ -33,12 +33,17 @@
 
 #define DES_NN  _Z30nearest_neighbor_interpolationRK5ParamR9VariablesRK26Barycentric_transformationRK7Array2DIdLi3EERKS7_IiLi4EEb
 #define DES_BRC _Z30barycentric_node_interpolationRK5ParamR9VariablesRK26Barycentric_transformationRK7Array2DIdLi3EERKS7_IiLi4EE
+#define DES_BRCT _Z35barycentric_node_interpolation_forTRK5ParamRK9VariablesRK26Barycentric_transformationRK7Array2DIdLi3EERKS8_IiLi4EERK7SupportRKSt6vectorIdSaIdEERSK_
 #define DES_CAT2(a, b) a##b
 #define DES_CAT(a, b) DES_CAT2(a, b)
 extern "C" void DES_CAT(__real_, DES_NN)(const Param &, Variables &, const Barycentric_transformation &,
                                          const array_t &, const conn_t &, const bool);
 extern "C" void DES_CAT(__real_, DES_BRC)(const Param &, Variables &, const Barycentric_transformation &,
                                           const array_t &, const conn_t &);
+
+extern "C" void DES_CAT(__real_, DES_BRCT)(const Param &, const Variables &, const Barycentric_transformation &,
+                                           const array_t &, const conn_t &, const Support &, const double_vec &,
+                                           double_vec &);
 
 namespace {
 bool use_reference()
@@ -170,4 +175,34 @@ extern "C" void DES_CAT(__wrap_, DES_BRC)(const Param &param, Variables &var,
         std::printf("    [B200] node transfer on the device: %d of %d by the wider search (%d on a face, %d outside), "
                     "search %.3f s + %.3f s, fields %.3f s\n", st.nchanged, var.nnode, st.n_on_face, st.n_outside,
                     st.search_seconds, st.acm_seconds, st.field_seconds);
+}
+
+// barycentric_node_interpolation_forT (brc-interpolation.cxx:425-443; called by ic-read-temp.cxx:154
+// to bring an external temperature field onto the mesh): the same search, one field, the input
+// mesh's own support lists.  The volumes are the ones the caller gave its Barycentric_transformation
+// (compute_volume on the input mesh, ic-read-temp.cxx:149-153): the reference's own function again.
+extern "C" void DES_CAT(__wrap_, DES_BRCT)(const Param &param, const Variables &var,
+                                           const Barycentric_transformation &bary,
+                                           const array_t &input_coord, const conn_t &input_conn,
+                                           const Support &input_support, const double_vec &input_temperature,
+                                           double_vec &output_temperature)
+{
+    if (use_reference()) {
+        DES_CAT(__real_, DES_BRCT)(param, var, bary, input_coord, input_conn, input_support, input_temperature,
+                                   output_temperature);
+        return;
+    }
+    double_vec volume(input_conn.size());
+    compute_volume(input_coord, input_conn, volume);
+    DesTransferMeshes m;
+    std::memset(&m, 0, sizeof(m));
+    m.old_nnode = input_coord.size(); m.old_coord = input_coord.data();
+    m.old_ncell = input_conn.size();  m.old_conn = input_conn.data();
+    m.old_size = volume.data();
+    m.new_nnode = var.nnode;          m.new_coord = var.coord->data();
+    DesTransferField f = { input_temperature.data(), output_temperature.data(), 1 };
+    if (int(output_temperature.size()) < var.nnode) transfer_die("barycentric_node_interpolation_forT: output too short", 3);
+    const int rc = des_remesh_transfer_nodes(transfer_device(), &m, input_support.idx_data.data(),
+                                             input_support.arr_data.data(), 1, &f, nullptr, nullptr, nullptr);
+    if (rc) transfer_die("des_remesh_transfer_nodes (external temperature)", rc);
 }

@@ -746,6 +746,27 @@ double desref_transfer_cells_case(int new_nnode, const double *new_coord, int ne
     return seconds;
 }
 
+// barycentric_node_interpolation_forT (brc-interpolation.cxx:425; ic-read-temp.cxx:154) with the
+// current mesh, its support lists and its temperature as the "input" mesh and new_coord as the
+// nodes to fill: out_T [new_nnode]
+int desref_forT_case(int new_nnode, const double *new_coord, double *out_T)
+{
+    Variables v2 = *g_var;
+    v2.nnode = new_nnode;
+    v2.coord = new array_t(new_nnode);
+    std::memcpy(v2.coord->data(), new_coord, sizeof(double) * 3 * size_t(new_nnode));
+    v2.bcflag = new uint_vec(new_nnode, 1u);        // "boundary": no warning lines for points off the mesh
+    double_vec out(new_nnode, 0.0);
+    {
+        Barycentric_transformation bary(*g_var->coord, *g_var->connectivity, *g_var->volume);
+        barycentric_node_interpolation_forT(*g_param, v2, bary, *g_var->coord, *g_var->connectivity,
+                                            g_var->support, *g_var->temperature, out);
+    }
+    std::memcpy(out_T, out.data(), sizeof(double) * size_t(new_nnode));
+    delete v2.coord; delete v2.bcflag;
+    return 0;
+}
+
 // ---- the material marker set, markersets[0], through MarkerSet's own accessors ----------------
 int desref_marker_count() { return g_var->markersets[0]->get_nmarkers(); }
 // elem [n], eta [4][n], mattype [n], tmp [n] (what phase_changes leaves with set_tmp); NULL = skip

@@ -157,7 +157,8 @@ def test_bridge_wrap_file_through_the_reference_remesh(tmp_path):
         out = str(tmp_path / ("wc%d.npz" % len(outs)))
         outs.append(out)
         procs.append(subprocess.Popen([sys.executable, script, cfg, "300", out] + extra,
-                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                                      env=dict(os.environ, OMP_NUM_THREADS="4")))
     logs = [p.communicate(timeout=600)[0].decode() for p in procs]
     assert all(p.returncode == 0 for p in procs), logs
     assert "Element ACM" in logs[0] and "Element ACM" not in logs[1]      # the second run bypassed nn-interpolation.cxx

@@ -30,7 +30,8 @@ def live_case(cfg, steps, tmp_path):
         return None
     out = os.path.join(str(tmp_path), "case.npz")
     subprocess.run([sys.executable, os.path.join(HERE, "transfer_capture.py"), os.path.join(HERE, "cfg", cfg),
-                    str(steps), out], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900)
+                    str(steps), out], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900,
+                   env=dict(os.environ, OMP_NUM_THREADS=str(min(8, os.cpu_count() or 1))))
     return load_case(out)
 
 

@@ -23,6 +23,19 @@ def main():
     work = tempfile.mkdtemp(prefix="deswc_")
     r = refharness.Ref(cfg, workdir=work, lib=lib)
     r.step(steps)
+    # barycentric_node_interpolation_forT onto the synthetic points of transfer_capture.py, with a
+    # non-trivial "input" temperature
+    import ctypes as C
+    from transfer_capture import synthetic_points
+    pts, _ = synthetic_points(r)
+    n = r.int("nnode")
+    x = r.get("coord").reshape(3, n)
+    T0 = r.get("temperature")
+    r.set("temperature", 300.0 + 1e-2 * np.abs(x[2]) + 1e-4 * x[0] + 3e-4 * x[1])
+    forT = np.empty(pts.size // 3)
+    r.lib.desref_forT_case.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+    assert r.lib.desref_forT_case(forT.size, pts.ctypes.data, forT.ctypes.data) == 0
+    r.set("temperature", T0)
     cwd = os.getcwd(); os.chdir(work)
     try:
         assert r.lib.desref_remesh(1) == 0
@@ -31,6 +44,7 @@ def main():
     r.step(5)                                   # the transferred state is stepped on
     d = {k: r.get(k) for k in FIELDS}
     d["dt"] = np.array([r.scalar("dt")])
+    d["forT"] = forT
     np.savez(out, **d)
 
 
