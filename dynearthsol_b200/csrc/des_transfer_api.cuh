@@ -90,17 +90,136 @@ __global__ void k_tr_node_locate(int nnew, const double *__restrict__ new_coord,
     if (i >= nnew) return;
     flag[i] = tr::node_locate_one(i, nnew, new_coord, g, m, nn, el, brc) ? 0 : 1;
 }
-__global__ void k_tr_node_bfs(int start, int count, const int *__restrict__ list, int nnew,
-                              const double *__restrict__ new_coord, tr::OldMesh m, const int *__restrict__ nn,
-                              int *__restrict__ table, int *__restrict__ frontier, int *__restrict__ el,
-                              double *__restrict__ brc, int *__restrict__ outcome)
+// The capped breadth-first search of prepare_interpolation (brc-interpolation.cxx:226-329), one
+// WARP per node.  tr::node_bfs_one (des_transfer.cuh) is the same search written serially -- the
+// statement of what this kernel must produce, and what the host-loop check runs; one thread
+// per node spent 22 ms on 354 hull nodes in chains of dependent global-memory trips.  Here the
+// visited set lives in shared memory and the elements around one node of a frontier element (one
+// patch, <= ~40 entries) are handled by the 32 lanes at once, in lane order = patch order:
+//   * new = not in the visited set and the lowest lane among equal ids of the batch, i.e. exactly
+//     the entries the serial walk would insert, in the same order (they are appended to the next
+//     frontier at rank popc(lower lanes));
+//   * "is inside" is decided per lane and the LOWEST hit lane wins -- the first hit of the serial walk;
+//   * the running "least outside" element takes the batch maximum only if it is strictly larger,
+//     ties inside the batch going to the lowest lane -- the serial walk's first maximum.
+__device__ __forceinline__ unsigned tr_hash(int key) { return (unsigned(key) * 2654435761u) & unsigned(tr::BFS_HCAP - 1); }
+__device__ __forceinline__ bool tr_probe(const int *table, int key)
 {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned h = tr_hash(key);
+    for (;;) {
+        const int v = table[h];
+        if (v == key) return true;
+        if (v < 0) return false;
+        h = (h + 1) & unsigned(tr::BFS_HCAP - 1);
+    }
+}
+__device__ __forceinline__ void tr_insert(int *table, int key)
+{
+    unsigned h = tr_hash(key);
+    for (;;) {
+        const int old = atomicCAS(table + h, -1, key);
+        if (old == -1 || old == key) return;
+        h = (h + 1) & unsigned(tr::BFS_HCAP - 1);
+    }
+}
+__global__ void __launch_bounds__(32) k_tr_node_bfs(int start, int count, const int *__restrict__ list, int nnew,
+                                                    const double *__restrict__ new_coord, tr::OldMesh m,
+                                                    const int *__restrict__ nn_of, int *__restrict__ frontier_all,
+                                                    int *__restrict__ el, double *__restrict__ brc,
+                                                    int *__restrict__ outcome)
+{
+    extern __shared__ int table[];                  // tr::BFS_HCAP slots, -1 = free
+    const unsigned FULL = 0xffffffffu;
+    const int t = blockIdx.x, lane = threadIdx.x;
     if (t >= count) return;
+    for (int s = lane; s < tr::BFS_HCAP; s += 32) table[s] = -1;
+    __syncwarp();
     const int i = list[start + t];
-    outcome[start + t] = tr::node_bfs_one(i, nnew, new_coord, m, nn[i], table + size_t(t) * tr::BFS_HCAP,
-                                          frontier + size_t(t) * 2 * tr::BFS_FCAP,
-                                          frontier + size_t(t) * 2 * tr::BFS_FCAP + tr::BFS_FCAP, el, brc);
+    const int nn = nn_of[i];
+    const double q[3] = {new_coord[i], new_coord[size_t(nnew) + i], new_coord[size_t(2) * nnew + i]};
+    const int *patch = m.sup_arr + m.sup_idx[nn];
+    const int np = m.sup_idx[nn + 1] - m.sup_idx[nn];
+    int *frontier = frontier_all + size_t(t) * 2 * tr::BFS_FCAP, *next = frontier + tr::BFS_FCAP;
+    if (np > tr::BFS_FCAP) { if (lane == 0) outcome[start + t] = -1; return; }
+    for (int j = lane; j < np; j += 32) { tr_insert(table, patch[j]); frontier[j] = patch[j]; }
+    __syncwarp();
+    int used = np, nf = np;
+    int best_e = (np == 0) ? 0 : patch[0];
+    double best_min = -1e30;
+    const int MAX_LAYERS = 3;
+    for (int layer = 0; layer < MAX_LAYERS && nf > 0; ++layer) {
+        int nnext = 0;
+        for (int f = 0; f < nf; ++f) {
+            const int ee = frontier[f];
+            for (int mm = 0; mm < 4; ++mm) {
+                const int npn = m.conn[size_t(mm) * m.nelem + ee];
+                const int base = m.sup_idx[npn], npe = m.sup_idx[npn + 1] - base;
+                for (int j0 = 0; j0 < npe; j0 += 32) {
+                    const int jj = j0 + lane;
+                    const bool valid = jj < npe;
+                    const int cand = valid ? m.sup_arr[base + jj] : -1 - lane;
+                    const bool seen = valid ? tr_probe(table, cand) : true;
+                    const unsigned same = __match_any_sync(FULL, cand);
+                    const bool is_new = valid && !seen && (__ffs(same) - 1 == lane);
+                    const unsigned newmask = __ballot_sync(FULL, is_new);
+                    if (!newmask) continue;
+                    const int nnew_here = __popc(newmask);
+                    if (used + nnew_here > tr::BFS_HCAP / 2) { if (lane == 0) outcome[start + t] = -1; return; }
+                    __syncwarp();
+                    if (is_new) tr_insert(table, cand);
+                    used += nnew_here;
+                    double r[3] = {0, 0, 0}, min_bary = -DBL_MAX;
+                    bool inside = false;
+                    if (is_new) {
+                        tr::transform(m.coeff + size_t(cand) * 12, 3, q, r);
+                        min_bary = r[0];
+                        for (int d = 1; d < 3; ++d) if (r[d] < min_bary) min_bary = r[d];
+                        double last = 1.0;
+                        for (int d = 0; d < 3; ++d) last -= r[d];
+                        if (last < min_bary) min_bary = last;
+                        inside = tr::is_inside(3, r);
+                    }
+                    __syncwarp();
+                    const unsigned hit = __ballot_sync(FULL, inside);
+                    if (hit) {
+                        if (lane == __ffs(hit) - 1) { tr::brc_store(i, cand, r, el, brc); outcome[start + t] = 0; }
+                        return;
+                    }
+                    double bm = min_bary; int bl = lane;
+                    for (int off = 16; off; off >>= 1) {
+                        const double om = __shfl_down_sync(FULL, bm, off);
+                        const int ol = __shfl_down_sync(FULL, bl, off);
+                        if (om > bm || (om == bm && ol < bl)) { bm = om; bl = ol; }
+                    }
+                    bm = __shfl_sync(FULL, bm, 0); bl = __shfl_sync(FULL, bl, 0);
+                    const int be = __shfl_sync(FULL, cand, bl);
+                    if (bm > best_min) { best_min = bm; best_e = be; }
+                    if (layer + 1 < MAX_LAYERS) {           // the last layer's list is never walked
+                        if (nnext + nnew_here > tr::BFS_FCAP) { if (lane == 0) outcome[start + t] = -1; return; }
+                        if (is_new) next[nnext + __popc(newmask & ((1u << lane) - 1u))] = cand;
+                        nnext += nnew_here;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        int *tmp = frontier; frontier = next; next = tmp;
+        nf = nnext;
+    }
+    if (lane != 0) return;
+    double r[3];
+    if (best_min > -1e-10) {                        // numerically on a face of best_e
+        tr::transform(m.coeff + size_t(best_e) * 12, 3, q, r);
+        tr::brc_store(i, best_e, r, el, brc);
+        outcome[start + t] = 1;
+        return;
+    }
+    // outside the old domain: the nearest old node stands in for q
+    const int e = patch[0];
+    const double qn[3] = {m.coord[nn], m.coord[size_t(m.nnode) + nn], m.coord[size_t(2) * m.nnode + nn]};
+    tr::transform(m.coeff + size_t(e) * 12, 3, qn, r);
+    tr::brc_store(i, e, r, el, brc);
+    outcome[start + t] = 2;
 }
 __global__ void k_tr_interp(int n_new, int n_old, int ncomp, const double *__restrict__ src,
                             double *__restrict__ dst, int old_nelem, const int *__restrict__ old_conn,
@@ -327,16 +446,16 @@ int des_remesh_transfer_nodes(int device, const DesTransferMeshes *m, const int 
 
     int n_face = 0, n_outside = 0;
     if (nflag) {
-        const int per_batch = std::min(nflag, 1024);
-        int *d_table, *d_frontier, *d_outcome;
-        TRK(buf.get(&d_table, size_t(per_batch) * tr::BFS_HCAP));
+        const int per_batch = std::min(nflag, 4096);
+        int *d_frontier, *d_outcome;
         TRK(buf.get(&d_frontier, size_t(per_batch) * 2 * tr::BFS_FCAP));
         TRK(buf.get(&d_outcome, size_t(nflag)));
+        const int smem = tr::BFS_HCAP * int(sizeof(int));
+        TRK(cudaFuncSetAttribute(k_tr_node_bfs, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         for (int start = 0; start < nflag; start += per_batch) {
             const int count = std::min(per_batch, nflag - start);
-            TRK(cudaMemset(d_table, 0xFF, size_t(count) * tr::BFS_HCAP * sizeof(int)));
-            k_tr_node_bfs<<<DES_GRID(count, 64), 64>>>(start, count, d_list, m->new_nnode, d_ncoord, om, d_nn,
-                                                       d_table, d_frontier, d_el, d_brc, d_outcome);
+            k_tr_node_bfs<<<count, 32, smem>>>(start, count, d_list, m->new_nnode, d_ncoord, om, d_nn,
+                                               d_frontier, d_el, d_brc, d_outcome);
         }
         TRK(cudaGetLastError());
         std::vector<int> outcome(nflag);

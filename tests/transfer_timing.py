@@ -74,11 +74,17 @@ def main():
         res_d["cells_is_changed_equal"] = bool(np.array_equal(changed, cells["nn0_is_changed"]))
         res_d["cells_fields_differing_values"] = {k: int((out[k] != cells["nn0_dst_" + k]).sum()) for k in f}
     nf = {k[8:]: v for k, v in nodes.items() if k.startswith("brc_src_")}
-    t0 = time.time()
-    outn, el, brc, stn = core.remesh_transfer_nodes(nodes["brc_old_coord"], nodes["brc_old_conn"], nodes["brc_old_size"],
-                                                    nodes["brc_old_support_idx"], nodes["brc_old_support_arr"],
-                                                    nodes["brc_new_coord"], nf)
-    res_d.update(device_nodes_s=time.time() - t0, nodes_by_wider_search=stn.nchanged, nodes_outside=stn.n_outside)
+    for rep in range(2):
+        t0 = time.time()
+        outn, el, brc, stn = core.remesh_transfer_nodes(nodes["brc_old_coord"], nodes["brc_old_conn"], nodes["brc_old_size"],
+                                                        nodes["brc_old_support_idx"], nodes["brc_old_support_arr"],
+                                                        nodes["brc_new_coord"], nf)
+        dev_nodes_s = time.time() - t0
+        if rep == 0:
+            res_d["device_nodes_first_call_s"] = dev_nodes_s
+    res_d.update(device_nodes_s=dev_nodes_s, device_nodes_locate_s=stn.search_seconds,
+                 device_nodes_wider_search_s=stn.acm_seconds, device_nodes_fields_s=stn.field_seconds,
+                 nodes_by_wider_search=stn.nchanged, nodes_outside=stn.n_outside)
     if not device_only:
         res_d["nodes_fields_differing_values"] = {k: int((outn[k] != nodes["brc_dst_" + k]).sum()) for k in nf}
         res_d["speedup_cells"] = ref_cells_s / dev_cells_s
