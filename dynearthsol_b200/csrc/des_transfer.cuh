@@ -15,9 +15,11 @@
 // FMA contraction off), so the transferred fields are bit-identical.
 //
 // Every per-item routine is a host/device inline function and the kernels are one-line loops
-// over them; tests/transfer_hostcheck.cu runs the same functions in host loops so that the
-// logic can be checked where there is no GPU (test infrastructure; the library's entry points
-// below only ever launch the kernels).
+// over them -- except the breadth-first search of the node transfer, which the device runs one
+// warp per node (des_transfer_api.cuh: k_tr_node_bfs) in the visiting order node_bfs_one below
+// states serially.  tests/hostcheck/transfer_hostcheck.cpp runs the same functions in host loops
+// so that the logic can be checked where there is no GPU (test infrastructure; the library's
+// entry points only ever launch the kernels).
 #pragma once
 #include <cfloat>
 #include <cmath>
