@@ -1,12 +1,10 @@
-# remesh field transfer on the device: the GPU tests, a memcheck pass over the recorded case, the
+# remesh field transfer on the device: the GPU tests (compute-sanitizer is closed on this pool), the
 # remeshing driver with the transfer on the device and through the reference's own functions
 set -x
 O=gpurun_out/transfer
 mkdir -p $O
 timeout 900 python -m pytest tests/test_transfer_gpu.py -m gpu -x -q -s --timeout 600 > $O/pytest_transfer.log 2>&1; echo "rc=$?" >> $O/pytest_transfer.log
 tail -25 $O/pytest_transfer.log
-timeout 400 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest tests/test_transfer_gpu.py -m gpu -x -q --timeout 380 -k "recorded or identity" > $O/memcheck.log 2>&1; echo "rc=$?" >> $O/memcheck.log
-tail -8 $O/memcheck.log
 for mode in dev ref; do
   W=/tmp/tr_$mode; mkdir -p $W
   ( cd $W; if [ $mode = ref ]; then export DES_BRIDGE_TRANSFER=ref; fi

@@ -58,6 +58,10 @@ def test_null_arguments_rejected():
     assert L.des_gpu_upload_mesh(None, None) == 3
     assert L.des_gpu_destroy(None) == 0
     assert L.des_host_build_support(0, 0, None, None, None, None) == 3
+    # device-resident markers / phase changes: argument checks come before any device work
+    assert L.des_gpu_upload_markers(None, 0, 0, None, None, None) == 3
+    assert L.des_gpu_phase_changes(None, 1, None, 0, None, None, None, None) == 3
+    assert L.des_gpu_download_elemmarkers(None, None) == 3
 
 
 def test_make_param_rejects_unknown_field():

@@ -89,6 +89,18 @@ def test_per_item_routines_reproduce_the_reference_transfer():
     assert exact.any() and not exact.all()      # the dist == 0 shortcut normalises the weights
 
 
+@pytest.mark.parametrize("resolution", [6e3, 3e3])
+def test_per_item_routines_on_tiny_meshes(resolution, tmp_path):
+    """10 and 120 elements: fewer old elements than neighbours asked for, every element changed."""
+    c = tc.tiny_box_case(resolution, tmp_path)
+    if c is None:
+        pytest.skip("oracle/_ref/libdesref.so not built")
+    L = hostcheck()
+    changed, st = tc.check_cells(c, "nn0_", False, host_cells(L))
+    assert st.nchanged == changed.size
+    tc.check_nodes(c, "brc_", host_nodes(L))
+
+
 @pytest.mark.parametrize("kind", ["random", "lattice", "flat"])
 def test_grid_knn_equals_brute_force(kind):
     L = hostcheck()

@@ -52,6 +52,18 @@ def test_transfer_matches_reference_remesh_of_test_3d_remesh(tmp_path):
              stn.search_seconds, stn.acm_seconds, stn.field_seconds))
 
 
+@pytest.mark.parametrize("resolution", [6e3, 3e3])
+def test_transfer_on_tiny_meshes(resolution, tmp_path):
+    """box-ep-tiny at 6 km (10 elements, fewer than the 32 neighbours asked for) and 3 km (120),
+    transferred onto its jittered self: every element changed; against the reference's own calls."""
+    c = tc.tiny_box_case(resolution, tmp_path)
+    if c is None:
+        pytest.skip("oracle/_ref/libdesref.so not built")
+    changed, st = tc.check_cells(c, "nn0_", False, dev_cells)
+    assert st.nchanged == changed.size
+    tc.check_nodes(c, "brc_", dev_nodes)
+
+
 def test_transfer_runs_twice_with_the_same_bits():
     c = tc.load_case(tc.GOLDEN)
     f = tc.fields_of(c, "nn0_")

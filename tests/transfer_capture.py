@@ -72,12 +72,32 @@ def synthetic_points(r, seed=7):
     return np.ascontiguousarray(pts).ravel(), bc
 
 
+def jittered(r, amount, seed=2):
+    """The current mesh with every node moved by up to `amount` resolutions (hull nodes stay on their
+    planes): the same connectivity, every centroid displaced."""
+    rng = np.random.default_rng(seed)
+    n = r.int("nnode")
+    x = r.get("coord").reshape(3, n).copy()
+    flag = r.get("bcflag")
+    d = rng.uniform(-amount, amount, (3, n)) * r.mesh_param("resolution")
+    for axis, bits in ((0, 1 | 2), (1, 4 | 8), (2, 16 | 32)):
+        d[axis, (flag & bits) != 0] = 0
+    return (x + d).ravel(), flag
+
+
 def main():
     cfg, steps, out = sys.argv[1], int(sys.argv[2]), sys.argv[3]
     slim = "--slim" in sys.argv
     work = tempfile.mkdtemp(prefix="destr_")
     r = Ref(cfg, workdir=work)
     r.step(steps)
+    if "--jitter" in sys.argv:
+        # no remesh: the reference's two transfer calls from the current mesh onto its jittered self
+        xn, flag = jittered(r, float(sys.argv[sys.argv.index("--jitter") + 1]))
+        cap, _ = r.transfer_cells_captured(xn, r.get("connectivity"))
+        cap.update(r.transfer_nodes_captured(xn, flag))
+        np.savez_compressed(out, **cap)
+        return
     xs, fs = synthetic_points(r)
     syn = r.transfer_nodes_captured(xs, fs)
     cap = {"syn_" + k[4:]: v for k, v in syn.items()}

@@ -24,13 +24,14 @@ def load_case(path):
     return c
 
 
-def live_case(cfg, steps, tmp_path):
-    """The same recording made now by the reference compiled under oracle/_ref (None if absent)."""
+def live_case(cfg, steps, tmp_path, extra=()):
+    """The same recording made now by the reference compiled under oracle/_ref (None if absent).
+    cfg: a file under tests/cfg or an absolute path; extra: more arguments for transfer_capture.py."""
     if not os.path.exists(REFLIB):
         return None
     out = os.path.join(str(tmp_path), "case.npz")
     subprocess.run([sys.executable, os.path.join(HERE, "transfer_capture.py"), os.path.join(HERE, "cfg", cfg),
-                    str(steps), out], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900,
+                    str(steps), out] + list(extra), check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900,
                    env=dict(os.environ, OMP_NUM_THREADS=str(min(8, os.cpu_count() or 1))))
     return load_case(out)
 
@@ -70,3 +71,12 @@ def check_nodes(c, pre, nodes):
     assert el.min() >= 0 and el.max() < nold
     assert np.all(np.abs(brc.sum(axis=1) - 1) < 1e-12)
     return el, brc, st
+
+
+def tiny_box_case(resolution, tmp_path):
+    """box-ep-tiny (12 x 8 x 6 km) at `resolution`, transferred onto its jittered self: at 6 km the
+    old mesh has 10 elements, fewer than the 32 neighbours find_acm_elem_ratios asks for
+    (max_el = min(32, old_nelem), nn-interpolation.cxx:99)."""
+    from conftest import cfg_variant
+    cfg, _ = cfg_variant("box-ep-tiny", {"mesh.resolution": resolution})
+    return live_case(cfg, 3, tmp_path, extra=("--jitter", "0.15"))
