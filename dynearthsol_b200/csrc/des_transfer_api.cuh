@@ -363,7 +363,9 @@ int des_remesh_transfer_cells(int device, const DesTransferMeshes *m, int is_sur
         const int max_el = std::min(tr::KMAX, m->old_ncell);
         double *d_eta; TRK(buf.get(&d_eta, eta.size()));
         TRK(cudaMemcpy(d_eta, eta.data(), eta.size() * sizeof(double), cudaMemcpyHostToDevice));
-        const int per_block = std::max(1, std::min(nchanged, (64 << 20) / nsample));
+        // cells per pass: 64 Mi sample points (256 MB of scratch); DES_TRANSFER_BLOCK overrides (tests)
+        int per_block = std::max(1, std::min(nchanged, (64 << 20) / nsample));
+        if (const char *e = std::getenv("DES_TRANSFER_BLOCK")) per_block = std::max(1, std::min(per_block, std::atoi(e)));
         int *d_found; TRK(buf.get(&d_found, size_t(per_block) * nsample));
         for (int start = 0; start < nchanged; start += per_block) {
             const int count = std::min(per_block, nchanged - start);
@@ -446,7 +448,8 @@ int des_remesh_transfer_nodes(int device, const DesTransferMeshes *m, const int 
 
     int n_face = 0, n_outside = 0;
     if (nflag) {
-        const int per_batch = std::min(nflag, 4096);
+        int per_batch = std::min(nflag, 4096);      // nodes per pass (64 KB of frontier scratch each)
+        if (const char *e = std::getenv("DES_TRANSFER_BLOCK")) per_batch = std::max(1, std::min(per_batch, std::atoi(e)));
         int *d_frontier, *d_outcome;
         TRK(buf.get(&d_frontier, size_t(per_batch) * 2 * tr::BFS_FCAP));
         TRK(buf.get(&d_outcome, size_t(nflag)));

@@ -64,6 +64,14 @@ def test_transfer_on_tiny_meshes(resolution, tmp_path):
     tc.check_nodes(c, "brc_", dev_nodes)
 
 
+def test_transfer_in_many_small_passes(monkeypatch):
+    """The sample points of the changed cells and the nodes of the wider search are processed in
+    passes that bound the scratch (64 Mi sample points / 4 096 nodes); forced down to 37 cells /
+    nodes per pass the recorded case still comes out bit-identical."""
+    monkeypatch.setenv("DES_TRANSFER_BLOCK", "37")
+    run_case(tc.load_case(tc.GOLDEN), True)
+
+
 def test_transfer_runs_twice_with_the_same_bits():
     c = tc.load_case(tc.GOLDEN)
     f = tc.fields_of(c, "nn0_")
