@@ -101,6 +101,14 @@ int des_gpu_upload_markers(DesGpu *h, int nmarkers, int stride, const int *elem,
     if (n > h->mk_cap) {                            // mesh-lifetime allocations, grown when needed
         int rc;
         const size_t cap = n + n / 8 + 1024;
+        void *old[] = { h->mk_elem, h->mk_mattype, h->mk_eta, h->mk_changed, h->mk_pos, h->mk_hyd, h->mk_out,
+                        h->mk_scan_tmp };
+        for (void *q : old) {                       // the smaller set is released now, not at the next upload_mesh
+            if (!q) continue;
+            auto it = std::find(h->mesh_allocs.begin(), h->mesh_allocs.end(), q);
+            if (it != h->mesh_allocs.end()) { cudaFree(q); h->mesh_allocs.erase(it); }
+        }
+        h->mk_cap = 0; h->mk_n = 0;
         if ((rc = dalloc(h, &h->mk_elem, cap))) return rc;
         if ((rc = dalloc(h, &h->mk_mattype, cap))) return rc;
         if ((rc = dalloc(h, &h->mk_eta, cap * 4))) return rc;

@@ -78,3 +78,28 @@ def test_phase_changes_without_hydrous_markers():
     want = np.flatnonzero((m0 != m1) & (m0 != 0))
     assert np.array_equal(cm, want) and np.array_equal(ct, m1[want])
     g.close()
+
+
+def test_marker_set_can_grow_and_shrink_between_uploads():
+    """Markers come and go on the host (surface processes, replenishment): a smaller set, then the
+    whole one (the device buffers are re-made), then a smaller one again."""
+    d = case()
+    g = refmodel.model_from_dump(d)
+    g.upload_elemmarkers(d["pc_elemmarkers0"])
+    g.upload_state(coord=d["pc_coord"], temperature=d["pc_temperature"])
+    m0, m1 = d["pc_mattype0"], d["pc_mattype1"]
+    k = 500
+    g.upload_markers(d["pc_elem"][:k], d["pc_eta"][:, :k], m0[:k])
+    cm, ct, hyd, n = g.phase_changes(option=1, hydrous_count=d["pc_hydrous"])
+    want = np.flatnonzero(m0[:k] != m1[:k])
+    assert np.array_equal(cm, want) and np.array_equal(ct, m1[want]) and hyd.size == k
+    g.upload_elemmarkers(d["pc_elemmarkers0"])      # the host's counters, as before the first call
+    g.upload_markers(d["pc_elem"], d["pc_eta"], m0)
+    cm, ct, hyd, n = g.phase_changes(option=1, hydrous_count=d["pc_hydrous"])
+    want = np.flatnonzero(m0 != m1)
+    assert np.array_equal(cm, want) and np.array_equal(ct, m1[want])
+    assert np.array_equal(g.download_elemmarkers(), d["pc_elemmarkers1"].reshape(-1, int(d["p_nmat"])))
+    g.upload_markers(d["pc_elem"][:k], d["pc_eta"][:, :k], m1[:k])
+    cm, ct, hyd, n = g.phase_changes(option=1, hydrous_count=d["pc_hydrous"])
+    assert n == 0
+    g.close()
