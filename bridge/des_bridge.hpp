@@ -39,6 +39,8 @@ int des_bridge_initial_body_force_adjustment(DesBridge *b, Param &param, Variabl
 double des_bridge_compute_dt(DesBridge *b, const Param &param, Variables &var);
 // device -> the reference's own arrays, before host code reads them
 int des_bridge_download(DesBridge *b, Variables &var, int what);
+// seconds of the device field transfers (bridge/des_transfer_wrap.cxx) inside the last remesh()
+double des_bridge_take_transfer_seconds();
 // phase_changes + refresh_elem_cache (dynearthsol.cxx:885-887) with the marker lookups on the
 // device (des_gpu_phase_changes); the changed rock types are written back into the MarkerSet
 int des_bridge_phase_changes(DesBridge *b, const Param &param, Variables &var);

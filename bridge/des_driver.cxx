@@ -191,8 +191,11 @@ int main(int argc, const char* argv[])
                     var.func_time.remesh_time += (t1 - t0) + (t4 - t3);
                     std::cout << "  [B200] download + host remesh + re-upload: ";
                     print_time_ns(t4 - t0 - (t2 - t1));
+                    const double transfer_s = des_bridge_take_transfer_seconds();
                     std::cout << "  (download " << (t1 - t0) * 1e-9 << " s, host remesh " << (t3 - t2) * 1e-9
-                              << " s, re-upload " << (t4 - t3) * 1e-9 << " s)\n";
+                              << " s";
+                    if (transfer_s > 0) std::cout << " of which field transfer on the device " << transfer_s << " s";
+                    std::cout << ", re-upload " << (t4 - t3) * 1e-9 << " s)\n";
                     if (param.sim.has_output_during_remeshing) var.output->write_exact(var);
                 }
             }

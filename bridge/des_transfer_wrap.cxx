@@ -100,7 +100,18 @@ struct Swap {
 };
 
 const bool verbose = std::getenv("DES_BRIDGE_TRANSFER_TIMING") != nullptr;
+double g_transfer_seconds = 0;      // device field transfers since the last des_bridge_take_transfer_seconds()
+void account(const DesTransferStats &st) { g_transfer_seconds += st.search_seconds + st.acm_seconds + st.field_seconds; }
 } // namespace
+
+// seconds the device field transfers took inside the remesh() that just returned (0 with
+// DES_BRIDGE_TRANSFER=ref); the driver prints them in its remesh-cycle line
+double des_bridge_take_transfer_seconds()
+{
+    const double s = g_transfer_seconds;
+    g_transfer_seconds = 0;
+    return s;
+}
 
 extern "C" void DES_CAT(__wrap_, DES_NN)(const Param &param, Variables &var,
                                          const Barycentric_transformation &bary,
@@ -129,6 +140,7 @@ extern "C" void DES_CAT(__wrap_, DES_NN)(const Param &param, Variables &var,
                                                  nullptr, &st);
         if (rc) transfer_die("des_remesh_transfer_cells (top surface)", rc);
         sw.commit();
+        account(st);
     } else {
         m.old_size = var.volume->data();                                // still the old mesh's volumes
         m.new_ncell = var.nelem; m.new_conn = var.connectivity->data();
@@ -142,6 +154,7 @@ extern "C" void DES_CAT(__wrap_, DES_NN)(const Param &param, Variables &var,
                                                  var.remesh_is_changed->data(), &st);
         if (rc) transfer_die("des_remesh_transfer_cells (elements)", rc);
         sw.commit();
+        account(st);
     }
     if (verbose)
         std::printf("    [B200] %s transfer on the device: %d of %d changed, search %.3f s, ratios %.3f s, fields %.3f s\n",
@@ -171,6 +184,7 @@ extern "C" void DES_CAT(__wrap_, DES_BRC)(const Param &param, Variables &var,
                                              nullptr, nullptr, &st);
     if (rc) transfer_die("des_remesh_transfer_nodes", rc);
     sw.commit();
+    account(st);
     if (verbose)
         std::printf("    [B200] node transfer on the device: %d of %d by the wider search (%d on a face, %d outside), "
                     "search %.3f s + %.3f s, fields %.3f s\n", st.nchanged, var.nnode, st.n_on_face, st.n_outside,

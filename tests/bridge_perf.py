@@ -31,10 +31,12 @@ def run(binary, cfg, wd, env=None):
     assert r.returncode == 0, (binary, cfg, r.stdout[-800:], r.stderr[-800:])
     m = re.search(r"Compute\s*:\s*\S+.*?/\s*(\d+)\s*=\s*([0-9.eE+-]+)\s*s/step", r.stdout)
     out = {"steps": int(m.group(1)), "compute_s_per_step": float(m.group(2))}
-    rm = re.findall(r"\[B200\] download \+ host remesh \+ re-upload:.*?\(download ([0-9.e+-]+) s, host remesh ([0-9.e+-]+) s, "
-                    r"re-upload ([0-9.e+-]+) s\)", r.stdout)
+    rm = re.findall(r"\[B200\] download \+ host remesh \+ re-upload:.*?\(download ([0-9.e+-]+) s, host remesh ([0-9.e+-]+) s"
+                    r"(?: of which field transfer on the device ([0-9.e+-]+) s)?, re-upload ([0-9.e+-]+) s\)", r.stdout)
     if rm:
-        out["remesh_cycles"] = [{"download_s": float(a), "host_remesh_s": float(b), "reupload_s": float(c)} for a, b, c in rm]
+        out["remesh_cycles"] = [{"download_s": float(a), "host_remesh_s": float(b),
+                                 "device_field_transfer_s": float(t) if t else None, "reupload_s": float(c)}
+                                for a, b, t, c in rm]
     pm = re.findall(r"\[B200\] mesh partitioned over (\d+) devices: partition ([0-9.]+) s, upload ([0-9.]+) s", r.stdout)
     if pm:
         out["partition"] = [{"parts": int(a), "partition_s": float(b), "upload_s": float(c)} for a, b, c in pm]
