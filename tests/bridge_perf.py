@@ -31,6 +31,9 @@ def run(binary, cfg, wd, env=None):
     assert r.returncode == 0, (binary, cfg, r.stdout[-800:], r.stderr[-800:])
     m = re.search(r"Compute\s*:\s*\S+.*?/\s*(\d+)\s*=\s*([0-9.eE+-]+)\s*s/step", r.stdout)
     out = {"steps": int(m.group(1)), "compute_s_per_step": float(m.group(2))}
+    m = re.search(r"Remesh\s*:\s*\S+.*?/\s*(\d+)\s*=\s*([0-9.eE+-]+)\s*s/remesh", r.stdout)
+    if m:       # the binary's own "Remesh" line (dynearthsol.cxx:1004-1011): seconds per remesh, 10 ms resolution
+        out["remesh_s_per_remesh"] = float(m.group(2))
     rm = re.findall(r"\[B200\] download \+ host remesh \+ re-upload:.*?\(download ([0-9.e+-]+) s, host remesh ([0-9.e+-]+) s"
                     r"(?: of which field transfer on the device ([0-9.e+-]+) s)?, re-upload ([0-9.e+-]+) s\)", r.stdout)
     if rm:
