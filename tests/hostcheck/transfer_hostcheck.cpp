@@ -127,12 +127,26 @@ int hostcheck_knn(int npts, const double *pts, int nq, const double *q, int k, i
     double lo[3], hi[3];
     bbox(npts, pts, false, lo, hi);
     HostGrid hg; hg.build(npts, pts, lo, hi);
+    int bad = 0;
     #pragma omp parallel for
     for (int i = 0; i < nq; ++i) {
         const double qq[3] = {q[i], q[size_t(nq) + i], q[size_t(2) * nq + i]};
         int id[tr::KMAX]; double d2[tr::KMAX];
         const int cnt = tr::knn(hg.g, qq, k, id, d2);
         for (int j = 0; j < k; ++j) idx_grid[size_t(i) * k + j] = j < cnt ? id[j] : -1;
+        // the fixed-size lists (the kernels use K = 1 for the nearest-neighbour searches) give the same entries
+        if (k == 1) {
+            tr::ListFixed<1> L; tr::knn_walk(hg.g, qq, L);
+            if (L.idx[0] != id[0] || L.d2[0] != d2[0]) {
+#pragma omp atomic
+                bad++; }
+        }
+        if (k == tr::ACM_K1 && cnt == k) {
+            tr::ListFixed<tr::ACM_K1> L; tr::knn_walk(hg.g, qq, L);
+            for (int j = 0; j < k; ++j) if (L.idx[j] != id[j] || L.d2[j] != d2[j]) {
+#pragma omp atomic
+                bad++; }
+        }
         int cb = 0; int ib[tr::KMAX]; double db[tr::KMAX];
         for (int p = 0; p < npts; ++p) {
             const double dx = qq[0] - pts[p], dy = qq[1] - pts[size_t(npts) + p], dz = qq[2] - pts[size_t(2) * npts + p];
@@ -141,7 +155,7 @@ int hostcheck_knn(int npts, const double *pts, int nq, const double *q, int k, i
         }
         for (int j = 0; j < k; ++j) idx_brute[size_t(i) * k + j] = j < cb ? ib[j] : -1;
     }
-    return 0;
+    return bad;
 }
 }
 

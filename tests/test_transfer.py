@@ -116,7 +116,7 @@ def test_grid_knn_equals_brute_force(kind):
         pts = np.concatenate([rng.uniform(0, 1e5, (2, 900)), np.zeros((1, 900))])
         q = np.concatenate([rng.uniform(-1e3, 1.01e5, (2, 300)), rng.uniform(-500, 500, (1, 300))])
     pts = np.ascontiguousarray(pts); q = np.ascontiguousarray(q)
-    for k in (1, 5, 32):
+    for k in (1, 5, 6, 32):                  # 1 and 6 (ACM_K1) also through the fixed-size lists of the kernels
         a = np.empty((q.shape[1], k), dtype=np.int32); b = np.empty_like(a)
         assert L.hostcheck_knn(pts.shape[1], pts.ctypes.data, q.shape[1], q.ctypes.data, k,
                                a.ctypes.data, b.ctypes.data) == 0
