@@ -35,7 +35,10 @@
 namespace tr {
 
 constexpr int KMAX = 32;            // nn_t / ratio_t width (nn-interpolation.hpp:4-5)
-constexpr int ACM_K1 = 6;           // first, short search of find_acm_elem_ratios' sample points
+#ifndef DES_ACM_K1
+#define DES_ACM_K1 6
+#endif
+constexpr int ACM_K1 = DES_ACM_K1;  // first, short search of find_acm_elem_ratios' sample points
 constexpr int BFS_HCAP = 32768;     // visited-set slots per node in the breadth-first search
 constexpr int BFS_FCAP = 8192;      // frontier entries per node
 
