@@ -124,6 +124,30 @@ def test_grid_knn_equals_brute_force(kind):
         assert (a >= 0).all()
 
 
+@pytest.mark.parametrize("kind", ["one-point", "coincident", "collinear", "two-cells-far-apart"])
+def test_grid_knn_on_degenerate_point_sets(kind):
+    """Point sets with no extent, or extent along one axis only: the cell grid degenerates to one
+    cell or one row of cells and the search still equals the brute-force one."""
+    L = hostcheck()
+    rng = np.random.default_rng(1)
+    if kind == "one-point":
+        pts = np.array([[3.0], [4.0], [5.0]])
+    elif kind == "coincident":
+        pts = np.tile(np.array([[1.0], [2.0], [3.0]]), (1, 40))
+    elif kind == "collinear":
+        pts = np.stack([np.linspace(0, 1e5, 300), np.full(300, 7.0), np.full(300, -2.0)])
+    else:
+        pts = np.concatenate([rng.uniform(0, 1, (3, 50)), rng.uniform(0, 1, (3, 50)) + 1e6], axis=1)
+    q = np.concatenate([pts[:, :20] + 0.25, rng.uniform(-10, 10, (3, 30)), rng.uniform(-1, 1, (3, 10)) * 2e6], axis=1)
+    pts = np.ascontiguousarray(pts); q = np.ascontiguousarray(q)
+    for k in (1, 6, 32):
+        a = np.empty((q.shape[1], k), dtype=np.int32); b = np.empty_like(a)
+        assert L.hostcheck_knn(pts.shape[1], pts.ctypes.data, q.shape[1], q.ctypes.data, k,
+                               a.ctypes.data, b.ctypes.data) == 0
+        assert np.array_equal(a, b), (kind, k)
+        assert ((a >= 0).sum(axis=1) == min(k, pts.shape[1])).all()
+
+
 def test_transfer_entry_points_check_their_arguments():
     """DES_E_ARG before any device is touched (this runs where there is none)."""
     L = core.load_library()
