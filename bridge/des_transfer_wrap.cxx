@@ -129,8 +129,9 @@ extern "C" void DES_CAT(__wrap_, DES_NN)(const Param &param, Variables &var,
     if (is_surface) {
         // the areas remesh() gave bary_surface (remeshing.cxx:2889-2892): the reference's own
         // function on the same coordinates
-        area.resize(old_conn.size());
-        for (int i = 0; i < old_conn.size(); ++i)
+        const int n_old = int(old_conn.size());
+        area.resize(n_old);
+        for (int i = 0; i < n_old; ++i)
             area[i] = compute_area_facet(old_coord.view_const(old_conn[i]));
         m.old_size = area.data();
         m.new_ncell = var.connectivity_surface->size(); m.new_conn = var.connectivity_surface->data();
