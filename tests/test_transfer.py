@@ -215,3 +215,19 @@ def test_checker_code_is_not_in_the_product_binaries():
         syms = subprocess.run(["nm", b200], capture_output=True, text=True, check=True).stdout
         assert "hostcheck" not in syms
         assert " U des_remesh_transfer_cells" in syms       # resolved by libdes_b200.so at load time
+
+
+def test_transfer_has_no_cpu_path():
+    """Valid arguments and no CUDA device: DES_E_NODEVICE, never a result computed on the host."""
+    from conftest import have_gpu
+    if have_gpu():
+        pytest.skip("a GPU is present")
+    c = tc.load_case(tc.GOLDEN)
+    with pytest.raises(core.DesError) as ei:
+        core.remesh_transfer_cells(c["nn0_old_coord"], c["nn0_old_conn"], c["nn0_old_size"], c["nn0_new_coord"],
+                                   c["nn0_new_conn"], {"plstrain": c["nn0_src_plstrain"]})
+    assert ei.value.code == 1
+    with pytest.raises(core.DesError) as ei:
+        core.remesh_transfer_nodes(c["brc_old_coord"], c["brc_old_conn"], c["brc_old_size"], c["brc_old_support_idx"],
+                                   c["brc_old_support_arr"], c["brc_new_coord"], {"temperature": c["brc_src_temperature"]})
+    assert ei.value.code == 1
